@@ -1,0 +1,53 @@
+/*
+ * b200_decoder_ops.h -- C-ABI of the ops either side of the hot path
+ * (SURVEY.md section 8(f) rows N1-N3): RMSNorm, RoPE, SiLU*mul, greedy argmax.
+ * In the reference these are MLX built-ins called by the mlx_lm layer code
+ * around `sdpa_forward` (attention/impls/sdpa.py:348-368 q/k norm + RoPE,
+ * attention/impls/varlen_rope_compat.py:70-82 batched single-token RoPE,
+ * v1/sampling_batch.py:342-348 mlx_greedy_tokens).  Same conventions as
+ * b200_paged_ops.h: device pointers, `stream` is a cudaStream_t, 0 on success.
+ */
+#ifndef B200_DECODER_OPS_H_
+#define B200_DECODER_OPS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* out[r,:] = x[r,:] * rsqrt(mean(x[r,:]^2) + eps) * weight   (mx.fast.rms_norm).
+ * If `residual` != NULL: residual[r,:] += x[r,:] first (in place, rounded to
+ * `dtype`), and the norm is taken of the updated residual (fused
+ * add + norm used between decoder sub-blocks).  `weight` may be NULL (=1). */
+int b200_rms_norm(const void* x, void* residual, const void* weight, void* out,
+                  int rows, int dim, int64_t x_stride, int64_t res_stride,
+                  int64_t out_stride, float eps, int dtype, void* stream);
+
+/* In-place rotary embedding of q [T, Hq, D] and k [T, Hk, D] (k may be NULL)
+ * at per-token positions (int32 [T]); the first rot_dim dims of each head are
+ * rotated.  traditional = 0: half-split pairs (i, i + rot_dim/2) (mlx
+ * nn.RoPE(traditional=False), the Llama/Qwen3 default); 1: interleaved pairs
+ * (2i, 2i+1).  inv_freq[i] = base^(-2i/rot_dim) computed in fp32. */
+int b200_rope(void* q, void* k, const int32_t* positions, int num_tokens,
+              int num_q_heads, int num_kv_heads, int head_dim, int rot_dim,
+              float base, int traditional, int64_t q_stride, int64_t k_stride,
+              int dtype, void* stream);
+
+/* out[r, i] = silu(gate_up[r, i]) * gate_up[r, inter + i], i in [0, inter). */
+int b200_silu_mul(const void* gate_up, void* out, int rows, int inter,
+                  int64_t in_stride, int64_t out_stride, int dtype, void* stream);
+
+/* out[r] = index of the first maximum of logits[r, :vocab] (mx.argmax). */
+int b200_argmax(const void* logits, int32_t* out, int rows, int vocab,
+                int64_t stride, int dtype, void* stream);
+
+/* y[r,:] += x[r,:] (residual add, rounded to dtype). */
+int b200_add_inplace(void* y, const void* x, int rows, int dim, int64_t y_stride,
+                     int64_t x_stride, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_DECODER_OPS_H_ */

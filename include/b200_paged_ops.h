@@ -1,0 +1,191 @@
+/*
+ * b200_paged_ops.h -- C-ABI of the B200-native decode hot path.
+ *
+ * This is the drop-in boundary "B3" of SURVEY.md section 8(b): every entry
+ * point below replaces one binding of the reference's native module
+ * `_paged_ops` (vllm_metal/metal/paged_ops.cpp:1618-1900) or, for the
+ * quantized linears, one MLX call the reference makes
+ * (vllm_metal/gguf/mlx_native.py:212-239).  Plain pointers and sizes only; no
+ * torch / MLX types.  All pointers are DEVICE pointers unless stated
+ * otherwise; `stream` is a `cudaStream_t` passed as `void*` (NULL = legacy
+ * default stream).  Every function returns 0 on success and a negative
+ * `b200_status` otherwise; `b200_last_error()` then returns a thread-local,
+ * NUL-terminated message.  Nothing here allocates device memory, synchronises
+ * the device or falls back to the host: work is enqueued on `stream` and the
+ * caller owns every buffer (same ownership rule as the reference: caches are
+ * updated in place, paged_ops.cpp:1743-1749).
+ */
+#ifndef B200_PAGED_OPS_H_
+#define B200_PAGED_OPS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 1
+
+/* Element types of activations / caches (reference: dtype_to_metal,
+ * paged_ops.cpp:185-196 -- float, half, bfloat16 are the supported set). */
+typedef enum b200_dtype {
+  B200_F32 = 0,
+  B200_F16 = 1,
+  B200_BF16 = 2
+} b200_dtype;
+
+typedef enum b200_status {
+  B200_OK = 0,
+  B200_ERR_INVALID_ARGUMENT = -1, /* reference: std::invalid_argument -> ValueError */
+  B200_ERR_RUNTIME = -2,          /* reference: std::runtime_error   -> RuntimeError */
+  B200_ERR_UNSUPPORTED = -3,      /* shape / dtype the kernels do not instantiate */
+  B200_ERR_CUDA = -4              /* a CUDA runtime call failed (message has the code) */
+} b200_status;
+
+/* Thread-local message of the last failing call on this thread ("" if none). */
+const char* b200_last_error(void);
+int b200_abi_version(void);
+
+/* Split-KV partition length in tokens.  Reference: PARTITION_SIZE = 512
+ * (vllm_metal/metal/constants.py:4, exported at paged_ops.cpp:1619-1622). */
+int b200_partition_size(void);
+
+/* Occupancy threshold of the split-KV gate: split-KV decode is engaged when
+ * `num_q_heads * total_q_tokens < b200_min_decode_grid()`.  Reference:
+ * min_decode_grid() = 8 * gpu_core_count (paged_ops.cpp:75-115); here it is a
+ * multiple of the SM count of the current device.  Returns <0 on error. */
+int b200_min_decode_grid(void);
+
+/* Number of SMs of the current device (<0 on error). */
+int b200_sm_count(void);
+
+/* ---------------------------------------------------------------------------
+ * reshape_and_cache -- replaces `_paged_ops.reshape_and_cache`
+ * (binding paged_ops.cpp:1718-1749, primitive :1117-1204, kernel
+ * kernels_v2/reshape_and_cache.metal:36-96).
+ *
+ * For every token t in [0, num_tokens): slot = slot_mapping[t]; slot < 0 is
+ * padding and is skipped (reshape_and_cache.metal:61-65); otherwise rows
+ * key[t], value[t] ([num_kv_heads, head_dim], contiguous) are copied bit for
+ * bit to cache[slot / block_size][slot % block_size].  Slots >= num_blocks *
+ * block_size are skipped as well (memory safety; the reference would write out
+ * of bounds).  Caches are [num_blocks, block_size, num_kv_heads, head_dim]
+ * with element strides `kv_block_stride` (dim 0) and `kv_token_stride`
+ * (dim 1); the [num_kv_heads, head_dim] row is contiguous.
+ * --------------------------------------------------------------------------- */
+int b200_reshape_and_cache(const void* key, const void* value, void* key_cache,
+                           void* value_cache, const int64_t* slot_mapping,
+                           int num_tokens, int num_kv_heads, int head_dim,
+                           int block_size, int64_t num_blocks,
+                           int64_t kv_block_stride, int64_t kv_token_stride,
+                           int dtype, void* stream);
+
+/* Copy-on-write block copies, `cache[dst[i]] = cache[src[i]]` for K and V.
+ * Reference: MetalPagedKVCache.copy_blocks (attention/caches/kv_cache.py:327-354).
+ * `block_bytes` = bytes of one block of one cache; src/dst are device int32. */
+int b200_copy_blocks(void* key_cache, void* value_cache, const int32_t* src,
+                     const int32_t* dst, int num_pairs, int64_t block_bytes,
+                     int64_t num_blocks, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * paged_attention -- replaces `_paged_ops.paged_attention_primitive`
+ * (binding paged_ops.cpp:1790-1854; argument set = bind_paged_attn_buffers,
+ * paged_ops.cpp:244-283; router :436-716; kernels
+ * kernels_v2/pagedattention.metal:817-1395 (per token), :1917-2144 (reduce),
+ * kernels_v2/pagedattention_tiled.metal:114-525 (varlen prefill / mixed)).
+ *
+ *   query, out    [num_q_tokens, num_q_heads, head_dim], row stride q_stride /
+ *                 out_stride elements, heads contiguous
+ *   key/value     [num_blocks, block_size, num_kv_heads, head_dim] with element
+ *                 strides kv_block_stride, kv_token_stride, kv_head_stride
+ *   block_tables  int32 [num_seqs, max_blocks_per_seq], rows padded with 0
+ *   seq_lens      int32 [num_seqs]  KV length INCLUDING this step's tokens
+ *   cu_seqlens_q  int32 [num_seqs + 1], starts at 0, ends at num_q_tokens
+ *   sinks         float32 [num_q_heads] or NULL
+ *
+ * Row r = (sequence s, position q_pos of q_len) attends KV positions
+ * [max(0, eff - W), eff) with eff = seq_len - q_len + q_pos + 1
+ * (pagedattention.metal:913, :1129-1133); W = sliding_window, < 0 disables.
+ * Softmax in the log2 domain with fp32 accumulation, optional softcap
+ * tanh(s/c)*c, sink folded once per row, out = O / (l + 1e-6)
+ * (pagedattention.metal:1138, :1318-1328, :1383).  Rows with eff <= 0 are left
+ * untouched (:917-920).
+ *
+ * `workspace` is scratch for split-KV partials; size it with
+ * b200_paged_attention_workspace_bytes() for the same args (0 is legal: the
+ * call then runs single pass).  `force_partitions`: 0 = heuristic gate,
+ * 1 = never split, >1 = split into partitions of b200_partition_size() tokens
+ * whenever max_seq_len allows (used by the parity tests to pin both routes).
+ * `kernel`: 0 = auto, 1 = generic scalar kernel, 2 = tensor-core decode kernel
+ * (fails with B200_ERR_UNSUPPORTED if the shape is not instantiated).
+ * --------------------------------------------------------------------------- */
+typedef struct b200_paged_attn_args {
+  void* out;
+  const void* query;
+  const void* key_cache;
+  const void* value_cache;
+  const int32_t* block_tables;
+  const int32_t* seq_lens;
+  const int32_t* cu_seqlens_q;
+  const float* sinks;
+  void* workspace;
+  size_t workspace_bytes;
+  int32_t num_q_tokens;
+  int32_t num_seqs;
+  int32_t num_q_heads;
+  int32_t num_kv_heads;
+  int32_t head_dim;
+  int32_t block_size;
+  int32_t max_blocks_per_seq;
+  int32_t max_seq_len;
+  int32_t sliding_window;
+  int32_t dtype;
+  int32_t force_partitions;
+  int32_t kernel;
+  int64_t q_stride;
+  int64_t out_stride;
+  int64_t kv_block_stride;
+  int64_t kv_token_stride;
+  int64_t kv_head_stride;
+  int64_t num_blocks;
+  float scale;
+  float softcap;
+} b200_paged_attn_args;
+
+size_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args* args);
+int b200_paged_attention(const b200_paged_attn_args* args, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * Affine group-quantized linears -- replace the MLX calls the reference makes:
+ * `mx.quantized_matmul(x, w, scales, biases, transpose=True, group_size, bits)`
+ * (vllm_metal/gguf/mlx_native.py:212-222; reached through
+ * nn.QuantizedLinear from attention/impls/sdpa.py:297,306,340,343,739) and
+ * `mx.dequantize(w[ids], scales[ids], biases[ids])` (mlx_native.py:232-239).
+ *
+ *   w       uint32 [N, K*bits/32]; element k of a row in word k/(32/bits) at
+ *           bit offset (k % (32/bits))*bits, lowest bits first
+ *   scales  [N, K/group_size], biases same; dtype sb_dtype
+ *   x       [M, K] row stride x_stride elements; y [M, N] row stride y_stride
+ *   bias    dense [N] of dtype `dtype` or NULL (gguf/wrappers.py:71-75)
+ *
+ *   y[m,n] = sum_k x[m,k] * (scales[n,k/g] * q[n,k] + biases[n,k/g]) (+ bias[n])
+ * fp32 accumulation, one rounding to `dtype`.  bits in {4, 8}; group_size in
+ * {32, 64, 128}; K % group_size == 0.
+ * --------------------------------------------------------------------------- */
+int b200_qlinear(const void* x, const uint32_t* w, const void* scales,
+                 const void* biases, const void* bias, void* y, int M, int N,
+                 int K, int group_size, int bits, int dtype, int sb_dtype,
+                 int64_t x_stride, int64_t y_stride, void* stream);
+
+/* out[r, :] = dequantize(row ids[r]) for r in [0, num_rows); ids == NULL means
+ * rows 0..num_rows-1 (plain mx.dequantize).  ids are int32 (token ids). */
+int b200_dequantize_rows(const uint32_t* w, const void* scales,
+                         const void* biases, const int32_t* ids, void* out,
+                         int num_rows, int N, int K, int group_size, int bits,
+                         int sb_dtype, int out_dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_PAGED_OPS_H_ */

@@ -1,0 +1,1 @@
+"""Paged-attention host side: per-step context, KV cache, SDPA forward."""

@@ -1,0 +1,107 @@
+"""Paged KV cache in HBM (reference: ``MetalPagedKVCache``,
+vllm_metal/attention/caches/kv_cache.py:37-373).
+
+Per layer one K and one V tensor ``[num_blocks, block_size, H_kv, D]``
+(token-major rows, kv_cache.py:223-234) in the model dtype.  On B200 all layers
+are carved out of ONE allocation per tensor kind (``[L, num_blocks, ...]``) so a
+180 GB part is sized with a single ``cudaMalloc`` and CoW block copies are one
+launch per layer; per-layer tensors are views into it.  Per-layer
+``kv_heads`` / ``head_dim`` / ``sliding_window`` lists are kept for models with
+mixed full/sliding layers (gpt-oss).
+"""
+
+from __future__ import annotations
+
+from collections.abc import Sequence
+
+import torch
+
+from ...metal import get_ops
+
+
+class B200PagedKVCache:
+    def __init__(
+        self,
+        num_layers: int,
+        num_kv_heads: int,
+        head_dim: int,
+        num_blocks: int,
+        block_size: int,
+        dtype: torch.dtype = torch.bfloat16,
+        device: torch.device | str = "cuda",
+        *,
+        kv_heads_per_layer: list[int] | None = None,
+        head_dim_per_layer: list[int] | None = None,
+        sliding_window_per_layer: list[int] | None = None,
+    ) -> None:
+        if dtype not in (torch.float16, torch.bfloat16, torch.float32):
+            raise ValueError(f"unsupported KV cache dtype {dtype}")
+        self.num_layers = num_layers
+        self.num_kv_heads = num_kv_heads
+        self.head_dim = head_dim
+        self.num_blocks = num_blocks
+        self.block_size = block_size
+        self.dtype = dtype
+        self.device = torch.device(device)
+        self.kv_heads_per_layer = kv_heads_per_layer or [num_kv_heads] * num_layers
+        self.head_dim_per_layer = head_dim_per_layer or [head_dim] * num_layers
+        self.sliding_window_per_layer = sliding_window_per_layer or [-1] * num_layers
+        for name, lst in (
+            ("kv_heads_per_layer", self.kv_heads_per_layer),
+            ("head_dim_per_layer", self.head_dim_per_layer),
+            ("sliding_window_per_layer", self.sliding_window_per_layer),
+        ):
+            if len(lst) != num_layers:
+                raise ValueError(f"{name} length {len(lst)} != num_layers {num_layers}")
+
+        self.key_caches: list[torch.Tensor] = []
+        self.value_caches: list[torch.Tensor] = []
+        uniform = len(set(self.kv_heads_per_layer)) == 1 and len(set(self.head_dim_per_layer)) == 1
+        if uniform:
+            shape = (num_layers, num_blocks, block_size, self.kv_heads_per_layer[0], self.head_dim_per_layer[0])
+            self._k_all = torch.zeros(shape, dtype=dtype, device=self.device)
+            self._v_all = torch.zeros(shape, dtype=dtype, device=self.device)
+            self.key_caches = [self._k_all[i] for i in range(num_layers)]
+            self.value_caches = [self._v_all[i] for i in range(num_layers)]
+        else:
+            for i in range(num_layers):
+                shape = (num_blocks, block_size, self.kv_heads_per_layer[i], self.head_dim_per_layer[i])
+                self.key_caches.append(torch.zeros(shape, dtype=dtype, device=self.device))
+                self.value_caches.append(torch.zeros(shape, dtype=dtype, device=self.device))
+
+    # -- reference API ----------------------------------------------------------
+    def block_size_for_layer(self, layer_idx: int) -> int:
+        return self.block_size
+
+    def group_index_for_layer(self, layer_idx: int) -> int:
+        return 0
+
+    def replace_layer_cache(self, layer_idx: int, key_cache: torch.Tensor, value_cache: torch.Tensor) -> None:
+        """Rebind the handles ``reshape_and_cache`` returns (kv_cache.py:310-325).
+        The op writes in place, so these alias the tensors already held."""
+        self.key_caches[layer_idx] = key_cache
+        self.value_caches[layer_idx] = value_cache
+
+    def copy_blocks(self, block_copies: Sequence[tuple[int, int]]) -> None:
+        """Scheduler copy-on-write: ``cache[dst] = cache[src]`` (kv_cache.py:327-354)."""
+        if not block_copies:
+            return
+        src_ids, dst_ids = zip(*block_copies, strict=True)
+        if any(b < 0 or b >= self.num_blocks for b in (*src_ids, *dst_ids)):
+            raise RuntimeError("paged KV block copy contains an out-of-range block id")
+        src = torch.tensor(src_ids, dtype=torch.int32, device=self.device)
+        dst = torch.tensor(dst_ids, dtype=torch.int32, device=self.device)
+        ops = get_ops()
+        for k, v in zip(self.key_caches, self.value_caches, strict=True):
+            ops.copy_blocks(k, v, src, dst)
+
+    def bytes_per_block(self) -> int:
+        esize = torch.empty((), dtype=self.dtype).element_size()
+        return sum(
+            2 * self.block_size * h * d * esize
+            for h, d in zip(self.kv_heads_per_layer, self.head_dim_per_layer, strict=True)
+        )
+
+    @property
+    def nbytes(self) -> int:
+        return self.bytes_per_block() * self.num_blocks

@@ -1,0 +1,222 @@
+// Elementwise / reduction ops either side of the hot path (include/b200_decoder_ops.h):
+// RMSNorm (+ fused residual add), RoPE, SiLU*mul, greedy argmax, residual add.
+// All HBM/launch bound; one CTA per row, fp32 math, one rounding to the I/O type.
+#include "common.cuh"
+#include "../../include/b200_decoder_ops.h"
+
+namespace b200 {
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  float t = lane < nw ? red[lane] : 0.f;
+  t = warp_sum(t);
+  __syncthreads();
+  return t;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+rms_norm_kernel(const T* __restrict__ x, T* __restrict__ residual, const T* __restrict__ weight,
+                T* __restrict__ out, int dim, int64_t x_stride, int64_t res_stride,
+                int64_t out_stride, float eps) {
+  __shared__ float red[32];
+  const int r = blockIdx.x;
+  const T* xr = x + (int64_t)r * x_stride;
+  T* rr = residual ? residual + (int64_t)r * res_stride : nullptr;
+  float ss = 0.f;
+  for (int d = threadIdx.x; d < dim; d += blockDim.x) {
+    float v = to_float(xr[d]);
+    if (rr) {
+      v = to_float(from_float<T>(v + to_float(rr[d])));  // residual stream kept in T
+      rr[d] = from_float<T>(v);
+    }
+    ss += v * v;
+  }
+  ss = block_sum(ss, red);
+  const float inv = rsqrtf(ss / (float)dim + eps);
+  T* orow = out + (int64_t)r * out_stride;
+  for (int d = threadIdx.x; d < dim; d += blockDim.x) {
+    const float v = rr ? to_float(rr[d]) : to_float(xr[d]);
+    const float w = weight ? to_float(weight[d]) : 1.f;
+    orow[d] = from_float<T>(v * inv * w);
+  }
+}
+
+// One CTA per token; threads over (head, pair).
+template <typename T>
+__global__ void __launch_bounds__(256)
+rope_kernel(T* __restrict__ q, T* __restrict__ k, const int32_t* __restrict__ positions,
+            int num_q_heads, int num_kv_heads, int head_dim, int rot_dim, float log2_base,
+            int traditional, int64_t q_stride, int64_t k_stride) {
+  const int t = blockIdx.x;
+  const float pos = (float)positions[t];
+  const int half = rot_dim >> 1;
+  const int total = (num_q_heads + (k ? num_kv_heads : 0)) * half;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const int h = idx / half, i = idx - h * half;
+    T* base = h < num_q_heads ? q + (int64_t)t * q_stride + (int64_t)h * head_dim
+                              : k + (int64_t)t * k_stride + (int64_t)(h - num_q_heads) * head_dim;
+    const float inv_freq = exp2f(-log2_base * (2.f * (float)i / (float)rot_dim));
+    float sn, cs;
+    sincosf(pos * inv_freq, &sn, &cs);
+    const int i0 = traditional ? 2 * i : i;
+    const int i1 = traditional ? 2 * i + 1 : i + half;
+    const float a = to_float(base[i0]), b = to_float(base[i1]);
+    base[i0] = from_float<T>(a * cs - b * sn);
+    base[i1] = from_float<T>(b * cs + a * sn);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+silu_mul_kernel(const T* __restrict__ gate_up, T* __restrict__ out, int inter, int64_t in_stride,
+                int64_t out_stride) {
+  const int r = blockIdx.y;
+  const T* g = gate_up + (int64_t)r * in_stride;
+  const T* u = g + inter;
+  T* o = out + (int64_t)r * out_stride;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < inter; i += gridDim.x * blockDim.x) {
+    const float a = to_float(g[i]);
+    const float s = a / (1.f + __expf(-a));
+    o[i] = from_float<T>(to_float(from_float<T>(s)) * to_float(u[i]));
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(1024)
+argmax_kernel(const T* __restrict__ logits, int32_t* __restrict__ out, int vocab, int64_t stride) {
+  __shared__ float sv[32];
+  __shared__ int si[32];
+  const int r = blockIdx.x;
+  const T* row = logits + (int64_t)r * stride;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+    const float v = to_float(row[i]);
+    if (v > best || (v == best && i < bi)) {
+      best = v;
+      bi = i;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) {
+      best = ov;
+      bi = oi;
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    sv[warp] = best;
+    si[warp] = bi;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+    best = lane < nw ? sv[lane] : -INFINITY;
+    bi = lane < nw ? si[lane] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > best || (ov == best && oi < bi)) {
+        best = ov;
+        bi = oi;
+      }
+    }
+    if (lane == 0) out[r] = bi == 0x7fffffff ? 0 : bi;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+add_inplace_kernel(T* __restrict__ y, const T* __restrict__ x, int dim, int64_t y_stride,
+                   int64_t x_stride) {
+  const int r = blockIdx.y;
+  T* yr = y + (int64_t)r * y_stride;
+  const T* xr = x + (int64_t)r * x_stride;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < dim; i += gridDim.x * blockDim.x)
+    yr[i] = from_float<T>(to_float(yr[i]) + to_float(xr[i]));
+}
+
+}  // namespace b200
+
+extern "C" int b200_rms_norm(const void* x, void* residual, const void* weight, void* out,
+                             int rows, int dim, int64_t x_stride, int64_t res_stride,
+                             int64_t out_stride, float eps, int dtype, void* stream) {
+  using namespace b200;
+  if (rows == 0) return B200_OK;
+  B200_CHECK_ARG(rows > 0 && dim > 0 && x && out, "rms_norm: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int threads = dim >= 1024 ? 256 : (dim >= 256 ? 128 : 32);
+  return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
+    rms_norm_kernel<T><<<rows, threads, 0, st>>>((const T*)x, (T*)residual, (const T*)weight,
+                                                 (T*)out, dim, x_stride, res_stride, out_stride,
+                                                 eps);
+    return check_launch("rms_norm_kernel");
+  });
+}
+
+extern "C" int b200_rope(void* q, void* k, const int32_t* positions, int num_tokens,
+                         int num_q_heads, int num_kv_heads, int head_dim, int rot_dim, float base,
+                         int traditional, int64_t q_stride, int64_t k_stride, int dtype,
+                         void* stream) {
+  using namespace b200;
+  if (num_tokens == 0) return B200_OK;
+  B200_CHECK_ARG(num_tokens > 0 && q && positions, "rope: bad arguments");
+  B200_CHECK_ARG(rot_dim > 0 && rot_dim % 2 == 0 && rot_dim <= head_dim,
+                 "rope: rot_dim (%d) must be even and <= head_dim (%d)", rot_dim, head_dim);
+  B200_CHECK_ARG(base > 0.f, "rope: base must be positive");
+  cudaStream_t st = (cudaStream_t)stream;
+  return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
+    rope_kernel<T><<<num_tokens, 256, 0, st>>>((T*)q, (T*)k, positions, num_q_heads, num_kv_heads,
+                                               head_dim, rot_dim, log2f(base), traditional,
+                                               q_stride, k_stride);
+    return check_launch("rope_kernel");
+  });
+}
+
+extern "C" int b200_silu_mul(const void* gate_up, void* out, int rows, int inter,
+                             int64_t in_stride, int64_t out_stride, int dtype, void* stream) {
+  using namespace b200;
+  if (rows == 0) return B200_OK;
+  B200_CHECK_ARG(rows > 0 && inter > 0 && gate_up && out, "silu_mul: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((inter + 1023) / 1024, rows);
+  return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
+    silu_mul_kernel<T><<<grid, 256, 0, st>>>((const T*)gate_up, (T*)out, inter, in_stride,
+                                             out_stride);
+    return check_launch("silu_mul_kernel");
+  });
+}
+
+extern "C" int b200_argmax(const void* logits, int32_t* out, int rows, int vocab, int64_t stride,
+                           int dtype, void* stream) {
+  using namespace b200;
+  if (rows == 0) return B200_OK;
+  B200_CHECK_ARG(rows > 0 && vocab > 0 && logits && out, "argmax: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
+    argmax_kernel<T><<<rows, 1024, 0, st>>>((const T*)logits, out, vocab, stride);
+    return check_launch("argmax_kernel");
+  });
+}
+
+extern "C" int b200_add_inplace(void* y, const void* x, int rows, int dim, int64_t y_stride,
+                                int64_t x_stride, int dtype, void* stream) {
+  using namespace b200;
+  if (rows == 0) return B200_OK;
+  B200_CHECK_ARG(rows > 0 && dim > 0 && y && x, "add_inplace: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((dim + 1023) / 1024, rows);
+  return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
+    add_inplace_kernel<T><<<grid, 256, 0, st>>>((T*)y, (const T*)x, dim, y_stride, x_stride);
+    return check_launch("add_inplace_kernel");
+  });
+}

@@ -1,0 +1,342 @@
+// Generic per-(token, q head) paged attention and the split-KV reduce.
+//
+// This is the any-shape CUDA path (fp32/fp16/bf16, any head_dim <= 512, any
+// power-of-two page size, varlen rows): one CTA per (q head, query row
+// [, partition]) as in the reference's per-token kernel
+// (kernels_v2/pagedattention.metal:817-1395), warp w walking tokens w, w+4, ...
+// with a per-warp online softmax in the log2 domain and a 4-warp merge.  The
+// bandwidth path for decode is paged_attention_decode.cu; this file is what
+// every other shape (and fp32) runs on, and the kernel the tensor-core paths
+// are checked against on the device.
+#include "paged_attention.cuh"
+
+namespace b200 {
+
+constexpr int kGenericWarps = 4;
+constexpr int kMaxEpl = 16;  // elements per lane: head_dim <= 512
+
+template <typename T>
+__global__ void __launch_bounds__(kGenericWarps * 32)
+paged_attention_generic_kernel(T* __restrict__ out, const T* __restrict__ query,
+                               const T* __restrict__ key_cache, const T* __restrict__ value_cache,
+                               const int32_t* __restrict__ block_tables,
+                               const int32_t* __restrict__ seq_lens,
+                               const int32_t* __restrict__ cu_seqlens_q,
+                               const float* __restrict__ sinks, int num_seqs, int num_q_heads,
+                               int num_kv_heads, int head_dim, int block_shift,
+                               int max_blocks_per_seq, int sliding_window, int64_t q_stride,
+                               int64_t out_stride, int64_t kv_block_stride,
+                               int64_t kv_token_stride, int64_t kv_head_stride, int64_t num_blocks,
+                               float scale, float softcap, SplitWorkspace ws, bool partitioned) {
+  const int h = blockIdx.x;
+  const int t = blockIdx.y;
+  const int part = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  const RowInfo ri = row_info(cu_seqlens_q, seq_lens, num_seqs, t, sliding_window);
+  const int s = ri.seq, eff = ri.eff;  // eff: pagedattention.metal:913
+  if (eff <= 0) return;                // :917-920 (row left untouched)
+
+  int lo = ri.beg, hi = eff;  // window: :1129-1133
+  if (partitioned) {
+    const int p0 = ri.base + part * ws.partition_size;
+    if (p0 >= eff) return;  // :922-926 empty partition: nothing written, reduce skips it
+    lo = max(lo, p0);
+    hi = min(hi, p0 + ws.partition_size);
+  }
+
+  const int kvh = h / (num_q_heads / num_kv_heads);  // :959-960
+  const int block_mask = (1 << block_shift) - 1;
+  const int32_t* table = block_tables + (int64_t)s * max_blocks_per_seq;
+
+  float q[kMaxEpl];
+  const T* qp = query + (int64_t)t * q_stride + (int64_t)h * head_dim;
+#pragma unroll
+  for (int i = 0; i < kMaxEpl; ++i) {
+    const int d = lane + 32 * i;
+    q[i] = d < head_dim ? to_float(qp[d]) * scale : 0.f;
+  }
+
+  float m = -INFINITY, l = 0.f;
+  float o[kMaxEpl];
+#pragma unroll
+  for (int i = 0; i < kMaxEpl; ++i) o[i] = 0.f;
+
+  for (int tok = lo + warp; tok < hi; tok += kGenericWarps) {
+    int64_t blk = table[tok >> block_shift];
+    if (blk < 0 || blk >= num_blocks) blk = 0;  // padded / corrupt entry: stay in bounds
+    const int64_t base = blk * kv_block_stride + (int64_t)(tok & block_mask) * kv_token_stride +
+                         (int64_t)kvh * kv_head_stride;
+    const T* kp = key_cache + base;
+    const T* vp = value_cache + base;
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxEpl; ++i) {
+      const int d = lane + 32 * i;
+      if (d < head_dim) dot = fmaf(q[i], to_float(kp[d]), dot);
+    }
+    dot = warp_sum(dot);
+    if (softcap > 0.f) dot = tanhf(dot / softcap) * softcap;  // :1120-1122
+    const float sc = dot * kLog2e;                            // :1138
+    const float m_new = fmaxf(m, sc);
+    const float corr = exp2f(m - m_new);  // m = -inf first time -> 0
+    const float p = exp2f(sc - m_new);
+    l = l * corr + p;
+#pragma unroll
+    for (int i = 0; i < kMaxEpl; ++i) {
+      const int d = lane + 32 * i;
+      if (d < head_dim) o[i] = fmaf(p, to_float(vp[d]), o[i] * corr);
+    }
+    m = m_new;
+  }
+
+  // ---- merge the warps (pagedattention.metal:1256-1307) ---------------------
+  extern __shared__ float smem[];
+  float* sm_m = smem;                      // [warps]
+  float* sm_l = smem + kGenericWarps;      // [warps]
+  float* sm_o = smem + 2 * kGenericWarps;  // [warps][head_dim]
+  if (lane == 0) {
+    sm_m[warp] = m;
+    sm_l[warp] = l;
+  }
+#pragma unroll
+  for (int i = 0; i < kMaxEpl; ++i) {
+    const int d = lane + 32 * i;
+    if (d < head_dim) sm_o[warp * head_dim + d] = o[i];
+  }
+  __syncthreads();
+
+  float M = -INFINITY;
+#pragma unroll
+  for (int w = 0; w < kGenericWarps; ++w) M = fmaxf(M, sm_m[w]);
+  float L = 0.f, wgt[kGenericWarps];
+#pragma unroll
+  for (int w = 0; w < kGenericWarps; ++w) {
+    wgt[w] = (sm_m[w] == -INFINITY) ? 0.f : exp2f(sm_m[w] - M);  // :1288-1289 skip empty warps
+    L += sm_l[w] * wgt[w];
+  }
+
+  if (partitioned) {
+    const int64_t row = ((int64_t)t * num_q_heads + h) * ws.num_partitions + part;
+    if (threadIdx.x == 0) {
+      ws.max_l2[row] = M;  // -inf when the whole partition is window-masked
+      ws.exp_sum[row] = L;
+    }
+    for (int d = threadIdx.x; d < head_dim; d += blockDim.x) {
+      float acc = 0.f;
+#pragma unroll
+      for (int w = 0; w < kGenericWarps; ++w) acc += sm_o[w * head_dim + d] * wgt[w];
+      ws.tmp_out[row * head_dim + d] = acc;
+    }
+    return;
+  }
+
+  if (M == -INFINITY) M = 0.f;  // everything masked (W == 0): clamp as :1169-1176
+  float c = 1.f;
+  if (sinks != nullptr) {  // :1318-1328 fold the sink once, after the merge
+    const float sk = sinks[h] * kLog2e;
+    const float M2 = fmaxf(M, sk);
+    c = exp2f(M - M2);
+    L = L * c + exp2f(sk - M2);
+  }
+  const float inv = c / (L + 1e-6f);  // :1383
+  T* op = out + (int64_t)t * out_stride + (int64_t)h * head_dim;
+  for (int d = threadIdx.x; d < head_dim; d += blockDim.x) {
+    float acc = 0.f;
+#pragma unroll
+    for (int w = 0; w < kGenericWarps; ++w) acc += sm_o[w * head_dim + d] * wgt[w];
+    op[d] = from_float<T>(acc * inv);
+  }
+}
+
+// LSE merge of the split-KV partials (reference paged_attention_v2_reduce,
+// pagedattention.metal:1917-2144): one CTA per (q head, row).
+template <typename T>
+__global__ void __launch_bounds__(128)
+split_reduce_kernel(T* __restrict__ out, const int32_t* __restrict__ seq_lens,
+                    const int32_t* __restrict__ cu_seqlens_q, const float* __restrict__ sinks,
+                    int num_seqs, int num_q_heads, int head_dim, int sliding_window,
+                    int64_t out_stride, SplitWorkspace ws) {
+  const int h = blockIdx.x, t = blockIdx.y;
+  const RowInfo ri = row_info(cu_seqlens_q, seq_lens, num_seqs, t, sliding_window);
+  const int eff = ri.eff;
+  if (eff <= 0) return;
+  int np = (eff - ri.base + ws.partition_size - 1) / ws.partition_size;  // :1946
+  np = min(np, ws.num_partitions);
+  const int64_t row = ((int64_t)t * num_q_heads + h) * ws.num_partitions;
+
+  float M = -INFINITY;
+  for (int j = 0; j < np; ++j) M = fmaxf(M, ws.max_l2[row + j]);
+  float sk = 0.f;
+  if (sinks != nullptr) {  // :2045-2072
+    sk = sinks[h] * kLog2e;
+    M = fmaxf(M, sk);
+  }
+  if (M == -INFINITY) M = 0.f;
+  float L = 0.f;
+  for (int j = 0; j < np; ++j) {
+    const float mj = ws.max_l2[row + j];
+    if (mj != -INFINITY) L += ws.exp_sum[row + j] * exp2f(mj - M);
+  }
+  if (sinks != nullptr) L += exp2f(sk - M);
+  const float inv = 1.f / (L + 1e-6f);  // :2074
+  T* op = out + (int64_t)t * out_stride + (int64_t)h * head_dim;
+  for (int d = threadIdx.x; d < head_dim; d += blockDim.x) {
+    float acc = 0.f;
+    for (int j = 0; j < np; ++j) {
+      const float mj = ws.max_l2[row + j];
+      if (mj != -INFINITY) acc += ws.tmp_out[(row + j) * head_dim + d] * exp2f(mj - M);
+    }
+    op[d] = from_float<T>(acc * inv);
+  }
+}
+
+static int log2_exact(int v) {
+  int s = 0;
+  while ((1 << s) < v) ++s;
+  return (1 << s) == v ? s : -1;
+}
+
+int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st) {
+  const int shift = log2_exact(a.block_size);
+  const size_t smem = (2 * kGenericWarps + (size_t)kGenericWarps * a.head_dim) * sizeof(float);
+  SplitWorkspace w{};
+  if (ws) w = *ws;
+  dim3 grid(a.num_q_heads, a.num_q_tokens, ws ? ws->num_partitions : 1);
+  return B200_DISPATCH_DTYPE(a.dtype, T, [&]() -> int {
+    paged_attention_generic_kernel<T><<<grid, kGenericWarps * 32, smem, st>>>(
+        (T*)a.out, (const T*)a.query, (const T*)a.key_cache, (const T*)a.value_cache,
+        a.block_tables, a.seq_lens, a.cu_seqlens_q, a.sinks, a.num_seqs, a.num_q_heads,
+        a.num_kv_heads, a.head_dim, shift, a.max_blocks_per_seq, a.sliding_window, a.q_stride,
+        a.out_stride, a.kv_block_stride, a.kv_token_stride, a.kv_head_stride, a.num_blocks,
+        a.scale, a.softcap, w, ws != nullptr);
+    return check_launch("paged_attention_generic_kernel");
+  });
+}
+
+int launch_split_reduce(const b200_paged_attn_args& a, const SplitWorkspace& ws, cudaStream_t st) {
+  dim3 grid(a.num_q_heads, a.num_q_tokens);
+  return B200_DISPATCH_DTYPE(a.dtype, T, [&]() -> int {
+    split_reduce_kernel<T><<<grid, 128, 0, st>>>((T*)a.out, a.seq_lens, a.cu_seqlens_q, a.sinks,
+                                                 a.num_seqs, a.num_q_heads, a.head_dim,
+                                                 a.sliding_window, a.out_stride, ws);
+    return check_launch("split_reduce_kernel");
+  });
+}
+
+// ---- validation + routing (reference: paged_attention_primitive_fn,
+// paged_ops.cpp:798-921, and dispatch_paged_attention_v2_online, :436-716) -----
+static int validate(const b200_paged_attn_args* a) {
+  B200_CHECK_ARG(a != nullptr, "paged_attention: args is NULL");
+  B200_CHECK_ARG(a->num_q_tokens >= 0 && a->num_seqs >= 0, "paged_attention: negative sizes");
+  if (a->num_q_tokens == 0 || a->num_seqs == 0) return B200_OK;
+  B200_CHECK_ARG(a->out && a->query && a->key_cache && a->value_cache && a->block_tables &&
+                     a->seq_lens && a->cu_seqlens_q,
+                 "paged_attention: null pointer argument");
+  B200_CHECK_ARG(a->num_q_heads > 0 && a->num_kv_heads > 0 &&
+                     a->num_q_heads % a->num_kv_heads == 0,
+                 "paged_attention: num_q_heads (%d) must be a positive multiple of num_kv_heads (%d)",
+                 a->num_q_heads, a->num_kv_heads);
+  B200_CHECK_ARG(a->head_dim > 0 && a->head_dim <= 32 * kMaxEpl,
+                 "paged_attention: head_dim %d outside (0, %d]", a->head_dim, 32 * kMaxEpl);
+  B200_CHECK_ARG(a->block_size > 0 && log2_exact(a->block_size) >= 0,
+                 "paged_attention: block_size must be a power of two, got %d", a->block_size);
+  B200_CHECK_ARG(a->max_blocks_per_seq > 0, "paged_attention: max_blocks_per_seq must be > 0");
+  B200_CHECK_ARG(a->dtype == B200_F32 || a->dtype == B200_F16 || a->dtype == B200_BF16,
+                 "paged_attention: unsupported dtype code %d", a->dtype);
+  B200_CHECK_ARG(a->num_blocks > 0, "paged_attention: num_blocks must be > 0");
+  return B200_OK;
+}
+
+// Longest KV span any row can cover: a windowed row only walks [eff-W, eff)
+// rounded out to 16-token tiles (see RowInfo).
+static int effective_span(const b200_paged_attn_args& a) {
+  int L = a.max_seq_len;
+  if (a.sliding_window >= 0 && a.sliding_window + 15 < L) L = a.sliding_window + 15;
+  return L < 1 ? 1 : L;
+}
+
+// Returns the partition length in tokens (a multiple of b200_partition_size())
+// and the partition count through *parts; parts == 1 means single pass.
+static int plan_partitions(const b200_paged_attn_args& a, bool mma, int* parts) {
+  const int unit = b200_partition_size();
+  const int span = effective_span(a);
+  const int max_parts = (span + unit - 1) / unit;  // paged_ops.cpp:520-521
+  *parts = 1;
+  if (a.force_partitions == 1 || max_parts < 2) return unit;
+  if (a.force_partitions > 1) {
+    *parts = max_parts;
+    return unit;
+  }
+  if (mma) {
+    // Bandwidth kernel: one CTA per (kv head, row, partition).  Split until the
+    // grid is a few waves of the 2 resident CTAs per SM, with partitions as long
+    // as that allows (fewer pipeline fills, smaller reduce).
+    const int64_t items = (int64_t)a.num_kv_heads * a.num_q_tokens;
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    const int64_t want = 8LL * sms;  // CTAs
+    int64_t p = (want + items - 1) / items;
+    if (p < 1) p = 1;
+    if (p > max_parts) p = max_parts;
+    int psize = (int)(((span + p - 1) / p + unit - 1) / unit) * unit;
+    *parts = (span + psize - 1) / psize;
+    return psize;
+  }
+  // Reference gate (paged_ops.cpp:539-541): pure decode && grid below occupancy bound.
+  const bool pure_decode = a.num_q_tokens == a.num_seqs;
+  const int gate = b200_min_decode_grid();
+  if (pure_decode && gate > 0 && (int64_t)a.num_q_heads * a.num_q_tokens < gate)
+    *parts = max_parts;
+  return unit;
+}
+
+static bool pick_mma(const b200_paged_attn_args& a) {
+  if (a.kernel == 1) return false;
+  return decode_mma_supported(a);
+}
+
+}  // namespace b200
+
+extern "C" size_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args* a) {
+  using namespace b200;
+  if (!a || a->num_q_tokens <= 0) return 0;
+  const int psize = b200_partition_size();
+  const int64_t P = (a->max_seq_len + psize - 1) / psize;
+  if (P < 2) return 0;
+  return split_workspace_bytes(a->num_q_tokens, a->num_q_heads, P, a->head_dim);
+}
+
+extern "C" int b200_paged_attention(const b200_paged_attn_args* a, void* stream) {
+  using namespace b200;
+  int rc = validate(a);
+  if (rc != B200_OK) return rc;
+  if (a->num_q_tokens == 0 || a->num_seqs == 0) return B200_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool mma = pick_mma(*a);
+  if (a->kernel == 2 && !mma)
+    return set_error(B200_ERR_UNSUPPORTED,
+                     "paged_attention: tensor-core decode kernel does not instantiate "
+                     "dtype=%d head_dim=%d block_size=%d group=%d",
+                     a->dtype, a->head_dim, a->block_size, a->num_q_heads / a->num_kv_heads);
+  int parts = 1;
+  const int psize = plan_partitions(*a, mma, &parts);
+  SplitWorkspace ws{};
+  if (parts > 1) {
+    const size_t need = split_workspace_bytes(a->num_q_tokens, a->num_q_heads, parts, a->head_dim);
+    if (a->workspace == nullptr || a->workspace_bytes < need) {
+      if (a->force_partitions > 1)
+        return set_error(B200_ERR_INVALID_ARGUMENT,
+                         "paged_attention: split-KV needs %zu workspace bytes, got %zu", need,
+                         a->workspace_bytes);
+      parts = 1;  // no scratch: single pass
+    } else {
+      ws = carve_workspace(a->workspace, a->num_q_tokens, a->num_q_heads, parts, a->head_dim,
+                           psize);
+    }
+  }
+  const SplitWorkspace* wsp = parts > 1 ? &ws : nullptr;
+  rc = mma ? launch_decode_mma(*a, wsp, st) : launch_generic(*a, wsp, st);
+  if (rc != B200_OK) return rc;
+  if (wsp) rc = launch_split_reduce(*a, ws, st);
+  return rc;
+}

@@ -1,0 +1,196 @@
+"""Decoder-only transformer over the paged ops (Llama / Qwen3 / gpt-oss attention).
+
+In the reference the layer wiring is third-party ``mlx_lm`` model code whose
+``self_attn`` modules are replaced by the paged-attention wrapper
+(vllm_metal/attention/impls/sdpa_wrapper.py:45-191); this file is the torch
+stand-in with the same attribute contract (``q_proj/k_proj/v_proj/o_proj`` or
+packed ``qkv_proj``, ``n_heads``, ``n_kv_heads``, ``scale``, ``q_norm``/
+``k_norm``, ``rope``, ``sinks``) so ``sdpa_forward`` duck-types it identically.
+Weights are MLX-affine quantized (``QuantizedLinear``); tensor parallelism shards
+heads / MLP columns per rank and sums o_proj / down_proj outputs with an
+allreduce.
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import torch
+from torch import nn
+
+from ..attention.impls.sdpa import sdpa_forward
+from ..metal import get_ops
+from ..quant.linear import QuantizedEmbedding, QuantizedLinear
+
+
+@dataclass
+class ModelArgs:
+    name: str
+    num_layers: int
+    hidden: int
+    n_heads: int
+    n_kv_heads: int
+    head_dim: int
+    intermediate: int
+    vocab: int
+    rms_eps: float = 1e-5
+    rope_base: float = 500000.0
+    qk_norm: bool = False
+    tie_embeddings: bool = False
+    sinks: bool = False
+    sliding_window: int = -1
+    # "full" | "sliding_attention" per layer (reference: build_sliding_window_per_layer,
+    # vllm_metal/v1/model_adapter.py:693-710)
+    layer_types: list[str] = field(default_factory=list)
+    bits: int = 4
+    group_size: int = 64
+    mlp: bool = True  # False: attention block only (gpt-oss config: MoE MLP out of scope)
+
+    def sliding_window_per_layer(self) -> list[int]:
+        if not self.layer_types:
+            return [-1] * self.num_layers
+        return [self.sliding_window if t == "sliding_attention" else -1 for t in self.layer_types]
+
+
+def _gpt_oss_layers(n: int) -> list[str]:
+    return ["sliding_attention" if i % 2 == 0 else "full_attention" for i in range(n)]
+
+
+PRESETS = {
+    "qwen3-0.6b": ModelArgs("Qwen3-0.6B", 28, 1024, 16, 8, 128, 3072, 151936, 1e-6, 1e6, True, True),
+    "llama-3.1-8b": ModelArgs("Llama-3.1-8B", 32, 4096, 32, 8, 128, 14336, 128256),
+    "qwen3-32b": ModelArgs("Qwen3-32B", 64, 5120, 64, 8, 128, 25600, 151936, 1e-6, 1e6, True, False, bits=8),
+    "llama-3.1-70b": ModelArgs("Llama-3.1-70B", 80, 8192, 64, 8, 128, 28672, 128256),
+    "gpt-oss-20b-attn": ModelArgs("gpt-oss-20b (attention blocks)", 24, 2880, 64, 8, 64, 2880, 201088, 1e-5,
+                                  150000.0, False, False, True, 128, _gpt_oss_layers(24), mlp=False),
+    "tiny": ModelArgs("tiny-test", 2, 256, 8, 2, 64, 512, 1024, 1e-6, 10000.0, True, True),
+}
+
+
+class RoPE:
+    """Parameters of ``mlx.nn.RoPE`` (dims, base, traditional); applied by ``ops.rope``."""
+
+    def __init__(self, dims: int, base: float, traditional: bool = False) -> None:
+        self.dims, self.base, self.traditional = dims, base, traditional
+
+
+class RMSNorm(nn.Module):
+    def __init__(self, dims: int, eps: float, dtype, device) -> None:
+        super().__init__()
+        self.register_buffer("weight", torch.ones(dims, dtype=dtype, device=device))
+        self.eps = eps
+
+    def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None) -> torch.Tensor:
+        return get_ops().rms_norm(x, self.weight, self.eps, residual=residual)
+
+
+def _rand_qlinear(in_f, out_f, args: ModelArgs, gen, dtype, device, std=0.02) -> QuantizedLinear:
+    w = torch.empty((out_f, in_f), dtype=torch.float32, device=device).normal_(0.0, std, generator=gen)
+    return QuantizedLinear.from_dense(w.to(dtype), None, args.group_size, args.bits, dtype)
+
+
+def _cat_rows(mods: list[QuantizedLinear]) -> QuantizedLinear:
+    """Fuse linears that share an input by stacking their output rows (row-wise
+    quantisation makes this exact)."""
+    m0 = mods[0]
+    out = QuantizedLinear(m0.in_features, sum(m.out_features for m in mods), False, m0.group_size, m0.bits,
+                          m0.scales.dtype, m0.weight.device)
+    out.weight.copy_(torch.cat([m.weight for m in mods], 0))
+    out.scales.copy_(torch.cat([m.scales for m in mods], 0))
+    out.biases.copy_(torch.cat([m.biases for m in mods], 0))
+    return out
+
+
+class Attention(nn.Module):
+    def __init__(self, args: ModelArgs, gen, dtype, device, rank: int, world: int) -> None:
+        super().__init__()
+        if args.n_kv_heads % world:
+            raise ValueError(f"n_kv_heads {args.n_kv_heads} not divisible by TP size {world}")
+        self.n_heads = args.n_heads // world
+        self.n_kv_heads = args.n_kv_heads // world
+        self.head_dim = args.head_dim
+        self.scale = args.head_dim ** -0.5
+        d = args.head_dim
+        q = _rand_qlinear(args.hidden, args.n_heads * d, args, gen, dtype, device).shard_rows(rank, world)
+        k = _rand_qlinear(args.hidden, args.n_kv_heads * d, args, gen, dtype, device).shard_rows(rank, world)
+        v = _rand_qlinear(args.hidden, args.n_kv_heads * d, args, gen, dtype, device).shard_rows(rank, world)
+        self.qkv_proj = _cat_rows([q, k, v])
+        self.o_proj = _rand_qlinear(args.n_heads * d, args.hidden, args, gen, dtype, device).shard_cols(rank, world)
+        if args.qk_norm:
+            self.q_norm = RMSNorm(d, args.rms_eps, dtype, device)
+            self.k_norm = RMSNorm(d, args.rms_eps, dtype, device)
+        else:
+            self.q_norm = self.k_norm = None
+        self.rope = RoPE(d, args.rope_base, False)
+        if args.sinks:
+            full = torch.empty(args.n_heads, dtype=torch.float32, device=device).normal_(0.0, 1.0, generator=gen)
+            self.register_buffer("sinks", full[rank * self.n_heads:(rank + 1) * self.n_heads].clone())
+        else:
+            self.sinks = None
+
+
+class MLP(nn.Module):
+    def __init__(self, args: ModelArgs, gen, dtype, device, rank: int, world: int) -> None:
+        super().__init__()
+        gate = _rand_qlinear(args.hidden, args.intermediate, args, gen, dtype, device).shard_rows(rank, world)
+        up = _rand_qlinear(args.hidden, args.intermediate, args, gen, dtype, device).shard_rows(rank, world)
+        self.gate_up_proj = _cat_rows([gate, up])
+        self.down_proj = _rand_qlinear(args.intermediate, args.hidden, args, gen, dtype, device).shard_cols(rank, world)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.down_proj(get_ops().silu_mul(self.gate_up_proj(x)))
+
+
+class DecoderLayer(nn.Module):
+    def __init__(self, args: ModelArgs, gen, dtype, device, rank: int, world: int) -> None:
+        super().__init__()
+        self.self_attn = Attention(args, gen, dtype, device, rank, world)
+        self.input_layernorm = RMSNorm(args.hidden, args.rms_eps, dtype, device)
+        self.mlp = MLP(args, gen, dtype, device, rank, world) if args.mlp else None
+        self.post_attention_layernorm = RMSNorm(args.hidden, args.rms_eps, dtype, device) if args.mlp else None
+
+
+class Model(nn.Module):
+    """``forward(input_ids [T], ctx|meta, kv_cache) -> logits`` for the packed batch."""
+
+    def __init__(self, args: ModelArgs, dtype=torch.bfloat16, device="cuda", seed: int = 0,
+                 rank: int = 0, world: int = 1, allreduce=None) -> None:
+        super().__init__()
+        self.args = args
+        self.rank, self.world = rank, world
+        self._allreduce = allreduce
+        gen = torch.Generator(device=device).manual_seed(seed)
+        emb = torch.empty((args.vocab, args.hidden), dtype=torch.float32, device=device).normal_(0, 0.02, generator=gen)
+        self.embed_tokens = QuantizedEmbedding.from_dense(emb.to(dtype), args.group_size, args.bits, dtype)
+        del emb
+        self.layers = nn.ModuleList(
+            [DecoderLayer(args, gen, dtype, device, rank, world) for _ in range(args.num_layers)])
+        self.norm = RMSNorm(args.hidden, args.rms_eps, dtype, device)
+        if args.tie_embeddings:
+            self.lm_head = None
+        else:
+            self.lm_head = _rand_qlinear(args.hidden, args.vocab, args, gen, dtype, device)
+
+    def _reduce(self, x: torch.Tensor) -> torch.Tensor:
+        if self.world > 1:
+            self._allreduce(x)
+        return x
+
+    def forward(self, input_ids: torch.Tensor, ctx, kv_cache, meta=None, logits_rows=None) -> torch.Tensor:
+        h = self.embed_tokens(input_ids)  # residual stream [T, hidden]
+        delta = None
+        for i, layer in enumerate(self.layers):
+            x = layer.input_layernorm(h if delta is None else delta, residual=None if delta is None else h)
+            a = self._reduce(sdpa_forward(layer.self_attn, x, ctx, kv_cache, i, meta=meta))
+            if layer.mlp is None:
+                delta = a
+                continue
+            x = layer.post_attention_layernorm(a, residual=h)  # h += a; x = norm(h)
+            delta = self._reduce(layer.mlp(x))
+        x = self.norm(delta, residual=h) if delta is not None else self.norm(h)
+        if logits_rows is not None:
+            x = x.index_select(0, logits_rows)
+        return self.embed_tokens.as_linear(x) if self.lm_head is None else self.lm_head(x)
+
+    def weight_bytes(self) -> int:
+        return sum(b.numel() * b.element_size() for b in self.buffers())

@@ -1,0 +1,127 @@
+"""``QuantizedLinear`` / ``QuantizedEmbedding`` with the MLX module protocol.
+
+The reference's hot-path linears are ``mlx.nn.QuantizedLinear`` objects whose
+``__call__`` is ``mx.quantized_matmul(x, weight, scales, biases, transpose=True,
+group_size, bits)`` (+ ``bias``); loaders and LoRA/AWQ code duck-type them by
+``hasattr(bits) and hasattr(group_size)`` and read ``in = scales.shape[1] *
+group_size``, ``out = scales.shape[0]`` (vllm_metal/quant/awq_loader.py:165-180,
+v1/lora/layers.py:21-50).  These torch modules keep those attribute names and
+shapes and call the sm_100a kernel through ``get_ops()``.
+"""
+
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from ..metal import get_ops
+from .affine import quantize
+
+
+class QuantizedLinear(nn.Module):
+    def __init__(self, in_features: int, out_features: int, bias: bool = False, group_size: int = 64,
+                 bits: int = 4, dtype: torch.dtype = torch.bfloat16, device=None) -> None:
+        super().__init__()
+        if in_features % group_size:
+            raise ValueError(f"in_features {in_features} not divisible by group_size {group_size}")
+        self.group_size = group_size
+        self.bits = bits
+        words = in_features * bits // 32
+        self.register_buffer("weight", torch.zeros((out_features, words), dtype=torch.int32, device=device))
+        self.register_buffer("scales", torch.zeros((out_features, in_features // group_size), dtype=dtype, device=device))
+        self.register_buffer("biases", torch.zeros((out_features, in_features // group_size), dtype=dtype, device=device))
+        if bias:
+            self.register_buffer("bias", torch.zeros((out_features,), dtype=dtype, device=device))
+        else:
+            self.bias = None
+
+    @property
+    def in_features(self) -> int:
+        return self.scales.shape[1] * self.group_size
+
+    @property
+    def out_features(self) -> int:
+        return self.scales.shape[0]
+
+    @classmethod
+    def from_dense(cls, weight: torch.Tensor, bias: torch.Tensor | None = None, group_size: int = 64,
+                   bits: int = 4, dtype: torch.dtype = torch.bfloat16) -> QuantizedLinear:
+        out_f, in_f = weight.shape
+        m = cls(in_f, out_f, bias is not None, group_size, bits, dtype, weight.device)
+        w, s, b = quantize(weight, group_size, bits, dtype)
+        m.weight.copy_(w)
+        m.scales.copy_(s)
+        m.biases.copy_(b)
+        if bias is not None:
+            m.bias.copy_(bias.to(dtype))
+        return m
+
+    def shard_rows(self, rank: int, world: int) -> QuantizedLinear:
+        """Column-parallel shard: rows (output features) [rank*N/world, ...)."""
+        n = self.out_features
+        if n % world:
+            raise ValueError(f"out_features {n} not divisible by world size {world}")
+        lo, hi = rank * n // world, (rank + 1) * n // world
+        m = QuantizedLinear(self.in_features, hi - lo, self.bias is not None, self.group_size, self.bits,
+                            self.scales.dtype, self.weight.device)
+        m.weight.copy_(self.weight[lo:hi])
+        m.scales.copy_(self.scales[lo:hi])
+        m.biases.copy_(self.biases[lo:hi])
+        if self.bias is not None:
+            m.bias.copy_(self.bias[lo:hi])
+        return m
+
+    def shard_cols(self, rank: int, world: int) -> QuantizedLinear:
+        """Row-parallel shard along K; K/world must be a multiple of group_size.
+        The dense bias stays on rank 0 only (added once after the allreduce)."""
+        k = self.in_features
+        if k % world or (k // world) % self.group_size:
+            raise ValueError(f"in_features {k} / {world} must be a multiple of group_size {self.group_size}")
+        kw = k // world
+        wl, wh = rank * kw * self.bits // 32, (rank + 1) * kw * self.bits // 32
+        gl, gh = rank * kw // self.group_size, (rank + 1) * kw // self.group_size
+        m = QuantizedLinear(kw, self.out_features, self.bias is not None and rank == 0, self.group_size,
+                            self.bits, self.scales.dtype, self.weight.device)
+        m.weight.copy_(self.weight[:, wl:wh])
+        m.scales.copy_(self.scales[:, gl:gh])
+        m.biases.copy_(self.biases[:, gl:gh])
+        if m.bias is not None:
+            m.bias.copy_(self.bias)
+        return m
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return get_ops().quantized_matmul(x, self.weight, self.scales, self.biases, transpose=True,
+                                          group_size=self.group_size, bits=self.bits, bias=self.bias)
+
+
+class QuantizedEmbedding(nn.Module):
+    """Quantized token embedding; ``as_linear`` is the tied lm_head
+    (reference: gguf/mlx_native.py:224-240, gguf/wrappers.py:88-116)."""
+
+    def __init__(self, num_embeddings: int, dims: int, group_size: int = 64, bits: int = 4,
+                 dtype: torch.dtype = torch.bfloat16, device=None) -> None:
+        super().__init__()
+        self.group_size = group_size
+        self.bits = bits
+        self.register_buffer("weight", torch.zeros((num_embeddings, dims * bits // 32), dtype=torch.int32, device=device))
+        self.register_buffer("scales", torch.zeros((num_embeddings, dims // group_size), dtype=dtype, device=device))
+        self.register_buffer("biases", torch.zeros((num_embeddings, dims // group_size), dtype=dtype, device=device))
+
+    @classmethod
+    def from_dense(cls, weight: torch.Tensor, group_size: int = 64, bits: int = 4,
+                   dtype: torch.dtype = torch.bfloat16) -> QuantizedEmbedding:
+        n, d = weight.shape
+        m = cls(n, d, group_size, bits, dtype, weight.device)
+        w, s, b = quantize(weight, group_size, bits, dtype)
+        m.weight.copy_(w)
+        m.scales.copy_(s)
+        m.biases.copy_(b)
+        return m
+
+    def forward(self, ids: torch.Tensor) -> torch.Tensor:
+        return get_ops().dequantize(self.weight, self.scales, self.biases, self.group_size, self.bits,
+                                    ids=ids, dtype=self.scales.dtype)
+
+    def as_linear(self, x: torch.Tensor) -> torch.Tensor:
+        return get_ops().quantized_matmul(x, self.weight, self.scales, self.biases, transpose=True,
+                                          group_size=self.group_size, bits=self.bits)

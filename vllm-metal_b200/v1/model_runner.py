@@ -1,0 +1,199 @@
+"""Paged-generate runner: packs a step, runs the model, returns greedy tokens.
+
+Covers the paged path of the reference's ``MetalModelRunner``
+(vllm_metal/v1/model_runner.py: ``_start_paged_forward`` :1138-1410 packs decode
+rows first then prefill chunks and calls ``prepare_grouped``; ``sample_tokens``
+:2733-2783 takes the last row of every segment; greedy = ``mlx_greedy_tokens``,
+v1/sampling_batch.py:342-348).  B200 design: all per-step integer metadata
+travels in ONE pinned staging buffer -> one H2D copy into persistent device
+buffers, the decode forward is a CUDA graph replayed per step (captured per
+batch size and split-KV bucket), and the only D2H is the sampled token ids.
+The reference's deferred one-step-ahead sampling (v1/decode_pipeline.py) is
+replaced by stream order + the graph.
+"""
+
+from __future__ import annotations
+
+from collections.abc import Sequence
+
+import numpy as np
+import torch
+
+from ..attention.context import clear_context, get_context, prepare_unified
+from ..attention.impls.sdpa import _KernelMetadata, _kernel_metadata
+from ..metal import get_ops
+from ..metal.constants import PARTITION_SIZE
+
+
+class StepBuffers:
+    """Persistent device metadata for a fixed-capacity decode batch + its pinned mirror."""
+
+    def __init__(self, max_batch: int, max_blocks: int, device) -> None:
+        self.max_batch, self.max_blocks = max_batch, max_blocks
+        b = max_batch
+        # layout in int32 words: slot_mapping (int64 -> 2b words, first for alignment)
+        sizes = {"slot_mapping": 2 * b, "input_ids": b, "positions": b, "seq_lens": b,
+                 "cu_seqlens": b + 2, "block_tables": b * max_blocks}
+        self.offsets, off = {}, 0
+        for k, n in sizes.items():
+            self.offsets[k] = (off, n)
+            off += n + (n & 1)  # keep every field 8-byte aligned
+        self.words = off
+        self.host = torch.zeros(off, dtype=torch.int32).pin_memory()
+        self.dev = torch.zeros(off, dtype=torch.int32, device=device)
+        self.host_np = self.host.numpy()
+        self.out_tokens = torch.zeros(b, dtype=torch.int32, device=device)
+        self.out_host = torch.zeros(b, dtype=torch.int32).pin_memory()
+
+    def view(self, name: str, on_host: bool = False):
+        off, n = self.offsets[name]
+        src = self.host if on_host else self.dev
+        v = src[off:off + n]
+        if name == "slot_mapping":
+            return v.view(torch.int64)
+        if name == "cu_seqlens":
+            return v[: self.max_batch + 1]
+        if name == "block_tables":
+            return v.view(self.max_batch, self.max_blocks)
+        return v
+
+    def np_view(self, name: str):
+        off, n = self.offsets[name]
+        v = self.host_np[off:off + n]
+        if name == "slot_mapping":
+            return v.view(np.int64)
+        if name == "cu_seqlens":
+            return v[: self.max_batch + 1]
+        if name == "block_tables":
+            return v.reshape(self.max_batch, self.max_blocks)
+        return v
+
+    def upload(self) -> int:
+        self.dev.copy_(self.host, non_blocking=True)
+        return self.words * 4
+
+
+class PagedModelRunner:
+    """Greedy generation over a paged KV cache (single KV group)."""
+
+    def __init__(self, model, kv_cache, *, max_batch: int = 64, max_model_len: int = 8192,
+                 use_cuda_graph: bool = True) -> None:
+        self.model, self.kv_cache = model, kv_cache
+        self.device = kv_cache.device
+        self.block_size = kv_cache.block_size
+        self.max_batch = max_batch
+        self.max_blocks = (max_model_len + self.block_size - 1) // self.block_size
+        self.use_cuda_graph = use_cuda_graph
+        self.buf = StepBuffers(max_batch, self.max_blocks, self.device)
+        self._graphs: dict[tuple[int, int], torch.cuda.CUDAGraph] = {}
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # -- generic (eager) path: any mix of prefill chunks and decode rows -----------
+    def execute(self, input_ids: Sequence[int], decode_requests, prefill_requests) -> list[int]:
+        """One packed forward; returns the greedy token of every segment's last row.
+
+        ``decode_requests``: ``(block_ids, seq_len)``; ``prefill_requests``:
+        ``(block_ids, num_tokens, start_pos)`` -- the ``prepare_unified`` contract.
+        """
+        prepare_unified(decode_requests, prefill_requests, self.block_size)
+        ctx = get_context()
+        try:
+            ids = torch.tensor(list(input_ids), dtype=torch.int32).pin_memory().to(self.device, non_blocking=True)
+            last_rows = torch.tensor([c - 1 for c in ctx.cu_seqlens[1:]], dtype=torch.int64).pin_memory().to(
+                self.device, non_blocking=True)
+            logits = self.model(ids, ctx, self.kv_cache, logits_rows=last_rows)
+            toks = get_ops().argmax(logits)
+            return toks.cpu().tolist()
+        finally:
+            clear_context()
+
+    # -- decode fast path: fixed batch, persistent buffers, CUDA graph ---------------
+    def _meta(self, batch: int, max_seq_len: int) -> _KernelMetadata:
+        b = self.buf
+        return _KernelMetadata(
+            slot_mapping=b.view("slot_mapping")[:batch],
+            seq_lens=b.view("seq_lens")[:batch],
+            cu_seqlens_q=b.view("cu_seqlens")[: batch + 1],
+            block_tables=b.view("block_tables")[:batch],
+            block_size=self.block_size,
+            max_seq_len=max_seq_len,
+            positions=b.view("positions")[:batch],
+        )
+
+    def _forward_decode(self, batch: int, max_seq_len: int) -> None:
+        meta = self._meta(batch, max_seq_len)
+        logits = self.model(self.buf.view("input_ids")[:batch], None, self.kv_cache, meta=meta)
+        get_ops().argmax(logits, out=self.buf.out_tokens[:batch])
+
+    def _bucket(self, max_seq_len: int) -> int:
+        """Graphs are keyed by the split-KV bucket: max_seq_len rounded up to a
+        multiple of PARTITION_SIZE (the partition plan depends only on it)."""
+        return (max_seq_len + PARTITION_SIZE - 1) // PARTITION_SIZE * PARTITION_SIZE
+
+    def fill_decode(self, token_ids: Sequence[int], block_ids: Sequence[Sequence[int]],
+                    seq_lens: Sequence[int]) -> int:
+        """Write one decode step's metadata into the pinned mirror (no GPU work).
+        ``seq_lens`` = tokens already cached per request.  Returns max KV length."""
+        b, n = self.buf, len(token_ids)
+        pos = np.asarray(seq_lens, dtype=np.int64)
+        tables = b.np_view("block_tables")
+        for i, ids in enumerate(block_ids):
+            tables[i, : len(ids)] = ids
+        blk = tables[np.arange(n), pos // self.block_size].astype(np.int64)
+        b.np_view("slot_mapping")[:n] = blk * self.block_size + pos % self.block_size
+        b.np_view("input_ids")[:n] = np.asarray(token_ids, dtype=np.int32)
+        b.np_view("positions")[:n] = pos
+        b.np_view("seq_lens")[:n] = pos + 1
+        b.np_view("cu_seqlens")[: n + 1] = np.arange(n + 1, dtype=np.int32)
+        return int(pos.max()) + 1
+
+    def decode_step(self, token_ids, block_ids, seq_lens, *, sync: bool = True):
+        """One pure-decode step through the public runner API: host metadata ->
+        pinned -> H2D -> (graph) forward -> D2H token ids."""
+        n = len(token_ids)
+        max_len = self.fill_decode(token_ids, block_ids, seq_lens)
+        self.h2d_bytes += self.buf.upload()
+        self.run_decode(n, max_len)
+        self.buf.out_host[:n].copy_(self.buf.out_tokens[:n], non_blocking=True)
+        self.d2h_bytes += n * 4
+        if sync:
+            torch.cuda.current_stream().synchronize()
+            return self.buf.out_host[:n].tolist()
+        return None
+
+    def run_decode(self, batch: int, max_seq_len: int) -> None:
+        """Forward + argmax over the persistent buffers (graph replay when enabled)."""
+        if not self.use_cuda_graph:
+            self._forward_decode(batch, max_seq_len)
+            return
+        key = (batch, self._bucket(max_seq_len))
+        g = self._graphs.get(key)
+        if g is None:
+            # warm up on a side stream (lazy module load, workspace growth), then capture
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                self._forward_decode(batch, key[1])
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._forward_decode(batch, key[1])
+            self._graphs[key] = g
+        g.replay()
+
+    def advance_on_device(self, batch: int) -> None:
+        """Device-side bookkeeping for back-to-back decode steps with no host in
+        the loop: feed the sampled tokens back and move every request one slot on."""
+        b = self.buf
+        pos = b.view("positions")[:batch]
+        pos.add_(1)
+        b.view("seq_lens")[:batch].add_(1)
+        b.view("input_ids")[:batch].copy_(b.out_tokens[:batch])
+        p64 = pos.to(torch.int64)
+        blk = b.view("block_tables")[:batch].gather(1, (p64 // self.block_size).unsqueeze(1)).squeeze(1)
+        b.view("slot_mapping")[:batch].copy_(blk.to(torch.int64) * self.block_size + p64 % self.block_size)
+
+
+__all__ = ["PagedModelRunner", "StepBuffers", "_kernel_metadata"]
