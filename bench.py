@@ -1,0 +1,391 @@
+#!/usr/bin/env python
+"""Headline benchmark: decode tok/s, Llama-3.1-8B affine int4 (g64), paged decode bs=64 ctx 4k.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+A "step" is one decode step of the whole model for the whole batch (32 layers of
+quantized qkv -> RoPE -> reshape_and_cache -> paged attention -> o_proj -> SwiGLU MLP, final
+norm, lm_head, greedy argmax) = 64 new tokens.  Synthetic data: random-init weights of the
+real architecture, KV pool pre-filled with N(0,1) at ctx 4096, pages in a random permutation.
+
+* ``value``      tokens/s with everything resident in HBM (CUDA-graph replay, device-side
+                 token feedback), CUDA events, max over ranks.
+* ``e2e``        same metric through the public runner API ``PagedModelRunner.decode_step``
+                 with HOST inputs: per step host lists -> pinned -> H2D, graph, D2H token ids.
+* ``roofline``   the dominant kernel (paged decode attention), timed live with CUDA events
+                 over all 32 layers' caches (32 GiB working set >> L2), algorithmic bytes/launch.
+* ``cpu_baseline`` the oracle's C port on the host cores over a bounded sample (rank 0, N=1).
+* N > 1: tensor parallel over heads / MLP columns, NCCL allreduce after o_proj and down_proj
+  (strong scaling: the global batch is fixed at 64).
+* ``--impl reference``: the reference path's CPU restatement (oracle C port; the reference's
+  own native code is Apple/Metal-only and cannot be built here) on the host cores.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+MODEL = "llama-3.1-8b"
+BATCH = 64
+CTX = 4096
+BLOCK = 16
+METRIC = "decode tok/s (Llama-3.1-8B int4, bs=64)"
+WORKLOAD = "Llama-3.1-8B affine int4 g64 random-init, paged decode bs=64 ctx 4096 block_size 16 (configs[1])"
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured"
+    except Exception:  # noqa: BLE001
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int) -> None:
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6], strict=True):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ CPU baseline ---
+
+class CpuSample:
+    """One decode layer (+ scaled lm_head) of the workload on the host cores, oracle C port."""
+
+    def __init__(self, seed: int = 0, batch: int = BATCH, ctx: int = CTX) -> None:
+        import numpy as np
+
+        from oracle import cport
+        from vllm_metal_b200.lm.decoder import PRESETS
+
+        self.np, self.cport = np, cport
+        a = self.a = PRESETS[MODEL]
+        rng = np.random.default_rng(seed)
+        self.batch = batch
+        hkv, hq, d = a.n_kv_heads, a.n_heads, a.head_dim
+        nblk = batch * ((ctx + BLOCK) // BLOCK + 1)
+        bf = lambda shape: rng.integers(0x3C00, 0x3F80, shape, dtype=np.uint16)  # noqa: E731  bf16 in [1, 2)
+        self.bf = bf
+        self.rng = rng
+        self.kc, self.vc = bf((nblk, BLOCK, hkv, d)), bf((nblk, BLOCK, hkv, d))
+        self.bt = rng.permutation(nblk).astype(np.int32).reshape(batch, -1)
+        self.cu = np.arange(batch + 1, dtype=np.int32)
+        self.seq = np.full(batch, ctx + 1, np.int32)
+        self.slots = self.bt[np.arange(batch), ctx // BLOCK].astype(np.int64) * BLOCK + ctx % BLOCK
+        self.pos = np.full(batch, ctx, np.int32)
+        self.wqkv, self.wo = self.qw((hq + 2 * hkv) * d, a.hidden), self.qw(a.hidden, hq * d)
+        self.wgu, self.wdn = self.qw(2 * a.intermediate, a.hidden), self.qw(a.hidden, a.intermediate)
+        self.norm_w = bf((a.hidden,))
+        self.h = bf((batch, a.hidden))
+        self.threads = cport.num_threads()
+
+    def qw(self, n, k):
+        np, a = self.np, self.a
+        return (self.rng.integers(0, 2**32, (n, k // 8), dtype=np.uint32), self.bf((n, k // a.group_size)),
+                self.bf((n, k // a.group_size)))
+
+    def layer(self) -> float:
+        np, cport, a, batch = self.np, self.cport, self.a, self.batch
+        hkv, hq, d, g, b = a.n_kv_heads, a.n_heads, a.head_dim, a.group_size, a.bits
+        t0 = time.perf_counter()
+        x = cport.rms_norm(self.h, self.norm_w, a.rms_eps)
+        qkv = cport.qmatmul(x, *self.wqkv, g, b)
+        q = np.ascontiguousarray(qkv[:, :hq * d]).reshape(batch, hq, d)
+        k = np.ascontiguousarray(qkv[:, hq * d:(hq + hkv) * d]).reshape(batch, hkv, d)
+        v = np.ascontiguousarray(qkv[:, (hq + hkv) * d:]).reshape(batch, hkv, d)
+        cport.rope_(q, self.pos, a.rope_base)
+        cport.rope_(k, self.pos, a.rope_base)
+        cport.reshape_and_cache(k, v, self.kc, self.vc, self.slots)
+        o = cport.paged_attention(q, self.kc, self.vc, self.bt, self.seq, self.cu, d ** -0.5)
+        att = cport.qmatmul(o.reshape(batch, hq * d), *self.wo, g, b)
+        res = self.h.copy()
+        x = cport.rms_norm(att, self.norm_w, a.rms_eps, residual=res)
+        cport.qmatmul(cport.silu_mul(cport.qmatmul(x, *self.wgu, g, b)), *self.wdn, g, b)
+        return time.perf_counter() - t0
+
+    def head(self) -> float:
+        """lm_head + argmax on 1/8 of the vocab rows, scaled to the full vocab."""
+        a = self.a
+        rows = a.vocab // 8
+        whead = self.qw(rows, a.hidden)
+        t0 = time.perf_counter()
+        logits = self.cport.qmatmul(self.h, *whead, a.group_size, a.bits)
+        self.cport.argmax(logits)
+        return (time.perf_counter() - t0) * (a.vocab / rows)
+
+
+def run_reference(args) -> None:
+    """--impl reference: the path's CPU restatement on the host cores, rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cs = CpuSample()
+    a = cs.a
+    for _ in range(args.warmup):
+        cs.layer()
+    t_head = cs.head()
+    # each "step" = a bounded sample of one decode step: 1 of 32 layers
+    times = [cs.layer() for _ in range(args.steps)]
+    t_layer = sum(times) / len(times)
+    step_s = a.num_layers * t_layer + t_head
+    val = BATCH / step_s
+    sample = (f"each step times 1 of {a.num_layers} layers (attention over 64x{CTX}-token bf16 KV + qkv/o/gate_up/down "
+              f"int4 g64 linears at M=64) with the oracle C port; step = {a.num_layers} x layer + lm_head "
+              f"(timed once on 1/8 of the vocab rows, x8)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "tok/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "reference native code is Apple/Metal-only (unbuildable here); "
+                   "this arm is the CPU restatement of the same path (oracle C port, OpenMP)"},
+        "cpu_baseline": {"value": val, "unit": "tok/s", "cores": cs.threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ------------------------------------------------------------------------ GPU arm ---
+
+def run_b200(args) -> None:
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
+    from vllm_metal_b200.lm.decoder import PRESETS, Model
+    from vllm_metal_b200.metal import get_ops
+    from vllm_metal_b200.v1.model_runner import PagedModelRunner
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus or world == 1, f"WORLD_SIZE={world} but --gpus {args.gpus}"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    ops = get_ops()
+    a = PRESETS[MODEL]
+
+    def allreduce(x):
+        dist.all_reduce(x)
+
+    model = Model(a, torch.bfloat16, dev, seed=0, rank=rank, world=world, allreduce=allreduce)
+    total = args.warmup + args.steps
+    max_len = CTX + 2 * total + 8
+    blocks_per_seq = (max_len + BLOCK - 1) // BLOCK
+    nb = 1 + BATCH * blocks_per_seq
+    cache = B200PagedKVCache(a.num_layers, a.n_kv_heads // world, a.head_dim, nb, BLOCK, torch.bfloat16, dev)
+    g = torch.Generator(device=dev).manual_seed(3 + rank)
+    for t in (cache._k_all, cache._v_all):
+        for i in range(a.num_layers):
+            t[i].normal_(0.0, 1.0, generator=g)
+    runner = PagedModelRunner(model, cache, max_batch=BATCH, max_model_len=blocks_per_seq * BLOCK,
+                              use_cuda_graph=True)
+    rng = np.random.default_rng(2)
+    tables = (rng.permutation(nb - 1) + 1).astype(np.int32).reshape(BATCH, blocks_per_seq)
+    tokens = rng.integers(0, a.vocab, BATCH).tolist()
+    seq_lens = [CTX] * BATCH
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- e2e through the public runner API (host inputs every step) ----------
+    for _ in range(args.warmup):
+        tokens = runner.decode_step(tokens, tables, seq_lens)
+        seq_lens = [n + 1 for n in seq_lens]
+    h2d0, d2h0 = runner.h2d_bytes, runner.d2h_bytes
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        tokens = runner.decode_step(tokens, tables, seq_lens)
+        seq_lens = [n + 1 for n in seq_lens]
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    h2d = (runner.h2d_bytes - h2d0) // args.steps
+    d2h = (runner.d2h_bytes - d2h0) // args.steps
+
+    # ---------------- device-resident loop: graph replay + on-device feedback --------------
+    max_len_now = runner.fill_decode(tokens, tables, seq_lens)
+    runner.buf.upload()
+    bucket_len = max_len_now + total  # same split-KV bucket for the whole run
+    for _ in range(args.warmup):
+        runner.run_decode(BATCH, bucket_len, advance=True)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    e0.record()
+    for _ in range(args.steps):
+        runner.run_decode(BATCH, bucket_len, advance=True)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    dev_ms = e0.elapsed_time(e1)
+    per_step_launches = runner.launches_per_graph.get((BATCH, runner._bucket(bucket_len), True), 0)
+
+    # ---------------- dominant kernel: paged decode attention, all layers' caches ----------
+    hq, hkv, d = a.n_heads // world, a.n_kv_heads // world, a.head_dim
+    meta = runner._meta(BATCH, runner._bucket(bucket_len))
+    q = torch.randn((BATCH, hq, d), device=dev, generator=g).bfloat16()
+    out = torch.empty_like(q)
+    cur_len = int(runner.buf.view("seq_lens")[:BATCH].max().item())
+
+    def attn_all_layers():
+        for i in range(a.num_layers):
+            ops.paged_attention_primitive(q, cache.key_caches[i], cache.value_caches[i], hkv, d ** -0.5, 0.0,
+                                          meta.block_tables, meta.seq_lens, meta.cu_seqlens_q, BLOCK,
+                                          meta.max_seq_len, -1, out)
+
+    for _ in range(3):
+        attn_all_layers()
+    barrier()
+    e0.record()
+    reps = max(3, min(args.steps, 10))
+    for _ in range(reps):
+        attn_all_layers()
+    e1.record()
+    barrier()
+    attn_ms = e0.elapsed_time(e1) / (reps * a.num_layers)
+    alg_bytes = BATCH * (2 * cur_len * hkv * d * 2 + 2 * hq * d * 2 + ((cur_len + BLOCK - 1) // BLOCK) * 4)
+    peak, peak_src = _peaks()
+    achieved = alg_bytes / (attn_ms * 1e-3) / 1e9
+
+    # ---------------- secondary: int4 GEMV (gate_up) ----------------------------------------
+    mlp = model.layers[0].mlp
+    x = torch.randn((BATCH, a.hidden), device=dev, generator=g).bfloat16()
+    for _ in range(3):
+        for layer in model.layers:
+            layer.mlp.gate_up_proj(x)
+    barrier()
+    e0.record()
+    for _ in range(reps):
+        for layer in model.layers:
+            layer.mlp.gate_up_proj(x)
+    e1.record()
+    barrier()
+    gemv_ms = e0.elapsed_time(e1) / (reps * a.num_layers)
+    n_gu, k_gu = mlp.gate_up_proj.out_features, mlp.gate_up_proj.in_features
+    gemv_bytes = n_gu * k_gu * (a.bits / 8 + 4 / a.group_size) + BATCH * (k_gu + n_gu) * 2
+    gemv_gbs = gemv_bytes / (gemv_ms * 1e-3) / 1e9
+
+    # max over ranks
+    times = torch.tensor([dev_ms, e2e_ms, attn_ms, gemv_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms, attn_ms, gemv_ms = times.tolist()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        layers = 6
+        cs = CpuSample()
+        cs.layer()
+        t_layer = sum(cs.layer() for _ in range(layers)) / layers
+        t_head, threads = cs.head(), cs.threads
+        step_s = a.num_layers * t_layer + t_head
+        cpu = {"value": BATCH / step_s, "unit": "tok/s", "cores": threads, "kind": "port",
+               "sample": f"{layers} of {a.num_layers} decode layers (bs=64, ctx 4096: int4 g64 linears + paged "
+                         f"attention over bf16 KV) and the lm_head on 1/8 of the vocab, timed with the oracle C "
+                         f"port (gcc -O3 -fopenmp), scaled to {a.num_layers} layers + full vocab"}
+
+    if rank == 0:
+        tok_s = BATCH * args.steps / (dev_ms * 1e-3)
+        line = {
+            "metric": METRIC, "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": BATCH, "ctx": CTX, "block_size": BLOCK,
+                       "parallelism": f"tp{world}", "kv_cache": "bf16",
+                       "l2_policy": "inputs larger than L2: each step streams the per-rank KV pool "
+                                    f"({cache.nbytes / 2**30:.1f} GiB) + {model.weight_bytes() / 2**30:.2f} GiB weights"},
+            "e2e": {"value": BATCH * args.steps / (e2e_ms * 1e-3), "unit": "tok/s",
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(per_step_launches * args.steps),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "paged_decode_mma_kernel (+ split_reduce_kernel)",
+                         "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                         "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0,
+                         "traffic": None, "bytes_per_launch": alg_bytes, "us_per_launch": attn_ms * 1e3},
+            "roofline_qgemv": {"bound": "hbm", "kernel": "qgemm_mma_kernel (gate_up 28672x4096 int4 g64, M=64)",
+                               "achieved": gemv_gbs, "peak": peak, "unit": "GB/s", "frac": gemv_gbs / peak,
+                               "bytes_per_launch": gemv_bytes, "us_per_launch": gemv_ms * 1e3},
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

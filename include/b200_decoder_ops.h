@@ -47,6 +47,17 @@ int b200_argmax(const void* logits, int32_t* out, int rows, int vocab,
 int b200_add_inplace(void* y, const void* x, int rows, int dim, int64_t y_stride,
                      int64_t x_stride, int dtype, void* stream);
 
+/* Device-side step bookkeeping for back-to-back decode steps (the host-side
+ * equivalent is the reference's per-step packing, v1/model_runner.py:1200-1240 +
+ * attention/context.py:219-223): for every request r in [0, batch):
+ *   input_ids[r] = sampled[r]; positions[r] += 1; seq_lens[r] += 1;
+ *   slot_mapping[r] = block_tables[r, pos / block_size] * block_size + pos % block_size
+ * with pos the new position.  block_tables is int32 [batch, max_blocks]. */
+int b200_advance_decode(int32_t* input_ids, int32_t* positions, int32_t* seq_lens,
+                        int64_t* slot_mapping, const int32_t* block_tables,
+                        const int32_t* sampled, int batch, int max_blocks, int block_size,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -145,7 +145,37 @@ add_inplace_kernel(T* __restrict__ y, const T* __restrict__ x, int dim, int64_t 
     yr[i] = from_float<T>(to_float(yr[i]) + to_float(xr[i]));
 }
 
+__global__ void advance_decode_kernel(int32_t* __restrict__ input_ids, int32_t* __restrict__ positions,
+                                      int32_t* __restrict__ seq_lens, int64_t* __restrict__ slot_mapping,
+                                      const int32_t* __restrict__ block_tables,
+                                      const int32_t* __restrict__ sampled, int batch, int max_blocks,
+                                      int block_size) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= batch) return;
+  const int pos = positions[r] + 1;
+  positions[r] = pos;
+  seq_lens[r] += 1;
+  input_ids[r] = sampled[r];
+  int page = pos / block_size;
+  if (page >= max_blocks) page = max_blocks - 1;
+  slot_mapping[r] = (int64_t)block_tables[(int64_t)r * max_blocks + page] * block_size + pos % block_size;
+}
+
 }  // namespace b200
+
+extern "C" int b200_advance_decode(int32_t* input_ids, int32_t* positions, int32_t* seq_lens,
+                                   int64_t* slot_mapping, const int32_t* block_tables,
+                                   const int32_t* sampled, int batch, int max_blocks, int block_size,
+                                   void* stream) {
+  using namespace b200;
+  if (batch == 0) return B200_OK;
+  B200_CHECK_ARG(batch > 0 && max_blocks > 0 && block_size > 0 && input_ids && positions && seq_lens &&
+                     slot_mapping && block_tables && sampled,
+                 "advance_decode: bad arguments");
+  advance_decode_kernel<<<(batch + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      input_ids, positions, seq_lens, slot_mapping, block_tables, sampled, batch, max_blocks, block_size);
+  return check_launch("advance_decode_kernel");
+}
 
 extern "C" int b200_rms_norm(const void* x, void* residual, const void* weight, void* out,
                              int rows, int dim, int64_t x_stride, int64_t res_stride,

@@ -97,6 +97,7 @@ EXPORTED_SYMBOLS = (
     "b200_silu_mul",
     "b200_argmax",
     "b200_add_inplace",
+    "b200_advance_decode",
 )
 
 
@@ -142,6 +143,7 @@ def load_library() -> ctypes.CDLL:
     lib.b200_silu_mul.argtypes = [vp, vp, i32, i32, i64, i64, i32, vp]
     lib.b200_argmax.argtypes = [vp, vp, i32, i32, i64, i32, vp]
     lib.b200_add_inplace.argtypes = [vp, vp, i32, i32, i64, i64, i32, vp]
+    lib.b200_advance_decode.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp]
     if lib.b200_partition_size() != PARTITION_SIZE:
         raise RuntimeError("PARTITION_SIZE mismatch between constants.py and the library")
     return lib
@@ -500,6 +502,22 @@ class _Ops:
         self._check(rc)
         self.launches += 1
         return y
+
+
+def _advance_decode(self, input_ids, positions, seq_lens, slot_mapping, block_tables, sampled, block_size):
+    """Feed sampled tokens back and move every decode request one slot on (device side)."""
+    _require_cuda("input_ids", input_ids)
+    if block_tables.stride(1) != 1:
+        raise ValueError("block_tables rows must be contiguous")
+    rc = self._lib.b200_advance_decode(
+        input_ids.data_ptr(), positions.data_ptr(), seq_lens.data_ptr(), slot_mapping.data_ptr(),
+        block_tables.data_ptr(), sampled.data_ptr(), input_ids.shape[0], block_tables.stride(0),
+        int(block_size), _stream())
+    self._check(rc)
+    self.launches += 1
+
+
+_Ops.advance_decode = _advance_decode
 
 
 def get_ops() -> _Ops:

@@ -85,7 +85,9 @@ class PagedModelRunner:
         self.max_blocks = (max_model_len + self.block_size - 1) // self.block_size
         self.use_cuda_graph = use_cuda_graph
         self.buf = StepBuffers(max_batch, self.max_blocks, self.device)
-        self._graphs: dict[tuple[int, int], torch.cuda.CUDAGraph] = {}
+        self._graphs: dict[tuple[int, int, bool], torch.cuda.CUDAGraph] = {}
+        # kernels of ours inside each captured graph (bench.py's gpu_launches)
+        self.launches_per_graph: dict[tuple[int, int, bool], int] = {}
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
@@ -121,10 +123,12 @@ class PagedModelRunner:
             positions=b.view("positions")[:batch],
         )
 
-    def _forward_decode(self, batch: int, max_seq_len: int) -> None:
+    def _forward_decode(self, batch: int, max_seq_len: int, advance: bool = False) -> None:
         meta = self._meta(batch, max_seq_len)
         logits = self.model(self.buf.view("input_ids")[:batch], None, self.kv_cache, meta=meta)
         get_ops().argmax(logits, out=self.buf.out_tokens[:batch])
+        if advance:
+            self.advance_on_device(batch)
 
     def _bucket(self, max_seq_len: int) -> int:
         """Graphs are keyed by the split-KV bucket: max_seq_len rounded up to a
@@ -138,8 +142,11 @@ class PagedModelRunner:
         b, n = self.buf, len(token_ids)
         pos = np.asarray(seq_lens, dtype=np.int64)
         tables = b.np_view("block_tables")
-        for i, ids in enumerate(block_ids):
-            tables[i, : len(ids)] = ids
+        if isinstance(block_ids, np.ndarray):
+            tables[:n, : block_ids.shape[1]] = block_ids
+        else:
+            for i, ids in enumerate(block_ids):
+                tables[i, : len(ids)] = ids
         blk = tables[np.arange(n), pos // self.block_size].astype(np.int64)
         b.np_view("slot_mapping")[:n] = blk * self.block_size + pos % self.block_size
         b.np_view("input_ids")[:n] = np.asarray(token_ids, dtype=np.int32)
@@ -162,38 +169,44 @@ class PagedModelRunner:
             return self.buf.out_host[:n].tolist()
         return None
 
-    def run_decode(self, batch: int, max_seq_len: int) -> None:
-        """Forward + argmax over the persistent buffers (graph replay when enabled)."""
+    def run_decode(self, batch: int, max_seq_len: int, *, advance: bool = False) -> None:
+        """Forward + argmax over the persistent buffers (graph replay when enabled).
+        ``advance=True`` appends the device-side bookkeeping kernel so steps can be
+        replayed back to back with no host in the loop."""
         if not self.use_cuda_graph:
-            self._forward_decode(batch, max_seq_len)
+            self._forward_decode(batch, max_seq_len, advance)
             return
-        key = (batch, self._bucket(max_seq_len))
+        key = (batch, self._bucket(max_seq_len), advance)
         g = self._graphs.get(key)
         if g is None:
+            if advance:
+                snap = self.buf.dev.clone()
             # warm up on a side stream (lazy module load, workspace growth), then capture
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(s):
-                self._forward_decode(batch, key[1])
+                self._forward_decode(batch, key[1], advance)
             torch.cuda.current_stream().wait_stream(s)
             torch.cuda.synchronize()
+            if advance:
+                self.buf.dev.copy_(snap)  # the warm-up run moved the requests one slot on
+            ops = get_ops()
+            n0 = ops.launches
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self._forward_decode(batch, key[1])
+                self._forward_decode(batch, key[1], advance)
+            self.launches_per_graph[key] = ops.launches - n0
             self._graphs[key] = g
         g.replay()
 
     def advance_on_device(self, batch: int) -> None:
         """Device-side bookkeeping for back-to-back decode steps with no host in
-        the loop: feed the sampled tokens back and move every request one slot on."""
+        the loop: feed the sampled tokens back and move every request one slot on
+        (one kernel; the reference does this on the host, model_runner.py:1200-1240)."""
         b = self.buf
-        pos = b.view("positions")[:batch]
-        pos.add_(1)
-        b.view("seq_lens")[:batch].add_(1)
-        b.view("input_ids")[:batch].copy_(b.out_tokens[:batch])
-        p64 = pos.to(torch.int64)
-        blk = b.view("block_tables")[:batch].gather(1, (p64 // self.block_size).unsqueeze(1)).squeeze(1)
-        b.view("slot_mapping")[:batch].copy_(blk.to(torch.int64) * self.block_size + p64 % self.block_size)
+        get_ops().advance_decode(b.view("input_ids")[:batch], b.view("positions")[:batch],
+                                 b.view("seq_lens")[:batch], b.view("slot_mapping")[:batch],
+                                 b.view("block_tables")[:batch], b.out_tokens[:batch], self.block_size)
 
 
 __all__ = ["PagedModelRunner", "StepBuffers", "_kernel_metadata"]
