@@ -276,6 +276,13 @@ def run_b200(args) -> None:
     barrier()
     clocks = sampler.stop()
     dev_ms = e0.elapsed_time(e1)
+    if os.environ.get("B200_PROFILE_RANGE"):
+        # one extra, untimed step inside a cudaProfilerStart/Stop range for
+        # `ncu --profile-from-start off` (profiles/: launch list + --set full capture)
+        torch.cuda.profiler.start()
+        runner.run_decode(BATCH, bucket_len, advance=True)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     per_step_launches = runner.launches_per_graph.get((BATCH, runner._bucket(bucket_len), True), 0)
 
     # ---------------- dominant kernel: paged decode attention, all layers' caches ----------
