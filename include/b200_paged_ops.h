@@ -178,6 +178,11 @@ int b200_qlinear(const void* x, const uint32_t* w, const void* scales,
                  int K, int group_size, int bits, int dtype, int sb_dtype,
                  int64_t x_stride, int64_t y_stride, void* stream);
 
+/* Test / tuning knob: which kernel b200_qlinear runs.  0 = auto (tcgen05 + TMEM + TMA kernel
+ * whenever the shape qualifies, else the mma.sync kernel), 1 = always the mma.sync kernel,
+ * 2 = tcgen05 kernel or B200_ERR_UNSUPPORTED.  Process-wide; returns 0 on success. */
+int b200_set_qlinear_kernel(int kernel);
+
 /* out[r, :] = dequantize(row ids[r]) for r in [0, num_rows); ids == NULL means
  * rows 0..num_rows-1 (plain mx.dequantize).  ids are int32 (token ids). */
 int b200_dequantize_rows(const uint32_t* w, const void* scales,

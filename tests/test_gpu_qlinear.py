@@ -46,9 +46,16 @@ def test_dequantize_bit_exact(ops, bits, group, dtype):
     assert np.array_equal(to_np(f32), oq.dequantize(wq, s, b, group, bits, "float32"))
 
 
-@pytest.mark.parametrize("m", [1, 3, 16, 17, 64, 100, 256])
-@pytest.mark.parametrize("bits,group", [(4, 64), (4, 32), (4, 128), (8, 64)])
-def test_quantized_matmul_vs_oracle(ops, m, bits, group):
+@pytest.fixture(params=[1, 2], ids=["mma_sync", "tcgen05"])
+def kernel(request, ops):
+    ops.set_qlinear_kernel(request.param)
+    yield request.param
+    ops.set_qlinear_kernel(0)
+
+
+@pytest.mark.parametrize("m", [1, 3, 16, 17, 64, 100, 256, 300, 513])
+@pytest.mark.parametrize("bits,group", [(4, 64), (4, 32), (4, 128), (8, 64), (8, 32), (8, 128)])
+def test_quantized_matmul_vs_oracle(ops, kernel, m, bits, group):
     n, k = 320, 1024
     wq, s, b, tw, ts, tb = _quantized(n, k, bits, group, seed=m)
     rng = np.random.default_rng(m + 1)
@@ -61,13 +68,48 @@ def test_quantized_matmul_vs_oracle(ops, m, bits, group):
 
 
 @pytest.mark.parametrize("n,k", [(4096, 4096), (1024, 4096), (6144, 4096), (4096, 14336), (2880, 2880), (136, 192)])
-def test_quantized_matmul_model_shapes(ops, n, k):
+def test_quantized_matmul_model_shapes(ops, kernel, n, k):
     """Llama-8B projections (q/o, k/v, fused qkv, down) and gpt-oss K=2880=45*64."""
     wq, s, b, tw, ts, tb = _quantized(n, k, 4, 64, seed=n % 97)
     x = round_to(np.random.default_rng(5).standard_normal((64, k)).astype(np.float32), "bfloat16")
     got = ops.quantized_matmul(torch.from_numpy(x).bfloat16().cuda(), tw, ts, tb, group_size=64, bits=4)
     want = oq.quantized_matmul(x, wq, s, b, 64, 4, dtype="bfloat16")
     assert_close(got, want, "bfloat16", f"{n}x{k}")
+
+
+@pytest.mark.parametrize("m", [1, 8, 16, 33, 64])
+@pytest.mark.parametrize("n,k,bits,group", [(256, 4096, 4, 64), (128, 2880, 4, 32), (512, 8192, 8, 128),
+                                           (1000, 2048, 4, 128), (384, 1536, 8, 64)])
+def test_tcgen05_cluster_split_k(ops, m, n, k, bits, group):
+    """Few row tiles -> K is split over a thread-block cluster and reduced through DSMEM;
+    includes K with a ragged last packed stage (2880 = 11.25 x 256) and a dense bias."""
+    ops.set_qlinear_kernel(2)
+    try:
+        wq, s, b, tw, ts, tb = _quantized(n, k, bits, group, seed=n + m)
+        x = round_to(np.random.default_rng(m).standard_normal((m, k)).astype(np.float32), "bfloat16")
+        bias = round_to(np.random.default_rng(7).standard_normal(n).astype(np.float32), "bfloat16")
+        got = ops.quantized_matmul(torch.from_numpy(x).bfloat16().cuda(), tw, ts, tb, group_size=group, bits=bits,
+                                   bias=torch.from_numpy(bias).bfloat16().cuda())
+        want = oq.quantized_matmul(x, wq, s, b, group, bits, bias=bias, dtype="bfloat16")
+        assert_close(got, want, "bfloat16", f"M={m} {n}x{k}")
+    finally:
+        ops.set_qlinear_kernel(0)
+
+
+def test_tcgen05_strided_rows(ops):
+    """x and y as column slices of wider buffers (row strides != K, N)."""
+    ops.set_qlinear_kernel(2)
+    try:
+        wq, s, b, tw, ts, tb = _quantized(192, 512, 4, 64, seed=9)
+        xw = torch.randn((20, 1024), device="cuda").bfloat16()
+        x = xw[:, 256:768]
+        yw = torch.zeros((20, 400), dtype=torch.bfloat16, device="cuda")
+        ops.quantized_matmul(x, tw, ts, tb, group_size=64, bits=4, out=yw[:, 8:200])
+        want = oq.quantized_matmul(to_np(x), wq, s, b, 64, 4, dtype="bfloat16")
+        assert_close(yw[:, 8:200], want, "bfloat16", "strided")
+        assert (yw[:, :8] == 0).all() and (yw[:, 200:] == 0).all()
+    finally:
+        ops.set_qlinear_kernel(0)
 
 
 def test_quantized_matmul_bias_fp16_and_leading_dims(ops):

@@ -1,0 +1,703 @@
+// Affine group-quantized GEMM on the 5th-gen tensor cores (tcgen05 + TMEM + TMA).
+//
+//   y[m,n] = sum_k x[m,k] * (scales[n,k/g] * q[n,k] + biases[n,k/g]) (+ bias[n])
+//
+// Replaces mx.quantized_matmul(x, w, scales, biases, transpose=True, ...) as the reference
+// calls it (vllm_metal/gguf/mlx_native.py:212-222; nn.QuantizedLinear from
+// attention/impls/sdpa.py:297-343,739) for every batch size: decode (M <= 64) is
+// weight-streaming / HBM-bound, prefill (M >= 256) is tensor-bound.
+//
+// One CTA owns 128 output features (UMMA M = 128 = weight rows) and a batch tile of NB rows
+// of x (UMMA N = NB in {16..256}); the fp32 accumulator [128 x NB] lives in TMEM.
+//
+//   warp 4 (1 thread)  TMA: packed uint32 weight tiles [128 rows x 128 B] -> smem ring (PS deep)
+//   warp 5 (1 thread)  TMA: x tiles [NB x 64] bf16, 128B-swizzled K-major  -> B ring (NS deep)
+//   warps 0-3          one thread per weight row: unpack 64 int4/int8 -> s*q+b (bf16x2 HFMA2, single
+//                      rounding) -> A ring in the canonical K-major SWIZZLE_128B layout
+//   warp 6 (1 thread)  tcgen05.mma.cta_group::1.kind::f16 128xNBx16, 4 per 64-wide k block;
+//                      tcgen05.commit frees the A/B stage and finally signals the epilogue
+//   warps 0-3          epilogue: tcgen05.ld -> (+bias) -> y
+//
+// Matrices with few row tiles (o_proj, down_proj: N = hidden) are split along K over a thread
+// block CLUSTER (1 x ksplit x 1); partial accumulators are exchanged through distributed
+// shared memory and reduced in-cluster, so the op stays a single launch with no workspace.
+//
+// Algorithmic bytes: N*K*(bits/8 + 2*sizeof(sb)/g) + (M*K + M*N)*2.
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace b200 {
+namespace qtc {
+
+constexpr int ROWS = 128;  // weight rows per CTA (UMMA M)
+constexpr int KB = 64;     // k elements per A/B stage (128 bytes of 16-bit)
+constexpr int A_STAGE_BYTES = ROWS * 128;
+constexpr int P_STAGE_BYTES = ROWS * 128;
+constexpr int NUM_THREADS = 7 * 32;
+
+// ---------------------------------------------------------------- PTX helpers ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 26)) __trap();  // a protocol bug must fault, not hang the box
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// K-major SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor):
+// start>>4 [0,14) | LBO>>4 [16,30) (unused for swizzled K-major, 1) | SBO>>4 [32,46) = 1024 B
+// between 8-row groups | version=1 [46,48) | layout_type=2 (SWIZZLE_128B) [61,64).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr) {
+  uint64_t d = (uint64_t)((addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 = 1 @4, a/b format
+// (0 = F16, 1 = BF16) @7/@10, K-major A and B (0) @15/@16, N>>3 @17, M>>4 @24.
+__host__ __device__ constexpr uint32_t make_idesc(int fmt, int M, int N) {
+  return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------- dequant traits ----
+template <typename T>
+struct Cvt;
+template <>
+struct Cvt<__nv_bfloat16> {
+  using T2 = __nv_bfloat162;
+  static constexpr int kFmt = 1;
+  static constexpr uint32_t kMagic = 0x43004300u;  // bf16 128.0: 128 + q exact for q < 128
+  __device__ static __forceinline__ T2 magic_off() { return __float2bfloat162_rn(-128.f); }
+  __device__ static __forceinline__ T2 bcast(uint16_t raw) {
+    __nv_bfloat16_raw r;
+    r.x = raw;
+    return __bfloat162bfloat162(__nv_bfloat16(r));
+  }
+  __device__ static __forceinline__ uint32_t f2(float lo, float hi) {
+    T2 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
+  __device__ static __forceinline__ float to_f(uint16_t raw) {
+    return __uint_as_float((uint32_t)raw << 16);
+  }
+};
+template <>
+struct Cvt<__half> {
+  using T2 = __half2;
+  static constexpr int kFmt = 0;
+  static constexpr uint32_t kMagic = 0x64006400u;  // fp16 1024.0: 1024 + q exact
+  __device__ static __forceinline__ T2 magic_off() { return __float2half2_rn(-1024.f); }
+  __device__ static __forceinline__ T2 bcast(uint16_t raw) {
+    __half_raw r;
+    r.x = raw;
+    return __half2half2(__half(r));
+  }
+  __device__ static __forceinline__ uint32_t f2(float lo, float hi) {
+    T2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
+  __device__ static __forceinline__ float to_f(uint16_t raw) {
+    __half_raw r;
+    r.x = raw;
+    return __half2float(__half(r));
+  }
+};
+
+// 8 nibbles of one packed word -> 8 values s*q+b in memory order (k0..k7), as 4 packed pairs.
+template <typename T>
+__device__ __forceinline__ uint4 dequant_word4(uint32_t w, typename Cvt<T>::T2 s2,
+                                               typename Cvt<T>::T2 b2) {
+  using C = Cvt<T>;
+  using T2 = typename C::T2;
+  uint32_t a[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    // (k_i, k_{i+4}) as the low/high halves: lop3 (and, or) on the shifted word
+    uint32_t v = ((w >> (4 * i)) & 0x000F000Fu) | C::kMagic;
+    T2 q = __hadd2(*reinterpret_cast<T2*>(&v), C::magic_off());  // exact: q in [0, 15]
+    T2 r = __hfma2(s2, q, b2);                                    // s*q+b, one rounding
+    a[i] = *reinterpret_cast<uint32_t*>(&r);
+  }
+  uint4 o;
+  o.x = __byte_perm(a[0], a[1], 0x5410);  // (k0, k1)
+  o.y = __byte_perm(a[2], a[3], 0x5410);  // (k2, k3)
+  o.z = __byte_perm(a[0], a[1], 0x7632);  // (k4, k5)
+  o.w = __byte_perm(a[2], a[3], 0x7632);  // (k6, k7)
+  return o;
+}
+// 4 bytes of one packed word -> 4 values (fp32 fma, then one rounding to T).
+template <typename T>
+__device__ __forceinline__ uint2 dequant_word8(uint32_t w, float s, float b) {
+  using C = Cvt<T>;
+  uint2 o;
+  o.x = C::f2(fmaf(s, (float)(w & 0xFFu), b), fmaf(s, (float)((w >> 8) & 0xFFu), b));
+  o.y = C::f2(fmaf(s, (float)((w >> 16) & 0xFFu), b), fmaf(s, (float)(w >> 24), b));
+  return o;
+}
+
+struct Params {
+  const uint16_t* scales;
+  const uint16_t* biases;
+  const void* bias;  // dense [N] of T or null
+  void* y;
+  int M, N, K, group_size;
+  int64_t y_stride;
+  int num_kb;        // K / 64
+  int kb_per_split;  // k blocks per cluster rank
+};
+
+template <int NB, int PS, int NS>
+constexpr int smem_bytes() {
+  return 1024 /*align slack*/ + PS * P_STAGE_BYTES + NS * (A_STAGE_BYTES + NB * 128) + 256;
+}
+
+__device__ __forceinline__ float4 ld_dsmem_v4(uint32_t local_addr, uint32_t peer) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(peer));
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(remote)
+               : "memory");
+  return v;
+}
+
+// TMEM -> registers: CW consecutive fp32 columns of this thread's lane.
+template <int CW>
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[CW]) {
+  if constexpr (CW == 32) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,"
+        "%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+          "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+          "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]),
+          "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]),
+          "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+  } else {
+    static_assert(CW == 16, "CW must be 16 or 32");
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+          "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+          "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
+  }
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// T: activation / scale type; BITS: 4|8; G: quantisation group; NB: batch tile (UMMA N);
+// PS/NS: ring depths.
+template <typename T, int BITS, int G, int NB, int PS, int NS>
+__global__ void __launch_bounds__(NUM_THREADS)
+qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
+                const Params p) {
+  using C = Cvt<T>;
+  using T2 = typename C::T2;
+  constexpr int KPP = 1024 / BITS;        // k per packed stage (128 B per row): 256 | 128
+  constexpr int KB_PER_P = KPP / KB;      // 4 | 2
+  constexpr int CH_PER_KB = KB * BITS / 128;  // 16-byte packed chunks per k block: 2 | 4
+  constexpr int B_STAGE_BYTES = NB * 128;
+  constexpr int TMEM_COLS = NB < 32 ? 32 : NB;
+  constexpr int GPP = KPP / G;  // groups per packed stage (>= 1)
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sm_p = base;
+  const uint32_t sm_a = sm_p + PS * P_STAGE_BYTES;
+  const uint32_t sm_b = sm_a + NS * A_STAGE_BYTES;
+  const uint32_t sm_bar = sm_b + NS * B_STAGE_BYTES;
+  // barriers (8 B each): full_p[PS], empty_p[PS], full_ab[NS], empty_ab[NS], tmem_full; then tmem ptr
+  const uint32_t bar_full_p = sm_bar, bar_empty_p = sm_bar + 8 * PS;
+  const uint32_t bar_full_ab = sm_bar + 16 * PS, bar_empty_ab = bar_full_ab + 8 * NS;
+  const uint32_t bar_tmem_full = bar_empty_ab + 8 * NS;
+  const uint32_t tmem_ptr_addr = bar_tmem_full + 8;
+  uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_ptr_addr - base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * ROWS;
+  const int m0 = blockIdx.z * NB;
+  const int ksplit = gridDim.y;
+  const int krank = ksplit > 1 ? (int)cluster_ctarank() : 0;
+  const int kb_begin = krank * p.kb_per_split;
+  int my_kb = p.num_kb - kb_begin;
+  if (my_kb > p.kb_per_split) my_kb = p.kb_per_split;
+  if (my_kb < 0) my_kb = 0;
+  const int my_ps = (my_kb + KB_PER_P - 1) / KB_PER_P;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < PS; ++i) {
+      mbar_init(bar_full_p + 8 * i, 1);
+      mbar_init(bar_empty_p + 8 * i, 4);
+    }
+    for (int i = 0; i < NS; ++i) {
+      mbar_init(bar_full_ab + 8 * i, 5);  // 4 dequant warps + the x producer's expect_tx arrive
+      mbar_init(bar_empty_ab + 8 * i, 1);
+    }
+    mbar_init(bar_tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 6) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_ptr_addr),
+                 "n"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_gen;
+
+  if (warp == 4) {
+    // ===== packed-weight TMA producer =====
+    if (lane == 0) {
+      for (int ps = 0; ps < my_ps; ++ps) {
+        const int st = ps % PS;
+        mbar_wait(bar_empty_p + 8 * st, ((ps / PS) & 1) ^ 1);
+        mbar_expect_tx(bar_full_p + 8 * st, P_STAGE_BYTES);
+        tma_load_2d(sm_p + st * P_STAGE_BYTES, &w_map, bar_full_p + 8 * st,
+                    (kb_begin + ps * KB_PER_P) * (KB * BITS / 32), n0);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 5) {
+    // ===== x tile TMA producer =====
+    if (lane == 0) {
+      for (int kb = 0; kb < my_kb; ++kb) {
+        const int st = kb % NS;
+        mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
+        mbar_expect_tx(bar_full_ab + 8 * st, B_STAGE_BYTES);
+        tma_load_2d(sm_b + st * B_STAGE_BYTES, &x_map, bar_full_ab + 8 * st, (kb_begin + kb) * KB, m0);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 6) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(C::kFmt, ROWS, NB);
+      for (int kb = 0; kb < my_kb; ++kb) {
+        const int st = kb % NS;
+        mbar_wait(bar_full_ab + 8 * st, (kb / NS) & 1);
+        tc_fence_after();
+        const uint64_t da = make_smem_desc(sm_a + st * A_STAGE_BYTES);
+        const uint64_t db = make_smem_desc(sm_b + st * B_STAGE_BYTES);
+#pragma unroll
+        for (int k = 0; k < KB / 16; ++k)  // +32 B (16 elements) inside the 128 B swizzle row
+          tc_mma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+        tc_commit(bar_empty_ab + 8 * st);
+      }
+      tc_commit(bar_tmem_full);
+    }
+    __syncwarp();
+  } else {
+    // ===== dequant warps: thread r owns weight row n0 + r =====
+    const int r = threadIdx.x;
+    const int n = min(n0 + r, p.N - 1);
+    const int groups_per_row = p.K / G;
+    const uint16_t* srow = p.scales + (int64_t)n * groups_per_row;
+    const uint16_t* brow = p.biases + (int64_t)n * groups_per_row;
+    const uint32_t xr = (uint32_t)(r & 7);
+    uint16_t s_nxt[GPP], b_nxt[GPP];
+    auto load_sb = [&](int ps) {
+      const int g0 = (kb_begin * KB + ps * KPP) / G;  // stage starts are group aligned
+#pragma unroll
+      for (int i = 0; i < GPP; ++i) {
+        const bool ok = g0 + i < groups_per_row;
+        s_nxt[i] = ok ? __ldg(srow + g0 + i) : (uint16_t)0;
+        b_nxt[i] = ok ? __ldg(brow + g0 + i) : (uint16_t)0;
+      }
+    };
+    if (my_ps > 0) load_sb(0);
+    for (int ps = 0; ps < my_ps; ++ps) {
+      const int pst = ps % PS;
+      // this stage's scales/biases, broadcast once; then prefetch the next stage's
+      T2 s2[GPP], b2[GPP];
+      float sf[GPP], bf[GPP];
+#pragma unroll
+      for (int i = 0; i < GPP; ++i) {
+        if constexpr (BITS == 4) {
+          s2[i] = C::bcast(s_nxt[i]);
+          b2[i] = C::bcast(b_nxt[i]);
+        } else {
+          sf[i] = C::to_f(s_nxt[i]);
+          bf[i] = C::to_f(b_nxt[i]);
+        }
+      }
+      (void)s2; (void)b2; (void)sf; (void)bf;
+      if (ps + 1 < my_ps) load_sb(ps + 1);
+      mbar_wait(bar_full_p + 8 * pst, (ps / PS) & 1);
+      const uint32_t prow = sm_p + pst * P_STAGE_BYTES + r * 128;
+#pragma unroll
+      for (int j = 0; j < KB_PER_P; ++j) {
+        const int kb = ps * KB_PER_P + j;
+        if (kb < my_kb) {
+          const int st = kb % NS;
+          mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
+          const uint32_t arow = sm_a + st * A_STAGE_BYTES + r * 128;
+#pragma unroll
+          for (int c = 0; c < CH_PER_KB; ++c) {
+            uint4 pk;
+            const uint32_t src = prow + ((((uint32_t)(j * CH_PER_KB + c)) ^ xr) << 4);
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(pk.x), "=r"(pk.y), "=r"(pk.z), "=r"(pk.w)
+                         : "r"(src));
+            if constexpr (BITS == 4) {  // chunk = 4 words x 8 nibbles = 32 k
+              const uint32_t words[4] = {pk.x, pk.y, pk.z, pk.w};
+#pragma unroll
+              for (int wi = 0; wi < 4; ++wi) {
+                constexpr int dummy = 0;
+                (void)dummy;
+                const int gi = (j * KB + c * 32 + wi * 8) / G;  // compile-time after unrolling
+                const uint4 o = dequant_word4<T>(words[wi], s2[gi], b2[gi]);
+                const uint32_t chunk = (uint32_t)(c * 4 + wi);  // 8 elements = 16 B of the A row
+                asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + ((chunk ^ xr) << 4)),
+                             "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w)
+                             : "memory");
+              }
+            } else {  // chunk = 4 words x 4 bytes = 16 k
+              const int gi = (j * KB + c * 16) / G;
+              const float s = sf[gi], b = bf[gi];
+              const uint2 lo0 = dequant_word8<T>(pk.x, s, b), lo1 = dequant_word8<T>(pk.y, s, b);
+              const uint2 hi0 = dequant_word8<T>(pk.z, s, b), hi1 = dequant_word8<T>(pk.w, s, b);
+              const uint32_t chunk = (uint32_t)(c * 2);
+              asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + ((chunk ^ xr) << 4)),
+                           "r"(lo0.x), "r"(lo0.y), "r"(lo1.x), "r"(lo1.y)
+                           : "memory");
+              asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + (((chunk + 1) ^ xr) << 4)),
+                           "r"(hi0.x), "r"(hi0.y), "r"(hi1.x), "r"(hi1.y)
+                           : "memory");
+            }
+          }
+          fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_full_ab + 8 * st);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_empty_p + 8 * pst);
+    }
+
+    // ===== epilogue (same 4 warps: thread r <-> TMEM lane r <-> output feature n0 + r) =====
+    if (my_kb > 0) {
+      mbar_wait(bar_tmem_full, 0);
+      tc_fence_after();
+    }
+    const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const int nn = n0 + r;
+    constexpr int CW = NB < 32 ? 16 : 32;  // columns per tcgen05.ld
+    if (ksplit == 1) {
+      T* yp = reinterpret_cast<T*>(p.y);
+      const float bias_v =
+          (p.bias != nullptr && nn < p.N) ? to_float(reinterpret_cast<const T*>(p.bias)[nn]) : 0.f;
+#pragma unroll 1
+      for (int c0 = 0; c0 < NB; c0 += CW) {
+        uint32_t v[CW];
+        if (my_kb > 0) {
+          tmem_ld<CW>(taddr + c0, v);
+        } else {
+#pragma unroll
+          for (int i = 0; i < CW; ++i) v[i] = 0u;
+        }
+        if (nn < p.N) {
+#pragma unroll
+          for (int i = 0; i < CW; ++i) {
+            const int m = m0 + c0 + i;
+            if (m < p.M) yp[(int64_t)m * p.y_stride + nn] = from_float<T>(__uint_as_float(v[i]) + bias_v);
+          }
+        }
+      }
+    } else {
+      // split-K: stage the fp32 partial [NB][128] in our own smem (the A ring is idle now)
+      const uint32_t red = sm_a;
+#pragma unroll 1
+      for (int c0 = 0; c0 < NB; c0 += CW) {
+        uint32_t v[CW];
+        if (my_kb > 0) {
+          tmem_ld<CW>(taddr + c0, v);
+        } else {
+#pragma unroll
+          for (int i = 0; i < CW; ++i) v[i] = 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < CW; ++i)
+          asm volatile("st.shared.u32 [%0], %1;" ::"r"(red + (uint32_t)(((c0 + i) * ROWS + r) * 4)), "r"(v[i])
+                       : "memory");
+      }
+    }
+  }
+
+  if (ksplit > 1) {
+    // every thread of every CTA of the cluster: partials are published ...
+    tc_fence_before();
+    cluster_sync_all();
+    if constexpr (NB <= 64) {
+      if (warp < 4) {
+        // Rank j owns the batch columns c with c % ksplit == j.  Thread t sums 4 consecutive
+        // output features (float4) of column group t / 32 over all peers' partials (DSMEM).
+        constexpr int NV = NB / 4;  // float4 loads per thread = (NB / ksplit / 4 columns) x ksplit peers
+        const int t = threadIdx.x;
+        const int r4 = (t & 31) * 4;
+        const int lk = 31 - __clz(ksplit);  // log2(ksplit)
+        const uint32_t red = sm_a;
+        float4 v[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const int ci = i >> lk, peer = i & (ksplit - 1);
+          const int c = krank + ((ci * 4 + (t >> 5)) << lk);
+          v[i] = ld_dsmem_v4(red + (uint32_t)((c * ROWS + r4) * 4), (uint32_t)peer);
+        }
+#pragma unroll
+        for (int step = 1; step < 8; step *= 2) {
+          if (step < ksplit) {
+#pragma unroll
+            for (int i = 0; i + step < NV; i += 2 * step) {
+              v[i].x += v[i + step].x;
+              v[i].y += v[i + step].y;
+              v[i].z += v[i + step].z;
+              v[i].w += v[i + step].w;
+            }
+          }
+        }
+        T* yp = reinterpret_cast<T*>(p.y);
+        const T* bp = reinterpret_cast<const T*>(p.bias);
+        const int nn = n0 + r4;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          if ((i & (ksplit - 1)) != 0) continue;
+          const int ci = i >> lk;
+          const int m = m0 + krank + ((ci * 4 + (t >> 5)) << lk);
+          if (m >= p.M) continue;
+          const float o[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (nn + e < p.N)
+              yp[(int64_t)m * p.y_stride + nn + e] =
+                  from_float<T>(o[e] + (bp ? to_float(bp[nn + e]) : 0.f));
+        }
+      }
+    }
+    // ... and nobody leaves (freeing its smem) before every peer has finished reading
+    cluster_sync_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 6) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS)
+                 : "memory");
+  }
+}
+
+// ----------------------------------------------------------------- host side ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+static int make_map_2d(CUtensorMap* map, CUtensorMapDataType dt, const void* ptr, uint64_t inner,
+                       uint64_t outer, uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer,
+                       CUtensorMapL2promotion promo) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return set_error(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult rc = fn(map, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS)
+    return set_error(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)rc);
+  return B200_OK;
+}
+
+struct HostArgs {
+  const void* x;
+  const uint32_t* w;
+  const void* scales;
+  const void* biases;
+  const void* bias;
+  void* y;
+  int M, N, K, group_size, bits, dtype;
+  int64_t x_stride, y_stride;
+};
+
+template <typename T, int BITS, int G, int NB, int PS, int NS>
+static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
+  constexpr int smem = smem_bytes<NB, PS, NS>();
+  auto kern = qgemm_tc_kernel<T, BITS, G, NB, PS, NS>;
+  constexpr int KB_PER_P = (1024 / BITS) / KB;
+  static bool configured = false;
+  if (!configured) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  CUtensorMap w_map, x_map;
+  const uint64_t words = (uint64_t)a.K * BITS / 32;
+  int rc = make_map_2d(&w_map, CU_TENSOR_MAP_DATA_TYPE_UINT32, a.w, words, (uint64_t)a.N, words * 4, 32, ROWS,
+                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+  if (rc != B200_OK) return rc;
+  rc = make_map_2d(&x_map, a.dtype == B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                   a.x, (uint64_t)a.K, (uint64_t)a.M, (uint64_t)a.x_stride * 2, KB, NB,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+  if (rc != B200_OK) return rc;
+  Params p;
+  p.scales = reinterpret_cast<const uint16_t*>(a.scales);
+  p.biases = reinterpret_cast<const uint16_t*>(a.biases);
+  p.bias = a.bias;
+  p.y = a.y;
+  p.M = a.M;
+  p.N = a.N;
+  p.K = a.K;
+  p.group_size = a.group_size;
+  p.y_stride = a.y_stride;
+  p.num_kb = a.K / KB;
+  // ranks start on packed-stage (hence group) boundaries
+  p.kb_per_split = ((p.num_kb + ksplit - 1) / ksplit + KB_PER_P - 1) / KB_PER_P * KB_PER_P;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((a.N + ROWS - 1) / ROWS, ksplit, (a.M + NB - 1) / NB);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = ksplit;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, w_map, x_map, p));
+  return B200_OK;
+}
+
+template <typename T, int BITS, int G>
+static int dispatch_g(const HostArgs& a, cudaStream_t st) {
+  const int tiles = (a.N + ROWS - 1) / ROWS;
+  const int num_kb = a.K / KB;
+  if (a.M <= 64) {
+    // Few row tiles: split K over a cluster until ~2 CTAs per SM stream weights.
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    int ksplit = 1;
+    while (ksplit < 8 && tiles * ksplit * 2 <= 2 * sms && num_kb / (ksplit * 2) >= 4) ksplit *= 2;
+    if (a.M <= 16)  // the in-cluster reduce needs >= 4 batch columns per rank
+      return launch_cfg<T, BITS, G, 16, 3, 2>(a, ksplit > 4 ? 4 : ksplit, st);
+    return launch_cfg<T, BITS, G, 64, 3, 2>(a, ksplit, st);
+  }
+  if (a.M <= 128) return launch_cfg<T, BITS, G, 128, 3, 3>(a, 1, st);
+  return launch_cfg<T, BITS, G, 256, 2, 3>(a, 1, st);
+}
+
+template <typename T, int BITS>
+static int dispatch(const HostArgs& a, cudaStream_t st) {
+  switch (a.group_size) {
+    case 32: return dispatch_g<T, BITS, 32>(a, st);
+    case 64: return dispatch_g<T, BITS, 64>(a, st);
+    case 128: return dispatch_g<T, BITS, 128>(a, st);
+    default: return set_error(B200_ERR_INVALID_ARGUMENT, "qgemm_tc: bad group size %d", a.group_size);
+  }
+}
+
+}  // namespace qtc
+
+// Shapes the tensor-core path takes; everything else runs on the mma.sync kernel in qlinear.cu.
+bool qgemm_tc_supported(const void* x, const uint32_t* w, int M, int N, int K, int group_size, int bits,
+                        int dtype, int sb_dtype, int64_t x_stride) {
+  if (dtype != B200_BF16) return false;  // fp16 activations stay on the mma.sync kernel
+  if (sb_dtype != dtype) return false;
+  if (K % 64 != 0 || K % group_size != 0) return false;
+  if ((uintptr_t)x % 16 || (uintptr_t)w % 16 || (x_stride * 2) % 16) return false;
+  if (((int64_t)K * bits / 8) % 16) return false;
+  (void)M;
+  (void)N;
+  return qtc::encode_fn() != nullptr;
+}
+
+int qgemm_tc_launch(const void* x, const uint32_t* w, const void* scales, const void* biases,
+                    const void* bias, void* y, int M, int N, int K, int group_size, int bits, int dtype,
+                    int64_t x_stride, int64_t y_stride, cudaStream_t st) {
+  qtc::HostArgs a{x, w, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride, y_stride};
+  return bits == 4 ? qtc::dispatch<__nv_bfloat16, 4>(a, st) : qtc::dispatch<__nv_bfloat16, 8>(a, st);
+}
+
+}  // namespace b200

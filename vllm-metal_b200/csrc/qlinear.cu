@@ -15,6 +15,15 @@
 
 namespace b200 {
 
+// qgemm_tc.cu: tcgen05 / TMEM / TMA path
+bool qgemm_tc_supported(const void* x, const uint32_t* w, int M, int N, int K, int group_size, int bits,
+                        int dtype, int sb_dtype, int64_t x_stride);
+int qgemm_tc_launch(const void* x, const uint32_t* w, const void* scales, const void* biases,
+                    const void* bias, void* y, int M, int N, int K, int group_size, int bits, int dtype,
+                    int64_t x_stride, int64_t y_stride, cudaStream_t st);
+
+static int g_qlinear_kernel = 0;  // 0 auto, 1 mma.sync kernel, 2 tcgen05 kernel
+
 namespace ql {
 
 constexpr int KT = 64;      // k elements per pipeline step
@@ -350,6 +359,17 @@ extern "C" int b200_qlinear(const void* x, const uint32_t* w, const void* scales
   B200_CHECK_ARG(dtype == B200_BF16 || dtype == B200_F16,
                  "qlinear: activations must be bf16 or fp16 (dtype code %d)", dtype);
   B200_CHECK_ARG(K % ql::KT == 0, "qlinear: K (%d) must be a multiple of %d", K, ql::KT);
+  cudaStream_t st0 = (cudaStream_t)stream;
+  if (g_qlinear_kernel != 1) {
+    const bool ok = y_stride >= N &&
+                    qgemm_tc_supported(x, w, M, N, K, group_size, bits, dtype, sb_dtype, x_stride);
+    if (ok) return qgemm_tc_launch(x, w, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride,
+                                   y_stride, st0);
+    if (g_qlinear_kernel == 2)
+      return set_error(B200_ERR_UNSUPPORTED,
+                       "qlinear: tcgen05 kernel does not take dtype=%d sb_dtype=%d K=%d x_stride=%lld",
+                       dtype, sb_dtype, K, (long long)x_stride);
+  }
   B200_CHECK_ARG(x_stride >= K && x_stride % 8 == 0 && ((uintptr_t)x % 16) == 0,
                  "qlinear: x rows must be 16-byte aligned (stride %lld)", (long long)x_stride);
   B200_CHECK_ARG(((uintptr_t)w % 16) == 0, "qlinear: packed weights must be 16-byte aligned");
@@ -360,6 +380,13 @@ extern "C" int b200_qlinear(const void* x, const uint32_t* w, const void* scales
     return bits == 4 ? ql::dispatch_tile<__nv_bfloat16, 4>(p, st)
                      : ql::dispatch_tile<__nv_bfloat16, 8>(p, st);
   return bits == 4 ? ql::dispatch_tile<__half, 4>(p, st) : ql::dispatch_tile<__half, 8>(p, st);
+}
+
+extern "C" int b200_set_qlinear_kernel(int kernel) {
+  if (kernel < 0 || kernel > 2)
+    return b200::set_error(B200_ERR_INVALID_ARGUMENT, "set_qlinear_kernel: expected 0, 1 or 2, got %d", kernel);
+  b200::g_qlinear_kernel = kernel;
+  return B200_OK;
 }
 
 extern "C" int b200_dequantize_rows(const uint32_t* w, const void* scales, const void* biases,

@@ -91,6 +91,7 @@ EXPORTED_SYMBOLS = (
     "b200_paged_attention_workspace_bytes",
     "b200_paged_attention",
     "b200_qlinear",
+    "b200_set_qlinear_kernel",
     "b200_dequantize_rows",
     "b200_rms_norm",
     "b200_rope",
@@ -414,6 +415,10 @@ class _Ops:
         self._check(rc)
         self.launches += 1
         return out.reshape(*lead, n_out)
+
+    def set_qlinear_kernel(self, kernel: int) -> None:
+        """0 = auto, 1 = mma.sync kernel, 2 = tcgen05 kernel (raises if the shape does not qualify)."""
+        self._check(self._lib.b200_set_qlinear_kernel(int(kernel)))
 
     def dequantize(self, w, scales, biases, group_size: int = 64, bits: int = 4, ids=None,
                    dtype: torch.dtype | None = None):
