@@ -35,6 +35,25 @@ int b200_rope(void* q, void* k, const int32_t* positions, int num_tokens,
               float base, int traditional, int64_t q_stride, int64_t k_stride,
               int dtype, void* stream);
 
+/* Fused per-head RMSNorm -> RoPE -> KV-cache write: the steps between the q/k/v projections
+ * and the attention kernel in the reference's sdpa_forward (attention/impls/sdpa.py:348-368
+ * q/k norm + RoPE, :542-544, :638 reshape_and_cache) as ONE launch.  Bit-identical to
+ * b200_rms_norm (per head, weight q_norm_weight / k_norm_weight [head_dim], NULL = no norm)
+ * followed by b200_rope followed by b200_reshape_and_cache:
+ *   q [T, Hq, D] (row stride q_stride) and k [T, Hk, D] (k_stride) are updated in place,
+ *   the updated k row and the v row [T, Hk, D] (v_stride) are written to
+ *   key_cache / value_cache [num_blocks, block_size, Hk, D] at slot_mapping[t]
+ *   (int64; negative or out-of-range = padding: q/k are still updated, nothing is cached).
+ * rot_dim = 0 disables RoPE (positions may then be NULL). */
+int b200_norm_rope_cache(void* q, void* k, const void* v, const void* q_norm_weight,
+                         const void* k_norm_weight, const int32_t* positions,
+                         const int64_t* slot_mapping, void* key_cache, void* value_cache,
+                         int num_tokens, int num_q_heads, int num_kv_heads, int head_dim,
+                         int rot_dim, float base, int traditional, float eps,
+                         int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                         int block_size, int64_t num_blocks, int64_t kv_block_stride,
+                         int64_t kv_token_stride, int dtype, void* stream);
+
 /* out[r, i] = silu(gate_up[r, i]) * gate_up[r, inter + i], i in [0, inter). */
 int b200_silu_mul(const void* gate_up, void* out, int rows, int inter,
                   int64_t in_stride, int64_t out_stride, int dtype, void* stream);

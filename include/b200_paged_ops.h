@@ -183,6 +183,11 @@ int b200_qlinear(const void* x, const uint32_t* w, const void* scales,
  * 2 = tcgen05 kernel or B200_ERR_UNSUPPORTED.  Process-wide; returns 0 on success. */
 int b200_set_qlinear_kernel(int kernel);
 
+/* Tuning knob of the tcgen05 kernel's weight-streaming (M <= 64) regime, used by the sweep in
+ * profiles/bench_kernels.py: `ksplit` = K split over a thread-block cluster (0 = heuristic, else
+ * 1, 2, 4 or 8), `dequant_warps` = 0 (default), 4 or 8.  Process-wide; returns 0 on success. */
+int b200_set_qlinear_tuning(int ksplit, int dequant_warps);
+
 /* out[r, :] = dequantize(row ids[r]) for r in [0, num_rows); ids == NULL means
  * rows 0..num_rows-1 (plain mx.dequantize).  ids are int32 (token ids). */
 int b200_dequantize_rows(const uint32_t* w, const void* scales,

@@ -1,0 +1,176 @@
+#!/usr/bin/env python
+"""Per-kernel timing of the decode step's pieces at the headline shapes (Llama-3.1-8B, bs=64).
+
+    python profiles/bench_kernels.py [--sweep] [--m 64] [--out gpurun_out/kernels.json]
+
+Every kernel is timed with CUDA events over a rotation of distinct buffers whose total size
+exceeds L2 (126 MB), so each launch streams its operands from HBM.  ``--sweep`` runs the tcgen05
+quantized-GEMM tuning grid (cluster split-K x dequant warps) per shape and checks every
+configuration against the mma.sync kernel.  Numbers printed here are tuning evidence; the
+judged numbers are bench.py's.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from vllm_metal_b200.metal import get_ops  # noqa: E402
+
+PEAK = 6553.0
+try:
+    with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+        PEAK = float(json.load(f)["hbm_gbs"])
+except Exception:  # noqa: BLE001
+    pass
+
+SHAPES = {  # name: (N, K)
+    "qkv": (6144, 4096),
+    "o_proj": (4096, 4096),
+    "gate_up": (28672, 4096),
+    "down": (4096, 14336),
+    "lm_head": (128256, 4096),
+}
+
+
+def time_us(fn, n_rot, reps=5, warm=2):
+    """Mean device time per launch: the rotation is captured in a CUDA graph so host launch
+    overhead (ctypes + argument checks, ~10 us) does not pace the kernels."""
+    for _ in range(warm):
+        for i in range(n_rot):
+            fn(i)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(n_rot):
+            fn(i)
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / (reps * n_rot)
+
+
+def make_qweights(n, k, bits, group, copies, gen):
+    ws = []
+    for _ in range(copies):
+        w = torch.randint(-2**31, 2**31 - 1, (n, k * bits // 32), dtype=torch.int32, device="cuda", generator=gen)
+        s = (torch.rand((n, k // group), device="cuda", generator=gen) * 0.01 + 0.001).bfloat16()
+        b = (-8.0 * s.float() + 0.001 * torch.randn((n, k // group), device="cuda", generator=gen)).bfloat16()
+        ws.append((w, s, b))
+    return ws
+
+
+def qgemm_bytes(m, n, k, bits, group):
+    return n * k * (bits / 8 + 4 / group) + m * (k + n) * 2
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--m", type=int, default=64)
+    ap.add_argument("--bits", type=int, default=4)
+    ap.add_argument("--group", type=int, default=64)
+    ap.add_argument("--shapes", default=",".join(SHAPES))
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    ops = get_ops()
+    gen = torch.Generator(device="cuda").manual_seed(0)
+    m = args.m
+    results = {"peak_gbs": PEAK, "m": m, "qgemm": {}, "ops": {}}
+
+    for name in args.shapes.split(","):
+        n, k = SHAPES[name]
+        per = n * k * args.bits // 8
+        copies = max(2, min(24, (300 << 20) // per + 1))
+        ws = make_qweights(n, k, args.bits, args.group, copies, gen)
+        x = torch.randn((m, k), device="cuda", generator=gen).bfloat16()
+        y = torch.empty((m, n), device="cuda", dtype=torch.bfloat16)
+        nbytes = qgemm_bytes(m, n, k, args.bits, args.group)
+
+        def run(i, ws=ws, x=x, y=y):
+            w, s, b = ws[i]
+            ops.quantized_matmul(x, w, s, b, group_size=args.group, bits=args.bits, out=y)
+
+        ops.set_qlinear_kernel(1)
+        ref = torch.empty_like(y)
+        ops.quantized_matmul(x, *ws[0], group_size=args.group, bits=args.bits, out=ref)
+        t_mma = time_us(run, copies)
+        ops.set_qlinear_kernel(0)
+        rows = {"mma_sync": {"us": t_mma, "gbs": nbytes / t_mma / 1e3}}
+        grid = [(0, 0)]
+        if args.sweep:
+            grid += [(ks, dq) for dq in (4, 8) for ks in (1, 2, 4, 8)]
+        for ks, dq in grid:
+            ops.set_qlinear_tuning(ks, dq)
+            try:
+                out = torch.empty_like(y)
+                ops.quantized_matmul(x, *ws[0], group_size=args.group, bits=args.bits, out=out)
+                torch.cuda.synchronize()
+                err = (out.float() - ref.float()).abs().max().item()
+                scale = ref.float().abs().max().item()
+                t = time_us(run, copies)
+                rows[f"tc_ks{ks}_dq{dq}"] = {"us": t, "gbs": nbytes / t / 1e3, "frac": nbytes / t / 1e3 / PEAK,
+                                             "max_abs_diff_vs_mma": err, "ref_max": scale}
+            except Exception as e:  # noqa: BLE001
+                rows[f"tc_ks{ks}_dq{dq}"] = {"error": str(e)[:200]}
+        ops.set_qlinear_tuning(0, 0)
+        results["qgemm"][name] = {"N": n, "K": k, "bytes": nbytes, "roofline_us": nbytes / PEAK / 1e3, **rows}
+        print(f"== {name} [{n} x {k}] int{args.bits} g{args.group} M={m}: {nbytes / 1e6:.1f} MB, "
+              f"roofline {nbytes / PEAK / 1e3:.1f} us")
+        for kname, r in rows.items():
+            if "error" in r:
+                print(f"   {kname:14s} ERROR {r['error']}")
+            else:
+                extra = f" diff {r['max_abs_diff_vs_mma']:.3g}/{r['ref_max']:.3g}" if "ref_max" in r else ""
+                print(f"   {kname:14s} {r['us']:8.1f} us {r['gbs']:8.0f} GB/s ({r['gbs'] / PEAK * 100:5.1f}%){extra}")
+        del ws
+
+    # ---- the small ops of a decode layer ----
+    hidden, hq, hkv, d, inter = 4096, 32, 8, 128, 14336
+    rot = 16
+    xs = [torch.randn((m, hidden), device="cuda", generator=gen).bfloat16() for _ in range(rot)]
+    rs = [torch.randn((m, hidden), device="cuda", generator=gen).bfloat16() for _ in range(rot)]
+    wn = torch.ones(hidden, device="cuda", dtype=torch.bfloat16)
+    o = torch.empty_like(xs[0])
+    results["ops"]["rms_norm_residual"] = time_us(lambda i: ops.rms_norm(xs[i], wn, 1e-5, residual=rs[i], out=o), rot)
+    gu = [torch.randn((m, 2 * inter), device="cuda", generator=gen).bfloat16() for _ in range(rot)]
+    so = torch.empty((m, inter), device="cuda", dtype=torch.bfloat16)
+    results["ops"]["silu_mul"] = time_us(lambda i: ops.silu_mul(gu[i], out=so), rot)
+    nb, bs = 4096, 16
+    kc = torch.zeros((nb, bs, hkv, d), device="cuda", dtype=torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    qkv = [torch.randn((m, (hq + 2 * hkv) * d), device="cuda", generator=gen).bfloat16() for _ in range(rot)]
+    pos = torch.arange(m, device="cuda", dtype=torch.int32) + 4096
+    slots = (torch.randperm(nb * bs, device="cuda", generator=gen)[:m]).long()
+
+    def fused(i):
+        q, k, v = qkv[i].split([hq * d, hkv * d, hkv * d], dim=-1)
+        ops.norm_rope_cache(q.reshape(m, hq, d), k.reshape(m, hkv, d), v.reshape(m, hkv, d), kc, vc, slots,
+                            positions=pos, rot_dim=d, base=5e5)
+
+    results["ops"]["norm_rope_cache"] = time_us(fused, rot)
+    logits = [torch.randn((m, 128256), device="cuda", generator=gen).bfloat16() for _ in range(8)]
+    tok = torch.empty(m, device="cuda", dtype=torch.int32)
+    results["ops"]["argmax"] = time_us(lambda i: ops.argmax(logits[i], out=tok), 8)
+    for kname, t in results["ops"].items():
+        print(f"   {kname:20s} {t:8.1f} us")
+    if args.out:
+        os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
+        with open(args.out, "w") as f:
+            json.dump(results, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()

@@ -23,6 +23,11 @@ from ..caches.kv_cache import B200PagedKVCache
 from ..context import PagedAttentionContext
 
 
+# Test knob: False runs the reference's step-by-step sequence (norm, rope, reshape_and_cache as
+# separate launches) instead of the fused kernel; both are bit-identical (tests/test_gpu_model.py).
+_FUSE_NORM_ROPE_CACHE = True
+
+
 def _pick_kernel_block_size(cache_block_size: int) -> int:
     """Largest kernel page size dividing the cache block size (sdpa.py:115-124)."""
     for kbs in KERNEL_BLOCK_SIZES:
@@ -160,21 +165,38 @@ def sdpa_forward(
     q = q.reshape(t, n_heads, hd)
     k = k.reshape(t, n_kv_heads, hd)
     v = v.reshape(t, n_kv_heads, hd)
-    if getattr(inner, "q_norm", None) is not None:  # Qwen3 per-head norms (sdpa.py:348-353)
-        q = inner.q_norm(q)
-        k = inner.k_norm(k)
     rope = getattr(inner, "rope", None)
-    if rope is not None:
-        if not q.is_contiguous():
-            q = q.contiguous()
-        if not k.is_contiguous():
-            k = k.contiguous()
-        ops.rope(q, k, meta.positions, rope.dims, rope.base, rope.traditional)
-    if q.dtype != kv_cache.dtype:
-        q, k, v = q.to(kv_cache.dtype), k.to(kv_cache.dtype), v.to(kv_cache.dtype)
-
-    k_cache, v_cache = ops.reshape_and_cache(
-        k, v, kv_cache.key_caches[layer_idx], kv_cache.value_caches[layer_idx], meta.slot_mapping)
+    q_norm, k_norm = getattr(inner, "q_norm", None), getattr(inner, "k_norm", None)
+    k_cache, v_cache = kv_cache.key_caches[layer_idx], kv_cache.value_caches[layer_idx]
+    fused = (
+        _FUSE_NORM_ROPE_CACHE
+        and q.dtype == kv_cache.dtype
+        and all(x.stride(2) == 1 and x.stride(1) == hd for x in (q, k, v))
+        and (q_norm is None) == (k_norm is None)
+        and (q_norm is None or (hasattr(q_norm, "weight") and hasattr(q_norm, "eps")))
+    )
+    if fused:
+        # one launch: per-head norm -> RoPE -> cache write, q/k/v read as strided views of qkv
+        k_cache, v_cache = ops.norm_rope_cache(
+            q, k, v, k_cache, v_cache, meta.slot_mapping, positions=meta.positions,
+            rot_dim=0 if rope is None else rope.dims, base=10000.0 if rope is None else rope.base,
+            traditional=False if rope is None else rope.traditional,
+            q_norm_weight=None if q_norm is None else q_norm.weight,
+            k_norm_weight=None if k_norm is None else k_norm.weight,
+            eps=1e-6 if q_norm is None else q_norm.eps)
+    else:
+        if q_norm is not None:  # Qwen3 per-head norms (sdpa.py:348-353)
+            q = q_norm(q)
+            k = k_norm(k)
+        if rope is not None:
+            if not q.is_contiguous():
+                q = q.contiguous()
+            if not k.is_contiguous():
+                k = k.contiguous()
+            ops.rope(q, k, meta.positions, rope.dims, rope.base, rope.traditional)
+        if q.dtype != kv_cache.dtype:
+            q, k, v = q.to(kv_cache.dtype), k.to(kv_cache.dtype), v.to(kv_cache.dtype)
+        k_cache, v_cache = ops.reshape_and_cache(k, v, k_cache, v_cache, meta.slot_mapping)
     kv_cache.replace_layer_cache(layer_idx, k_cache, v_cache)
 
     if meta.block_size != cache_block_size:  # zero-copy view at the kernel page size
@@ -182,8 +204,7 @@ def sdpa_forward(
         k_cache = k_cache.reshape(-1, meta.block_size, kvh, d)
         v_cache = v_cache.reshape(-1, meta.block_size, kvh, d)
 
-    q = q.contiguous()
-    out = torch.empty_like(q)
+    out = torch.empty((t, n_heads, hd), dtype=q.dtype, device=q.device)
     ops.paged_attention_primitive(
         q, k_cache, v_cache, kv_cache.kv_heads_per_layer[layer_idx], float(scale), 0.0,
         meta.block_tables, meta.seq_lens, meta.cu_seqlens_q, meta.block_size, meta.max_seq_len,

@@ -46,6 +46,70 @@ rms_norm_kernel(const T* __restrict__ x, T* __restrict__ residual, const T* __re
   }
 }
 
+// Vectorised row kernel for 16-bit types: one 16-byte load per thread per pass, the row
+// stays in registers between the sum-of-squares and the scale (one HBM read, one write).
+// Requires dim % 8 == 0, 16-byte aligned rows, dim <= blockDim.x * 8 * NV.
+template <typename T, int NV>
+__global__ void __launch_bounds__(1024)
+rms_norm_vec_kernel(const T* __restrict__ x, T* __restrict__ residual, const T* __restrict__ weight,
+                    T* __restrict__ out, int dim, int64_t x_stride, int64_t res_stride,
+                    int64_t out_stride, float eps) {
+  __shared__ float red[32];
+  const int r = blockIdx.x;
+  const int nvec = dim >> 3;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + (int64_t)r * x_stride);
+  uint4* rr = residual ? reinterpret_cast<uint4*>(residual + (int64_t)r * res_stride) : nullptr;
+  float v[NV][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int i = threadIdx.x + j * blockDim.x;
+    if (i < nvec) {
+      uint4 a = xr[i];
+      const T* ae = reinterpret_cast<const T*>(&a);
+      if (rr) {
+        uint4 b = rr[i];
+        const T* be = reinterpret_cast<const T*>(&b);
+        uint4 c;
+        T* ce = reinterpret_cast<T*>(&c);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          ce[e] = from_float<T>(to_float(ae[e]) + to_float(be[e]));  // residual stream kept in T
+          v[j][e] = to_float(ce[e]);
+        }
+        rr[i] = c;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[j][e] = to_float(ae[e]);
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ss += v[j][e] * v[j][e];
+    }
+  }
+  ss = block_sum(ss, red);
+  const float inv = rsqrtf(ss / (float)dim + eps);
+  uint4* orow = reinterpret_cast<uint4*>(out + (int64_t)r * out_stride);
+  const uint4* wv = reinterpret_cast<const uint4*>(weight);
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int i = threadIdx.x + j * blockDim.x;
+    if (i < nvec) {
+      uint4 c;
+      T* ce = reinterpret_cast<T*>(&c);
+      if (weight) {
+        uint4 w = __ldg(wv + i);
+        const T* we = reinterpret_cast<const T*>(&w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ce[e] = from_float<T>(v[j][e] * inv * to_float(we[e]));
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ce[e] = from_float<T>(v[j][e] * inv);
+      }
+      orow[i] = c;
+    }
+  }
+}
+
 // One CTA per token; threads over (head, pair).
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -185,6 +249,33 @@ extern "C" int b200_rms_norm(const void* x, void* residual, const void* weight, 
   B200_CHECK_ARG(rows > 0 && dim > 0 && x && out, "rms_norm: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   const int threads = dim >= 1024 ? 256 : (dim >= 256 ? 128 : 32);
+  const bool aligned = dim % 8 == 0 && dtype != B200_F32 && x_stride % 8 == 0 && res_stride % 8 == 0 &&
+                       out_stride % 8 == 0 && (uintptr_t)x % 16 == 0 && (uintptr_t)out % 16 == 0 &&
+                       (uintptr_t)residual % 16 == 0 && (uintptr_t)weight % 16 == 0;
+  if (aligned && dim >= 512 && dim <= 1024 * 8 * 2) {
+    // threads: one 16-byte vector each (two for dim > 8192), rounded up to whole warps
+    const int nvec = dim / 8;
+    const int nv = nvec > 1024 ? 2 : 1;
+    const int vt = ((nvec + nv - 1) / nv + 31) / 32 * 32;
+    if (dtype == B200_BF16) {
+      using T = __nv_bfloat16;
+      if (nv == 1)
+        rms_norm_vec_kernel<T, 1><<<rows, vt, 0, st>>>((const T*)x, (T*)residual, (const T*)weight, (T*)out,
+                                                        dim, x_stride, res_stride, out_stride, eps);
+      else
+        rms_norm_vec_kernel<T, 2><<<rows, vt, 0, st>>>((const T*)x, (T*)residual, (const T*)weight, (T*)out,
+                                                        dim, x_stride, res_stride, out_stride, eps);
+    } else {
+      using T = __half;
+      if (nv == 1)
+        rms_norm_vec_kernel<T, 1><<<rows, vt, 0, st>>>((const T*)x, (T*)residual, (const T*)weight, (T*)out,
+                                                        dim, x_stride, res_stride, out_stride, eps);
+      else
+        rms_norm_vec_kernel<T, 2><<<rows, vt, 0, st>>>((const T*)x, (T*)residual, (const T*)weight, (T*)out,
+                                                        dim, x_stride, res_stride, out_stride, eps);
+    }
+    return check_launch("rms_norm_vec_kernel");
+  }
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
     rms_norm_kernel<T><<<rows, threads, 0, st>>>((const T*)x, (T*)residual, (const T*)weight,
                                                  (T*)out, dim, x_stride, res_stride, out_stride,

@@ -10,13 +10,14 @@
 // One CTA owns 128 output features (UMMA M = 128 = weight rows) and a batch tile of NB rows
 // of x (UMMA N = NB in {16..256}); the fp32 accumulator [128 x NB] lives in TMEM.
 //
-//   warp 4 (1 thread)  TMA: packed uint32 weight tiles [128 rows x 128 B] -> smem ring (PS deep)
-//   warp 5 (1 thread)  TMA: x tiles [NB x 64] bf16, 128B-swizzled K-major  -> B ring (NS deep)
-//   warps 0-3          one thread per weight row: unpack 64 int4/int8 -> s*q+b (bf16x2 HFMA2, single
-//                      rounding) -> A ring in the canonical K-major SWIZZLE_128B layout
-//   warp 6 (1 thread)  tcgen05.mma.cta_group::1.kind::f16 128xNBx16, 4 per 64-wide k block;
+//   warps 0..DQW-1     dequant: DQW/4 threads per weight row, each unpacks its share of the 64-wide
+//                      k block (int4/int8 -> s*q+b, bf16x2 HFMA2, single rounding) -> A ring in the
+//                      canonical K-major SWIZZLE_128B layout
+//   warp DQW   (1 thr)  TMA: packed uint32 weight tiles [128 rows x 128 B] -> smem ring (PS deep)
+//   warp DQW+1 (1 thr)  TMA: x tiles [NB x 64] bf16, 128B-swizzled K-major  -> B ring (NS deep)
+//   warp DQW+2 (1 thr)  tcgen05.mma.cta_group::1.kind::f16 128xNBx16, 4 per 64-wide k block;
 //                      tcgen05.commit frees the A/B stage and finally signals the epilogue
-//   warps 0-3          epilogue: tcgen05.ld -> (+bias) -> y
+//   warps 0..DQW-1     epilogue: tcgen05.ld -> (+bias) -> y (warp w reads TMEM lanes 32*(w%4)..)
 //
 // Matrices with few row tiles (o_proj, down_proj: N = hidden) are split along K over a thread
 // block CLUSTER (1 x ksplit x 1); partial accumulators are exchanged through distributed
@@ -34,7 +35,6 @@ constexpr int ROWS = 128;  // weight rows per CTA (UMMA M)
 constexpr int KB = 64;     // k elements per A/B stage (128 bytes of 16-bit)
 constexpr int A_STAGE_BYTES = ROWS * 128;
 constexpr int P_STAGE_BYTES = ROWS * 128;
-constexpr int NUM_THREADS = 7 * 32;
 
 // ---------------------------------------------------------------- PTX helpers ----
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -254,8 +254,8 @@ __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[CW]) {
 
 // T: activation / scale type; BITS: 4|8; G: quantisation group; NB: batch tile (UMMA N);
 // PS/NS: ring depths.
-template <typename T, int BITS, int G, int NB, int PS, int NS>
-__global__ void __launch_bounds__(NUM_THREADS)
+template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW>
+__global__ void __launch_bounds__((DQW + 3) * 32, NB <= 64 ? 2 : 1)
 qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
                 const Params p) {
   using C = Cvt<T>;
@@ -266,6 +266,11 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   constexpr int B_STAGE_BYTES = NB * 128;
   constexpr int TMEM_COLS = NB < 32 ? 32 : NB;
   constexpr int GPP = KPP / G;  // groups per packed stage (>= 1)
+  constexpr int TPR = DQW / 4;                // dequant threads per weight row: 1 | 2
+  constexpr int CH_T = CH_PER_KB / TPR;       // packed chunks per thread per k block
+  constexpr int W_TMA = DQW, W_X = DQW + 1, W_MMA = DQW + 2;
+  static_assert(DQW == 4 || DQW == 8, "4 or 8 dequant warps");
+  static_assert(CH_PER_KB % TPR == 0, "chunks must split evenly over the row's threads");
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -295,16 +300,16 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   if (threadIdx.x == 0) {
     for (int i = 0; i < PS; ++i) {
       mbar_init(bar_full_p + 8 * i, 1);
-      mbar_init(bar_empty_p + 8 * i, 4);
+      mbar_init(bar_empty_p + 8 * i, DQW);
     }
     for (int i = 0; i < NS; ++i) {
-      mbar_init(bar_full_ab + 8 * i, 5);  // 4 dequant warps + the x producer's expect_tx arrive
+      mbar_init(bar_full_ab + 8 * i, DQW + 1);  // dequant warps + the x producer's expect_tx arrive
       mbar_init(bar_empty_ab + 8 * i, 1);
     }
     mbar_init(bar_tmem_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 6) {
+  if (warp == W_MMA) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_ptr_addr),
                  "n"(TMEM_COLS)
                  : "memory");
@@ -315,7 +320,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
 
-  if (warp == 4) {
+  if (warp == W_TMA) {
     // ===== packed-weight TMA producer =====
     if (lane == 0) {
       for (int ps = 0; ps < my_ps; ++ps) {
@@ -327,7 +332,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
       }
     }
     __syncwarp();
-  } else if (warp == 5) {
+  } else if (warp == W_X) {
     // ===== x tile TMA producer =====
     if (lane == 0) {
       for (int kb = 0; kb < my_kb; ++kb) {
@@ -338,7 +343,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
       }
     }
     __syncwarp();
-  } else if (warp == 6) {
+  } else if (warp == W_MMA) {
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(C::kFmt, ROWS, NB);
@@ -357,16 +362,49 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
     }
     __syncwarp();
   } else {
-    // ===== dequant warps: thread r owns weight row n0 + r =====
-    const int r = threadIdx.x;
+    // ===== dequant warps: row n0 + r is shared by TPR threads (hsel picks the chunk share) =====
+    const int r = threadIdx.x & (ROWS - 1);
+    const int hsel = threadIdx.x >> 7;  // 0 .. TPR-1
     const int n = min(n0 + r, p.N - 1);
     const int groups_per_row = p.K / G;
     const uint16_t* srow = p.scales + (int64_t)n * groups_per_row;
     const uint16_t* brow = p.biases + (int64_t)n * groups_per_row;
     const uint32_t xr = (uint32_t)(r & 7);
     uint16_t s_nxt[GPP], b_nxt[GPP];
+    // rows of scales/biases are 2*K/G bytes: vector loads need every stage start aligned
+    const bool sb_vec = (GPP == 1) || ((groups_per_row % GPP) == 0);
     auto load_sb = [&](int ps) {
       const int g0 = (kb_begin * KB + ps * KPP) / G;  // stage starts are group aligned
+      if (sb_vec && g0 + GPP <= groups_per_row) {
+        if constexpr (GPP == 8) {
+          const uint4 sv = __ldg(reinterpret_cast<const uint4*>(srow + g0));
+          const uint4 bv = __ldg(reinterpret_cast<const uint4*>(brow + g0));
+          const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w}, bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            s_nxt[2 * i] = (uint16_t)(sw[i] & 0xFFFFu);
+            s_nxt[2 * i + 1] = (uint16_t)(sw[i] >> 16);
+            b_nxt[2 * i] = (uint16_t)(bw[i] & 0xFFFFu);
+            b_nxt[2 * i + 1] = (uint16_t)(bw[i] >> 16);
+          }
+        } else if constexpr (GPP == 4) {
+          const uint2 sv = __ldg(reinterpret_cast<const uint2*>(srow + g0));
+          const uint2 bv = __ldg(reinterpret_cast<const uint2*>(brow + g0));
+          s_nxt[0] = (uint16_t)(sv.x & 0xFFFFu); s_nxt[1] = (uint16_t)(sv.x >> 16);
+          s_nxt[2] = (uint16_t)(sv.y & 0xFFFFu); s_nxt[3] = (uint16_t)(sv.y >> 16);
+          b_nxt[0] = (uint16_t)(bv.x & 0xFFFFu); b_nxt[1] = (uint16_t)(bv.x >> 16);
+          b_nxt[2] = (uint16_t)(bv.y & 0xFFFFu); b_nxt[3] = (uint16_t)(bv.y >> 16);
+        } else if constexpr (GPP == 2) {
+          const uint32_t sv = __ldg(reinterpret_cast<const uint32_t*>(srow + g0));
+          const uint32_t bv = __ldg(reinterpret_cast<const uint32_t*>(brow + g0));
+          s_nxt[0] = (uint16_t)(sv & 0xFFFFu); s_nxt[1] = (uint16_t)(sv >> 16);
+          b_nxt[0] = (uint16_t)(bv & 0xFFFFu); b_nxt[1] = (uint16_t)(bv >> 16);
+        } else {
+          s_nxt[0] = __ldg(srow + g0);
+          b_nxt[0] = __ldg(brow + g0);
+        }
+        return;
+      }
 #pragma unroll
       for (int i = 0; i < GPP; ++i) {
         const bool ok = g0 + i < groups_per_row;
@@ -378,16 +416,27 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
     for (int ps = 0; ps < my_ps; ++ps) {
       const int pst = ps % PS;
       // this stage's scales/biases, broadcast once; then prefetch the next stage's
-      T2 s2[GPP], b2[GPP];
-      float sf[GPP], bf[GPP];
+      // (G == 32 with two threads per row: a thread only ever touches group 2j + hsel of k block j)
+      constexpr bool SEL = (G < KB) && (TPR == 2);
+      constexpr int NG = SEL ? GPP / 2 : GPP;
+      T2 s2[NG], b2[NG];
+      float sf[NG], bf[NG];
 #pragma unroll
-      for (int i = 0; i < GPP; ++i) {
-        if constexpr (BITS == 4) {
-          s2[i] = C::bcast(s_nxt[i]);
-          b2[i] = C::bcast(b_nxt[i]);
+      for (int i = 0; i < NG; ++i) {
+        uint16_t sr, br;
+        if constexpr (SEL) {
+          sr = hsel ? s_nxt[2 * i + 1] : s_nxt[2 * i];
+          br = hsel ? b_nxt[2 * i + 1] : b_nxt[2 * i];
         } else {
-          sf[i] = C::to_f(s_nxt[i]);
-          bf[i] = C::to_f(b_nxt[i]);
+          sr = s_nxt[i];
+          br = b_nxt[i];
+        }
+        if constexpr (BITS == 4) {
+          s2[i] = C::bcast(sr);
+          b2[i] = C::bcast(br);
+        } else {
+          sf[i] = C::to_f(sr);
+          bf[i] = C::to_f(br);
         }
       }
       (void)s2; (void)b2; (void)sf; (void)bf;
@@ -399,40 +448,63 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
         const int kb = ps * KB_PER_P + j;
         if (kb < my_kb) {
           const int st = kb % NS;
+          // all of this thread's packed chunks first (independent loads), then the ring slot
+          uint4 pk[CH_T];
+#pragma unroll
+          for (int cc = 0; cc < CH_T; ++cc) {
+            const uint32_t c = (uint32_t)(hsel * CH_T + cc);
+            const uint32_t src = prow + ((((uint32_t)(j * CH_PER_KB) + c) ^ xr) << 4);
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(pk[cc].x), "=r"(pk[cc].y), "=r"(pk[cc].z), "=r"(pk[cc].w)
+                         : "r"(src));
+          }
           mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
           const uint32_t arow = sm_a + st * A_STAGE_BYTES + r * 128;
 #pragma unroll
-          for (int c = 0; c < CH_PER_KB; ++c) {
-            uint4 pk;
-            const uint32_t src = prow + ((((uint32_t)(j * CH_PER_KB + c)) ^ xr) << 4);
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(pk.x), "=r"(pk.y), "=r"(pk.z), "=r"(pk.w)
-                         : "r"(src));
+          for (int cc = 0; cc < CH_T; ++cc) {
+            const int c = hsel * CH_T + cc;
             if constexpr (BITS == 4) {  // chunk = 4 words x 8 nibbles = 32 k
-              const uint32_t words[4] = {pk.x, pk.y, pk.z, pk.w};
+              const uint32_t words[4] = {pk[cc].x, pk[cc].y, pk[cc].z, pk[cc].w};
+              // group of this 32-k chunk: one per k block for G >= 64, one per chunk for G == 32
+              T2 sg, bg;
+              if constexpr (G >= KB) {
+                sg = s2[(j * KB) / G];
+                bg = b2[(j * KB) / G];
+              } else if constexpr (SEL) {
+                sg = s2[j];
+                bg = b2[j];
+              } else {  // one thread per row: cc is a compile-time chunk index
+                sg = s2[j * 2 + (cc & 1)];
+                bg = b2[j * 2 + (cc & 1)];
+              }
+              uint4 o[4];
+#pragma unroll
+              for (int wi = 0; wi < 4; ++wi) o[wi] = dequant_word4<T>(words[wi], sg, bg);
 #pragma unroll
               for (int wi = 0; wi < 4; ++wi) {
-                constexpr int dummy = 0;
-                (void)dummy;
-                const int gi = (j * KB + c * 32 + wi * 8) / G;  // compile-time after unrolling
-                const uint4 o = dequant_word4<T>(words[wi], s2[gi], b2[gi]);
                 const uint32_t chunk = (uint32_t)(c * 4 + wi);  // 8 elements = 16 B of the A row
                 asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + ((chunk ^ xr) << 4)),
-                             "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w)
-                             : "memory");
+                             "r"(o[wi].x), "r"(o[wi].y), "r"(o[wi].z), "r"(o[wi].w));
               }
             } else {  // chunk = 4 words x 4 bytes = 16 k
-              const int gi = (j * KB + c * 16) / G;
-              const float s = sf[gi], b = bf[gi];
-              const uint2 lo0 = dequant_word8<T>(pk.x, s, b), lo1 = dequant_word8<T>(pk.y, s, b);
-              const uint2 hi0 = dequant_word8<T>(pk.z, s, b), hi1 = dequant_word8<T>(pk.w, s, b);
+              float sc, bi;
+              if constexpr (G >= KB) {
+                sc = sf[(j * KB) / G];
+                bi = bf[(j * KB) / G];
+              } else if constexpr (SEL) {  // G == 32: chunks 0,1 -> first group of the k block, 2,3 -> second
+                sc = sf[j];
+                bi = bf[j];
+              } else {
+                sc = sf[j * 2 + (cc >> 1)];
+                bi = bf[j * 2 + (cc >> 1)];
+              }
+              const uint2 lo0 = dequant_word8<T>(pk[cc].x, sc, bi), lo1 = dequant_word8<T>(pk[cc].y, sc, bi);
+              const uint2 hi0 = dequant_word8<T>(pk[cc].z, sc, bi), hi1 = dequant_word8<T>(pk[cc].w, sc, bi);
               const uint32_t chunk = (uint32_t)(c * 2);
               asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + ((chunk ^ xr) << 4)),
-                           "r"(lo0.x), "r"(lo0.y), "r"(lo1.x), "r"(lo1.y)
-                           : "memory");
+                           "r"(lo0.x), "r"(lo0.y), "r"(lo1.x), "r"(lo1.y));
               asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + (((chunk + 1) ^ xr) << 4)),
-                           "r"(hi0.x), "r"(hi0.y), "r"(hi1.x), "r"(hi1.y)
-                           : "memory");
+                           "r"(hi0.x), "r"(hi0.y), "r"(hi1.x), "r"(hi1.y));
             }
           }
           fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
@@ -444,40 +516,47 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
       if (lane == 0) mbar_arrive(bar_empty_p + 8 * pst);
     }
 
-    // ===== epilogue (same 4 warps: thread r <-> TMEM lane r <-> output feature n0 + r) =====
+    // ===== epilogue (dequant warps: thread <-> TMEM lane r <-> output feature n0 + r;
+    //       with 8 warps the batch columns are split in two halves) =====
     if (my_kb > 0) {
       mbar_wait(bar_tmem_full, 0);
       tc_fence_after();
     }
-    const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     const int nn = n0 + r;
     constexpr int CW = NB < 32 ? 16 : 32;  // columns per tcgen05.ld
+    constexpr int ESPLIT = (NB / TPR >= CW) ? TPR : 1;  // column shares among the row's threads
+    constexpr int ECOLS = NB / ESPLIT;
+    const bool epi_active = hsel < ESPLIT;
+    const int ec0 = hsel * ECOLS;
     if (ksplit == 1) {
       T* yp = reinterpret_cast<T*>(p.y);
       const float bias_v =
           (p.bias != nullptr && nn < p.N) ? to_float(reinterpret_cast<const T*>(p.bias)[nn]) : 0.f;
+      if (epi_active) {
 #pragma unroll 1
-      for (int c0 = 0; c0 < NB; c0 += CW) {
-        uint32_t v[CW];
-        if (my_kb > 0) {
-          tmem_ld<CW>(taddr + c0, v);
-        } else {
+        for (int c0 = ec0; c0 < ec0 + ECOLS; c0 += CW) {
+          uint32_t v[CW];
+          if (my_kb > 0) {
+            tmem_ld<CW>(taddr + c0, v);
+          } else {
 #pragma unroll
-          for (int i = 0; i < CW; ++i) v[i] = 0u;
-        }
-        if (nn < p.N) {
+            for (int i = 0; i < CW; ++i) v[i] = 0u;
+          }
+          if (nn < p.N) {
 #pragma unroll
-          for (int i = 0; i < CW; ++i) {
-            const int m = m0 + c0 + i;
-            if (m < p.M) yp[(int64_t)m * p.y_stride + nn] = from_float<T>(__uint_as_float(v[i]) + bias_v);
+            for (int i = 0; i < CW; ++i) {
+              const int m = m0 + c0 + i;
+              if (m < p.M) yp[(int64_t)m * p.y_stride + nn] = from_float<T>(__uint_as_float(v[i]) + bias_v);
+            }
           }
         }
       }
-    } else {
+    } else if (epi_active) {
       // split-K: stage the fp32 partial [NB][128] in our own smem (the A ring is idle now)
       const uint32_t red = sm_a;
 #pragma unroll 1
-      for (int c0 = 0; c0 < NB; c0 += CW) {
+      for (int c0 = ec0; c0 < ec0 + ECOLS; c0 += CW) {
         uint32_t v[CW];
         if (my_kb > 0) {
           tmem_ld<CW>(taddr + c0, v);
@@ -498,48 +577,48 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
     tc_fence_before();
     cluster_sync_all();
     if constexpr (NB <= 64) {
-      if (warp < 4) {
-        // Rank j owns the batch columns c with c % ksplit == j.  Thread t sums 4 consecutive
-        // output features (float4) of column group t / 32 over all peers' partials (DSMEM).
-        constexpr int NV = NB / 4;  // float4 loads per thread = (NB / ksplit / 4 columns) x ksplit peers
-        const int t = threadIdx.x;
-        const int r4 = (t & 31) * 4;
-        const int lk = 31 - __clz(ksplit);  // log2(ksplit)
+      if (warp < DQW) {
+        // Rank j owns the batch columns c with c % ksplit == j.  A warp sums, for one such column,
+        // 4 consecutive output features per lane (float4) over all peers' partials through
+        // DSMEM, in peer order (deterministic), and writes 8 contiguous bytes per lane.
+        const int r4 = lane * 4;
         const uint32_t red = sm_a;
-        float4 v[NV];
-#pragma unroll
-        for (int i = 0; i < NV; ++i) {
-          const int ci = i >> lk, peer = i & (ksplit - 1);
-          const int c = krank + ((ci * 4 + (t >> 5)) << lk);
-          v[i] = ld_dsmem_v4(red + (uint32_t)((c * ROWS + r4) * 4), (uint32_t)peer);
-        }
-#pragma unroll
-        for (int step = 1; step < 8; step *= 2) {
-          if (step < ksplit) {
-#pragma unroll
-            for (int i = 0; i + step < NV; i += 2 * step) {
-              v[i].x += v[i + step].x;
-              v[i].y += v[i + step].y;
-              v[i].z += v[i + step].z;
-              v[i].w += v[i + step].w;
-            }
-          }
-        }
+        const int cols_owned = NB / ksplit;
         T* yp = reinterpret_cast<T*>(p.y);
         const T* bp = reinterpret_cast<const T*>(p.bias);
         const int nn = n0 + r4;
+        for (int ci = warp; ci < cols_owned; ci += DQW) {
+          const int c = krank + ci * ksplit;
+          float4 v[8];
 #pragma unroll
-        for (int i = 0; i < NV; ++i) {
-          if ((i & (ksplit - 1)) != 0) continue;
-          const int ci = i >> lk;
-          const int m = m0 + krank + ((ci * 4 + (t >> 5)) << lk);
+          for (int peer = 0; peer < 8; ++peer)
+            if (peer < ksplit) v[peer] = ld_dsmem_v4(red + (uint32_t)((c * ROWS + r4) * 4), (uint32_t)peer);
+          float4 acc = v[0];
+#pragma unroll
+          for (int peer = 1; peer < 8; ++peer)
+            if (peer < ksplit) {
+              acc.x += v[peer].x;
+              acc.y += v[peer].y;
+              acc.z += v[peer].z;
+              acc.w += v[peer].w;
+            }
+          const int m = m0 + c;
           if (m >= p.M) continue;
-          const float o[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+          const float o[4] = {acc.x, acc.y, acc.z, acc.w};
+          if (nn + 3 < p.N && ((p.y_stride & 3) == 0) && (((uintptr_t)yp & 7) == 0)) {
+            const float b0 = bp ? to_float(bp[nn]) : 0.f, b1 = bp ? to_float(bp[nn + 1]) : 0.f;
+            const float b2v = bp ? to_float(bp[nn + 2]) : 0.f, b3 = bp ? to_float(bp[nn + 3]) : 0.f;
+            uint2 pkd;
+            pkd.x = C::f2(o[0] + b0, o[1] + b1);
+            pkd.y = C::f2(o[2] + b2v, o[3] + b3);
+            *reinterpret_cast<uint2*>(yp + (int64_t)m * p.y_stride + nn) = pkd;
+          } else {
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (nn + e < p.N)
-              yp[(int64_t)m * p.y_stride + nn + e] =
-                  from_float<T>(o[e] + (bp ? to_float(bp[nn + e]) : 0.f));
+            for (int e = 0; e < 4; ++e)
+              if (nn + e < p.N)
+                yp[(int64_t)m * p.y_stride + nn + e] =
+                    from_float<T>(o[e] + (bp ? to_float(bp[nn + e]) : 0.f));
+          }
         }
       }
     }
@@ -549,7 +628,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 6) {
+  if (warp == W_MMA) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS)
                  : "memory");
@@ -603,10 +682,10 @@ struct HostArgs {
   int64_t x_stride, y_stride;
 };
 
-template <typename T, int BITS, int G, int NB, int PS, int NS>
+template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW>
 static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
   constexpr int smem = smem_bytes<NB, PS, NS>();
-  auto kern = qgemm_tc_kernel<T, BITS, G, NB, PS, NS>;
+  auto kern = qgemm_tc_kernel<T, BITS, G, NB, PS, NS, DQW>;
   constexpr int KB_PER_P = (1024 / BITS) / KB;
   static bool configured = false;
   if (!configured) {
@@ -637,7 +716,7 @@ static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
   p.kb_per_split = ((p.num_kb + ksplit - 1) / ksplit + KB_PER_P - 1) / KB_PER_P * KB_PER_P;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((a.N + ROWS - 1) / ROWS, ksplit, (a.M + NB - 1) / NB);
-  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.blockDim = dim3((DQW + 3) * 32);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -651,21 +730,32 @@ static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
   return B200_OK;
 }
 
+// Tuning knobs (b200_set_qlinear_tuning): 0 = heuristic.
+static int g_force_ksplit = 0;
+static int g_force_dqw = 0;
+
 template <typename T, int BITS, int G>
 static int dispatch_g(const HostArgs& a, cudaStream_t st) {
   const int tiles = (a.N + ROWS - 1) / ROWS;
   const int num_kb = a.K / KB;
+  constexpr int KB_PER_P = (1024 / BITS) / KB;
   if (a.M <= 64) {
-    // Few row tiles: split K over a cluster until ~2 CTAs per SM stream weights.
+    // Weight-streaming regime.  Two CTAs fit per SM; matrices with few row tiles are split along
+    // K over a cluster until every SM has CTAs streaming, keeping >= 2 packed stages per rank.
     const int sms = sm_count() > 0 ? sm_count() : 148;
     int ksplit = 1;
-    while (ksplit < 8 && tiles * ksplit * 2 <= 2 * sms && num_kb / (ksplit * 2) >= 4) ksplit *= 2;
-    if (a.M <= 16)  // the in-cluster reduce needs >= 4 batch columns per rank
-      return launch_cfg<T, BITS, G, 16, 3, 2>(a, ksplit > 4 ? 4 : ksplit, st);
-    return launch_cfg<T, BITS, G, 64, 3, 2>(a, ksplit, st);
+    while (ksplit < 8 && tiles * ksplit < 2 * sms && num_kb / (ksplit * 2) >= 2 * KB_PER_P) ksplit *= 2;
+    if (g_force_ksplit > 0) ksplit = g_force_ksplit;
+    while (ksplit > 1 && num_kb / ksplit < KB_PER_P) ksplit /= 2;
+    const bool dq8 = g_force_dqw ? g_force_dqw == 8 : true;
+    if (a.M <= 16)
+      return dq8 ? launch_cfg<T, BITS, G, 16, 3, 2, 8>(a, ksplit, st)
+                 : launch_cfg<T, BITS, G, 16, 3, 2, 4>(a, ksplit, st);
+    return dq8 ? launch_cfg<T, BITS, G, 64, 3, 2, 8>(a, ksplit, st)
+               : launch_cfg<T, BITS, G, 64, 3, 2, 4>(a, ksplit, st);
   }
-  if (a.M <= 128) return launch_cfg<T, BITS, G, 128, 3, 3>(a, 1, st);
-  return launch_cfg<T, BITS, G, 256, 2, 3>(a, 1, st);
+  if (a.M <= 128) return launch_cfg<T, BITS, G, 128, 3, 3, 8>(a, 1, st);
+  return launch_cfg<T, BITS, G, 256, 2, 3, 8>(a, 1, st);
 }
 
 template <typename T, int BITS>
@@ -691,6 +781,17 @@ bool qgemm_tc_supported(const void* x, const uint32_t* w, int M, int N, int K, i
   (void)M;
   (void)N;
   return qtc::encode_fn() != nullptr;
+}
+
+int qgemm_tc_set_tuning(int ksplit, int dequant_warps) {
+  if (!(ksplit == 0 || ksplit == 1 || ksplit == 2 || ksplit == 4 || ksplit == 8))
+    return set_error(B200_ERR_INVALID_ARGUMENT, "qlinear tuning: ksplit must be 0, 1, 2, 4 or 8, got %d", ksplit);
+  if (!(dequant_warps == 0 || dequant_warps == 4 || dequant_warps == 8))
+    return set_error(B200_ERR_INVALID_ARGUMENT, "qlinear tuning: dequant_warps must be 0, 4 or 8, got %d",
+                     dequant_warps);
+  qtc::g_force_ksplit = ksplit;
+  qtc::g_force_dqw = dequant_warps;
+  return B200_OK;
 }
 
 int qgemm_tc_launch(const void* x, const uint32_t* w, const void* scales, const void* biases,

@@ -22,6 +22,8 @@ int qgemm_tc_launch(const void* x, const uint32_t* w, const void* scales, const 
                     const void* bias, void* y, int M, int N, int K, int group_size, int bits, int dtype,
                     int64_t x_stride, int64_t y_stride, cudaStream_t st);
 
+int qgemm_tc_set_tuning(int ksplit, int dequant_warps);
+
 static int g_qlinear_kernel = 0;  // 0 auto, 1 mma.sync kernel, 2 tcgen05 kernel
 
 namespace ql {
@@ -387,6 +389,10 @@ extern "C" int b200_set_qlinear_kernel(int kernel) {
     return b200::set_error(B200_ERR_INVALID_ARGUMENT, "set_qlinear_kernel: expected 0, 1 or 2, got %d", kernel);
   b200::g_qlinear_kernel = kernel;
   return B200_OK;
+}
+
+extern "C" int b200_set_qlinear_tuning(int ksplit, int dequant_warps) {
+  return b200::qgemm_tc_set_tuning(ksplit, dequant_warps);
 }
 
 extern "C" int b200_dequantize_rows(const uint32_t* w, const void* scales, const void* biases,

@@ -92,9 +92,11 @@ EXPORTED_SYMBOLS = (
     "b200_paged_attention",
     "b200_qlinear",
     "b200_set_qlinear_kernel",
+    "b200_set_qlinear_tuning",
     "b200_dequantize_rows",
     "b200_rms_norm",
     "b200_rope",
+    "b200_norm_rope_cache",
     "b200_silu_mul",
     "b200_argmax",
     "b200_add_inplace",
@@ -141,6 +143,8 @@ def load_library() -> ctypes.CDLL:
     lib.b200_dequantize_rows.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
     lib.b200_rms_norm.argtypes = [vp, vp, vp, vp, i32, i32, i64, i64, i64, f32, i32, vp]
     lib.b200_rope.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i64, i64, i32, vp]
+    lib.b200_norm_rope_cache.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32,
+                                         f32, i64, i64, i64, i32, i64, i64, i64, i32, vp]
     lib.b200_silu_mul.argtypes = [vp, vp, i32, i32, i64, i64, i32, vp]
     lib.b200_argmax.argtypes = [vp, vp, i32, i32, i64, i32, vp]
     lib.b200_add_inplace.argtypes = [vp, vp, i32, i32, i64, i64, i32, vp]
@@ -420,6 +424,10 @@ class _Ops:
         """0 = auto, 1 = mma.sync kernel, 2 = tcgen05 kernel (raises if the shape does not qualify)."""
         self._check(self._lib.b200_set_qlinear_kernel(int(kernel)))
 
+    def set_qlinear_tuning(self, ksplit: int = 0, dequant_warps: int = 0) -> None:
+        """Sweep knob of the tcgen05 kernel's M <= 64 regime (0 = heuristic)."""
+        self._check(self._lib.b200_set_qlinear_tuning(int(ksplit), int(dequant_warps)))
+
     def dequantize(self, w, scales, biases, group_size: int = 64, bits: int = 4, ids=None,
                    dtype: torch.dtype | None = None):
         """``mx.dequantize(w[ids], scales[ids], biases[ids], group_size, bits)``."""
@@ -473,6 +481,45 @@ class _Ops:
                                  0 if k is None else k.stride(0), _dtype_code("q", q), _stream())
         self._check(rc)
         self.launches += 1
+
+    def norm_rope_cache(self, q, k, v, key_cache, value_cache, slot_mapping, positions=None,
+                        rot_dim: int = 0, base: float = 10000.0, traditional: bool = False,
+                        q_norm_weight=None, k_norm_weight=None, eps: float = 1e-6):
+        """Fused per-head RMSNorm -> RoPE -> cache write (sdpa.py:348-368,:638 in one launch).
+
+        ``q [T,Hq,D]``, ``k``/``v [T,Hk,D]`` may be strided views of one qkv buffer (head rows
+        contiguous); q and k are updated in place, rotated k and v land in the caches.
+        """
+        for n, t in (("q", q), ("k", k), ("v", v), ("key_cache", key_cache), ("value_cache", value_cache),
+                     ("slot_mapping", slot_mapping)):
+            _require_cuda(n, t)
+        if q.dim() != 3 or k.dim() != 3 or v.shape != k.shape:
+            raise ValueError("q must be [T, Hq, D]; k and v must both be [T, Hk, D]")
+        t, hq, d = q.shape
+        hk = k.shape[1]
+        for n, x in (("q", q), ("k", k), ("v", v)):
+            if x.stride(2) != 1 or x.stride(1) != d:
+                raise ValueError(f"{n}: heads must be contiguous ([T, H, D] with unit head stride)")
+        if key_cache.dim() != 4 or value_cache.shape != key_cache.shape or key_cache.shape[2:] != (hk, d):
+            raise ValueError("key_cache/value_cache must both be [num_blocks, block_size, Hk, D]")
+        if not (q.dtype == k.dtype == v.dtype == key_cache.dtype == value_cache.dtype):
+            raise ValueError("q/k/v must already be in the cache dtype")
+        if key_cache.stride()[2:] != (d, 1) or value_cache.stride() != key_cache.stride():
+            raise ValueError("cache rows [Hk, D] must be contiguous and K/V strides equal")
+        if slot_mapping.dtype != torch.int64 or slot_mapping.shape != (t,):
+            raise ValueError("slot_mapping must be int64 [T]")
+        if rot_dim and (positions is None or positions.dtype != torch.int32):
+            raise ValueError("positions must be int32 [T] when rot_dim > 0")
+        nb, bs = key_cache.shape[:2]
+        rc = self._lib.b200_norm_rope_cache(
+            q.data_ptr(), k.data_ptr(), v.data_ptr(), _ptr(q_norm_weight), _ptr(k_norm_weight),
+            _ptr(positions), slot_mapping.contiguous().data_ptr(), key_cache.data_ptr(),
+            value_cache.data_ptr(), t, hq, hk, d, int(rot_dim), float(base), int(traditional), float(eps),
+            q.stride(0), k.stride(0), v.stride(0), bs, nb, key_cache.stride(0), key_cache.stride(1),
+            _dtype_code("q", q), _stream())
+        self._check(rc)
+        self.launches += 1
+        return key_cache, value_cache
 
     def silu_mul(self, gate_up, out=None):
         _require_cuda("gate_up", gate_up)
