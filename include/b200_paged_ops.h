@@ -188,6 +188,27 @@ int b200_set_qlinear_kernel(int kernel);
  * 1, 2, 4 or 8), `dequant_warps` = 0 (default), 4 or 8.  Process-wide; returns 0 on success. */
 int b200_set_qlinear_tuning(int ksplit, int dequant_warps);
 
+/* Ring-configuration knob of the M <= 64 regime for the sweep (0 = default: TMA-staged
+ * scales/biases, packed ring 2 / operand ring 3; 1 = per-thread scale loads, rings 3/2;
+ * 2 = TMA-staged scales, rings 3/2).  Process-wide. */
+int b200_set_qlinear_variant(int variant);
+
+/* Load-time repack into the streaming layout read by b200_qlinear_prepacked: same shape as
+ * `w` ([N, K*bits/32] uint32); for bits == 4 the 8 nibbles of every word are permuted so that
+ * nibbles (i, i+4) hold elements (2i, 2i+1); bits == 8 is a copy.  `inverse` != 0 undoes it
+ * (bit-exact round trip).  `out` may alias `w`.  Reference counterpart: none -- MLX streams its
+ * own layout; this is the B200 analogue of a loader-side weight transform such as
+ * quant/awq_loader.py:49-224. */
+int b200_qlinear_prepack(const uint32_t* w, uint32_t* out, int N, int K, int bits,
+                         int inverse, void* stream);
+
+/* b200_qlinear over weights in the streaming layout (scales / biases unchanged).  Only the
+ * tcgen05 kernel reads this layout: shapes it does not take fail with B200_ERR_UNSUPPORTED. */
+int b200_qlinear_prepacked(const void* x, const uint32_t* wp, const void* scales,
+                           const void* biases, const void* bias, void* y, int M, int N,
+                           int K, int group_size, int bits, int dtype, int sb_dtype,
+                           int64_t x_stride, int64_t y_stride, void* stream);
+
 /* out[r, :] = dequantize(row ids[r]) for r in [0, num_rows); ids == NULL means
  * rows 0..num_rows-1 (plain mx.dequantize).  ids are int32 (token ids). */
 int b200_dequantize_rows(const uint32_t* w, const void* scales,

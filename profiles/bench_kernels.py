@@ -109,22 +109,40 @@ def main():
         t_mma = time_us(run, copies)
         ops.set_qlinear_kernel(0)
         rows = {"mma_sync": {"us": t_mma, "gbs": nbytes / t_mma / 1e3}}
-        grid = [(0, 0)]
+        # (ksplit, dequant warps, ring variant, prepacked layout)
+        grid = [(0, 0, 0, 0), (0, 0, 0, 1)]
         if args.sweep:
-            grid += [(ks, dq) for dq in (4, 8) for ks in (1, 2, 4, 8)]
-        for ks, dq in grid:
+            grid += [(0, 0, 1, 0), (0, 0, 2, 0), (0, 0, 2, 1)]
+            grid += [(ks, 0, 0, 1) for ks in (1, 2, 4, 8)]
+        wps = None
+        for ks, dq, var, pre in grid:
             ops.set_qlinear_tuning(ks, dq)
+            ops.set_qlinear_variant(var)
+            key = f"tc_ks{ks}_v{var}" + ("_pre" if pre else "")
             try:
+                if pre and wps is None:
+                    wps = [(ops.qlinear_prepack(w, args.bits), s_, b_) for (w, s_, b_) in ws]
+                    back = ops.qlinear_prepack(wps[0][0], args.bits, inverse=True)
+                    assert torch.equal(back, ws[0][0]), "prepack round trip is not bit exact"
+                cur = wps if pre else ws
+
+                def run2(i, cur=cur, x=x, y=y, pre=pre):
+                    w, s_, b_ = cur[i]
+                    ops.quantized_matmul(x, w, s_, b_, group_size=args.group, bits=args.bits, out=y,
+                                         prepacked=bool(pre))
+
                 out = torch.empty_like(y)
-                ops.quantized_matmul(x, *ws[0], group_size=args.group, bits=args.bits, out=out)
+                ops.quantized_matmul(x, *cur[0], group_size=args.group, bits=args.bits, out=out, prepacked=bool(pre))
                 torch.cuda.synchronize()
                 err = (out.float() - ref.float()).abs().max().item()
                 scale = ref.float().abs().max().item()
-                t = time_us(run, copies)
-                rows[f"tc_ks{ks}_dq{dq}"] = {"us": t, "gbs": nbytes / t / 1e3, "frac": nbytes / t / 1e3 / PEAK,
-                                             "max_abs_diff_vs_mma": err, "ref_max": scale}
+                t = time_us(run2, copies)
+                rows[key] = {"us": t, "gbs": nbytes / t / 1e3, "frac": nbytes / t / 1e3 / PEAK,
+                             "max_abs_diff_vs_mma": err, "ref_max": scale}
             except Exception as e:  # noqa: BLE001
-                rows[f"tc_ks{ks}_dq{dq}"] = {"error": str(e)[:200]}
+                rows[key] = {"error": str(e)[:200]}
+        ops.set_qlinear_variant(0)
+        del wps
         ops.set_qlinear_tuning(0, 0)
         results["qgemm"][name] = {"N": n, "K": k, "bytes": nbytes, "roofline_us": nbytes / PEAK / 1e3, **rows}
         print(f"== {name} [{n} x {k}] int{args.bits} g{args.group} M={m}: {nbytes / 1e6:.1f} MB, "

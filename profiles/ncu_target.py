@@ -37,9 +37,12 @@ def main():
         x = torch.randn((m, k), device="cuda", generator=gen).bfloat16()
         y = torch.empty((m, n), device="cuda", dtype=torch.bfloat16)
         ops.set_qlinear_tuning(ks, dq)
+        pre = os.environ.get("PRE", "1") == "1"
+        if pre:
+            ws = [(ops.qlinear_prepack(w, 4), s, b) for (w, s, b) in ws]
         for _ in range(2):
             for w, s, b in ws:
-                ops.quantized_matmul(x, w, s, b, group_size=64, bits=4, out=y)
+                ops.quantized_matmul(x, w, s, b, group_size=64, bits=4, out=y, prepacked=pre)
         torch.cuda.synchronize()
         print("qgemm ok", name, float(y.float().abs().mean()))
     else:

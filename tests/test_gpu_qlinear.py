@@ -217,3 +217,70 @@ def test_silu_mul_argmax_add(ops):
     y0 = y.clone()
     ops.add_(y, x)
     assert torch.equal(y, (y0.float() + x.float()).bfloat16())
+
+
+@pytest.mark.parametrize("bits", [4, 8])
+def test_prepack_round_trip_bit_exact(ops, bits):
+    """b200_qlinear_prepack is a bijection on packed words (inverse restores the MLX layout)."""
+    g = torch.Generator(device="cuda").manual_seed(bits)
+    w = torch.randint(-2**31, 2**31 - 1, (257, 96), dtype=torch.int32, device="cuda", generator=g)
+    wp = ops.qlinear_prepack(w, bits)
+    assert wp.shape == w.shape
+    assert torch.equal(ops.qlinear_prepack(wp, bits, inverse=True), w)
+    if bits == 4:
+        # nibbles (i, i+4) of the streaming word hold elements (2i, 2i+1) of the MLX word
+        a, b = w.cpu().numpy().view(np.uint32), wp.cpu().numpy().view(np.uint32)
+        for i in range(4):
+            assert np.array_equal((b >> (4 * i)) & 0xF, (a >> (8 * i)) & 0xF)
+            assert np.array_equal((b >> (4 * i + 16)) & 0xF, (a >> (8 * i + 4)) & 0xF)
+    else:
+        assert torch.equal(wp, w)
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2])
+@pytest.mark.parametrize("m", [1, 16, 17, 64, 100, 300])
+@pytest.mark.parametrize("n,k,bits,group", [(320, 1024, 4, 64), (256, 4096, 4, 64), (128, 2880, 4, 32),
+                                           (1000, 2048, 4, 128), (384, 1536, 8, 64), (192, 4608, 8, 32)])
+def test_prepacked_matmul_vs_oracle(ops, variant, m, n, k, bits, group):
+    """Streaming layout + TMA-staged scales (variant 0/2) and per-thread scale loads (1): same
+    results as the MLX-layout call (bit for bit) and within tolerance of the oracle."""
+    ops.set_qlinear_variant(variant)
+    try:
+        wq, s, b, tw, ts, tb = _quantized(n, k, bits, group, seed=n + m)
+        x = round_to(np.random.default_rng(m).standard_normal((m, k)).astype(np.float32), "bfloat16")
+        tx = torch.from_numpy(x).bfloat16().cuda()
+        bias = round_to(np.random.default_rng(7).standard_normal(n).astype(np.float32), "bfloat16")
+        tbias = torch.from_numpy(bias).bfloat16().cuda()
+        wp = ops.qlinear_prepack(tw, bits)
+        got = ops.quantized_matmul(tx, wp, ts, tb, group_size=group, bits=bits, bias=tbias, prepacked=True)
+        ops.set_qlinear_kernel(2)
+        plain = ops.quantized_matmul(tx, tw, ts, tb, group_size=group, bits=bits, bias=tbias)
+        want = oq.quantized_matmul(x, wq, s, b, group, bits, bias=bias, dtype="bfloat16")
+        assert_close(got, want, "bfloat16", f"prepacked M={m} {n}x{k}")
+        assert torch.equal(got, plain), "streaming layout changed the result"
+    finally:
+        ops.set_qlinear_kernel(0)
+        ops.set_qlinear_variant(0)
+
+
+def test_prepacked_rejects_unsupported(ops):
+    """fp16 activations are not read by the tcgen05 kernel: loud error, no fallback."""
+    wq, s, b, tw, ts, tb = _quantized(128, 512, 4, 64, "float16", seed=3)
+    x = torch.randn((4, 512), device="cuda").half()
+    with pytest.raises(ValueError, match="streaming layout"):
+        ops.quantized_matmul(x, ops.qlinear_prepack(tw, 4), ts, tb, group_size=64, bits=4, prepacked=True)
+
+
+def test_quantized_linear_module_prepack(ops):
+    from vllm_metal_b200.quant.linear import QuantizedLinear
+
+    w = torch.randn((256, 512), device="cuda").bfloat16() * 0.02
+    lin = QuantizedLinear.from_dense(w, None, 64, 4, torch.bfloat16)
+    x = torch.randn((8, 512), device="cuda").bfloat16()
+    y0 = lin(x)
+    lin.prepack()
+    assert lin.weight_streaming.shape == lin.weight.shape
+    assert torch.equal(lin(x), y0)
+    lin2 = QuantizedLinear.from_dense(w, None, 64, 4, torch.bfloat16).prepack(keep_mlx_layout=False)
+    assert lin2.weight.shape[0] == 0 and torch.equal(lin2.mlx_weight(), lin.weight)
+    assert torch.equal(lin2(x), y0)

@@ -50,21 +50,24 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
 }
+// try_wait with a suspend-time hint: the hardware parks the thread until the phase completes or
+// the hint (ns) expires, so a waiting warp costs almost no issue slots.
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(bar), "r"(parity)
+      : "r"(bar), "r"(parity), "r"(20000u)
       : "memory");
   return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) __trap();  // a protocol bug must fault, not hang the box
+    if (++spins > (1u << 22)) __trap();  // a protocol bug must fault, not hang the box
   }
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
@@ -167,25 +170,35 @@ struct Cvt<__half> {
 };
 
 // 8 nibbles of one packed word -> 8 values s*q+b in memory order (k0..k7), as 4 packed pairs.
-template <typename T>
+// PRE: the word was nibble-permuted at load time (b200_qlinear_prepack) so that nibbles
+// (i, i+4) hold (k_{2i}, k_{2i+1}); the extraction then yields the pairs in memory order
+// and the four PRMTs disappear.
+template <typename T, bool PRE>
 __device__ __forceinline__ uint4 dequant_word4(uint32_t w, typename Cvt<T>::T2 s2,
                                                typename Cvt<T>::T2 b2) {
   using C = Cvt<T>;
   using T2 = typename C::T2;
   uint32_t a[4];
+  const uint32_t mask = 0x000F000Fu, magic = C::kMagic;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    // (k_i, k_{i+4}) as the low/high halves: lop3 (and, or) on the shifted word
-    uint32_t v = ((w >> (4 * i)) & 0x000F000Fu) | C::kMagic;
+    // (nibble i, nibble i+4) as the low/high halves: one LOP3 ((x & mask) | magic) on the
+    // shifted word (both constants live in registers so ptxas keeps it a single instruction)
+    uint32_t v;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(v) : "r"(w >> (4 * i)), "r"(mask), "r"(magic));
     T2 q = __hadd2(*reinterpret_cast<T2*>(&v), C::magic_off());  // exact: q in [0, 15]
     T2 r = __hfma2(s2, q, b2);                                    // s*q+b, one rounding
     a[i] = *reinterpret_cast<uint32_t*>(&r);
   }
   uint4 o;
-  o.x = __byte_perm(a[0], a[1], 0x5410);  // (k0, k1)
-  o.y = __byte_perm(a[2], a[3], 0x5410);  // (k2, k3)
-  o.z = __byte_perm(a[0], a[1], 0x7632);  // (k4, k5)
-  o.w = __byte_perm(a[2], a[3], 0x7632);  // (k6, k7)
+  if constexpr (PRE) {
+    o.x = a[0]; o.y = a[1]; o.z = a[2]; o.w = a[3];
+  } else {
+    o.x = __byte_perm(a[0], a[1], 0x5410);  // (k0, k1)
+    o.y = __byte_perm(a[2], a[3], 0x5410);  // (k2, k3)
+    o.z = __byte_perm(a[0], a[1], 0x7632);  // (k4, k5)
+    o.w = __byte_perm(a[2], a[3], 0x7632);  // (k6, k7)
+  }
   return o;
 }
 // 4 bytes of one packed word -> 4 values (fp32 fma, then one rounding to T).
@@ -209,9 +222,13 @@ struct Params {
   int kb_per_split;  // k blocks per cluster rank
 };
 
-template <int NB, int PS, int NS>
+constexpr int SB_STAGE_BYTES = 2 * ROWS * 16;  // 8 groups of scales + 8 of biases per row
+constexpr int SBS = 2;                         // scale/bias ring depth
+
+// The dynamic shared window is declared __align__(1024) (SWIZZLE_128B stage bases); no slack.
+template <int NB, int PS, int NS, bool SBT>
 constexpr int smem_bytes() {
-  return 1024 /*align slack*/ + PS * P_STAGE_BYTES + NS * (A_STAGE_BYTES + NB * 128) + 256;
+  return PS * P_STAGE_BYTES + NS * (A_STAGE_BYTES + NB * 128) + (SBT ? SBS * SB_STAGE_BYTES : 0) + 256;
 }
 
 __device__ __forceinline__ float4 ld_dsmem_v4(uint32_t local_addr, uint32_t peer) {
@@ -253,10 +270,12 @@ __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[CW]) {
 }
 
 // T: activation / scale type; BITS: 4|8; G: quantisation group; NB: batch tile (UMMA N);
-// PS/NS: ring depths.
-template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW>
+// PS/NS: ring depths; SBT: scales/biases staged by TMA (8 groups per stage) instead of per-thread
+// global loads; PRE: packed words are in the prepacked nibble order (see dequant_word4).
+template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW, bool SBT, bool PRE>
 __global__ void __launch_bounds__((DQW + 3) * 32, NB <= 64 ? 2 : 1)
 qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
+                const __grid_constant__ CUtensorMap s_map, const __grid_constant__ CUtensorMap b_map,
                 const Params p) {
   using C = Cvt<T>;
   using T2 = typename C::T2;
@@ -269,21 +288,28 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   constexpr int TPR = DQW / 4;                // dequant threads per weight row: 1 | 2
   constexpr int CH_T = CH_PER_KB / TPR;       // packed chunks per thread per k block
   constexpr int W_TMA = DQW, W_X = DQW + 1, W_MMA = DQW + 2;
+  constexpr int SB_PER = SBT ? (8 * G) / KPP : 1;  // packed stages per scale/bias stage
   static_assert(DQW == 4 || DQW == 8, "4 or 8 dequant warps");
   static_assert(CH_PER_KB % TPR == 0, "chunks must split evenly over the row's threads");
+  static_assert(!SBT || (8 * G) % KPP == 0, "a scale/bias stage must cover whole packed stages");
 
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);
+  if ((base & 1023u) != 0) __trap();  // SWIZZLE_128B stages need 1 KiB alignment: fail loudly
   const uint32_t sm_p = base;
   const uint32_t sm_a = sm_p + PS * P_STAGE_BYTES;
   const uint32_t sm_b = sm_a + NS * A_STAGE_BYTES;
-  const uint32_t sm_bar = sm_b + NS * B_STAGE_BYTES;
-  // barriers (8 B each): full_p[PS], empty_p[PS], full_ab[NS], empty_ab[NS], tmem_full; then tmem ptr
+  const uint32_t sm_sb = sm_b + NS * B_STAGE_BYTES;
+  const uint32_t sm_bar = sm_sb + (SBT ? SBS * SB_STAGE_BYTES : 0);
+  // barriers (8 B each): full_p[PS], empty_p[PS], full_ab[NS], empty_ab[NS], tmem_full,
+  // full_sb[SBS], empty_sb[SBS]; then the tmem pointer
   const uint32_t bar_full_p = sm_bar, bar_empty_p = sm_bar + 8 * PS;
   const uint32_t bar_full_ab = sm_bar + 16 * PS, bar_empty_ab = bar_full_ab + 8 * NS;
   const uint32_t bar_tmem_full = bar_empty_ab + 8 * NS;
-  const uint32_t tmem_ptr_addr = bar_tmem_full + 8;
-  uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t bar_full_sb = bar_tmem_full + 8, bar_empty_sb = bar_full_sb + 8 * SBS;
+  const uint32_t tmem_ptr_addr = bar_empty_sb + 8 * SBS;
+  static_assert(8 * (2 * PS + 2 * NS + 1 + 2 * SBS) + 4 <= 256, "barrier block overflows its 256 bytes");
+  uint8_t* gen_base = smem_raw;
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_ptr_addr - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -296,6 +322,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   if (my_kb > p.kb_per_split) my_kb = p.kb_per_split;
   if (my_kb < 0) my_kb = 0;
   const int my_ps = (my_kb + KB_PER_P - 1) / KB_PER_P;
+  const int gps0 = kb_begin / KB_PER_P;  // global index of this rank's first packed stage
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < PS; ++i) {
@@ -307,6 +334,10 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
       mbar_init(bar_empty_ab + 8 * i, 1);
     }
     mbar_init(bar_tmem_full, 1);
+    for (int i = 0; i < SBS; ++i) {
+      mbar_init(bar_full_sb + 8 * i, 1);
+      mbar_init(bar_empty_sb + 8 * i, DQW);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == W_MMA) {
@@ -325,6 +356,19 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
     if (lane == 0) {
       for (int ps = 0; ps < my_ps; ++ps) {
         const int st = ps % PS;
+        if constexpr (SBT) {
+          // scale/bias stages sit on the GLOBAL grid of 8 groups (TMA needs the inner start
+          // coordinate 16-byte aligned); a cluster rank may start in the middle of one
+          const int gps = gps0 + ps;
+          if (ps == 0 || gps % SB_PER == 0) {
+            const int sbi = gps / SB_PER - gps0 / SB_PER, sst = sbi % SBS;
+            mbar_wait(bar_empty_sb + 8 * sst, ((sbi / SBS) & 1) ^ 1);
+            mbar_expect_tx(bar_full_sb + 8 * sst, SB_STAGE_BYTES);
+            const int g0 = (gps / SB_PER) * 8;
+            tma_load_2d(sm_sb + sst * SB_STAGE_BYTES, &s_map, bar_full_sb + 8 * sst, g0, n0);
+            tma_load_2d(sm_sb + sst * SB_STAGE_BYTES + ROWS * 16, &b_map, bar_full_sb + 8 * sst, g0, n0);
+          }
+        }
         mbar_wait(bar_empty_p + 8 * st, ((ps / PS) & 1) ^ 1);
         mbar_expect_tx(bar_full_p + 8 * st, P_STAGE_BYTES);
         tma_load_2d(sm_p + st * P_STAGE_BYTES, &w_map, bar_full_p + 8 * st,
@@ -412,9 +456,39 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
         b_nxt[i] = ok ? __ldg(brow + g0 + i) : (uint16_t)0;
       }
     };
-    if (my_ps > 0) load_sb(0);
+    // SBT: this packed stage's GPP scales and biases sit in the TMA-staged ring, 16 B per row
+    auto load_sb_smem = [&](int ps) {
+      const int gps = gps0 + ps;
+      const int sbi = gps / SB_PER - gps0 / SB_PER, sst = sbi % SBS;
+      if (ps == 0 || gps % SB_PER == 0) mbar_wait(bar_full_sb + 8 * sst, (sbi / SBS) & 1);
+      const uint32_t sa = sm_sb + sst * SB_STAGE_BYTES + r * 16 + (gps % SB_PER) * (GPP * 2);
+      const uint32_t ba = sa + ROWS * 16;
+      uint32_t sw[4] = {0, 0, 0, 0}, bw[4] = {0, 0, 0, 0};
+      if constexpr (GPP == 8) {
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(sw[0]), "=r"(sw[1]), "=r"(sw[2]), "=r"(sw[3]) : "r"(sa));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(bw[0]), "=r"(bw[1]), "=r"(bw[2]), "=r"(bw[3]) : "r"(ba));
+      } else if constexpr (GPP == 4) {
+        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(sw[0]), "=r"(sw[1]) : "r"(sa));
+        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(bw[0]), "=r"(bw[1]) : "r"(ba));
+      } else if constexpr (GPP == 2) {
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sw[0]) : "r"(sa));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(bw[0]) : "r"(ba));
+      } else {
+        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(sw[0]) : "r"(sa));
+        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(bw[0]) : "r"(ba));
+      }
+#pragma unroll
+      for (int i = 0; i < GPP; ++i) {
+        s_nxt[i] = (uint16_t)((sw[i >> 1] >> (16 * (i & 1))) & 0xFFFFu);
+        b_nxt[i] = (uint16_t)((bw[i >> 1] >> (16 * (i & 1))) & 0xFFFFu);
+      }
+    };
+    if constexpr (!SBT) {
+      if (my_ps > 0) load_sb(0);
+    }
     for (int ps = 0; ps < my_ps; ++ps) {
       const int pst = ps % PS;
+      if constexpr (SBT) load_sb_smem(ps);
       // this stage's scales/biases, broadcast once; then prefetch the next stage's
       // (G == 32 with two threads per row: a thread only ever touches group 2j + hsel of k block j)
       constexpr bool SEL = (G < KB) && (TPR == 2);
@@ -440,7 +514,16 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
         }
       }
       (void)s2; (void)b2; (void)sf; (void)bf;
-      if (ps + 1 < my_ps) load_sb(ps + 1);
+      if constexpr (SBT) {
+        // values are in registers now: hand the scale/bias stage back after its last packed stage
+        const int gps = gps0 + ps;
+        if (gps % SB_PER == SB_PER - 1 || ps == my_ps - 1) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_empty_sb + 8 * ((gps / SB_PER - gps0 / SB_PER) % SBS));
+        }
+      } else {
+        if (ps + 1 < my_ps) load_sb(ps + 1);
+      }
       mbar_wait(bar_full_p + 8 * pst, (ps / PS) & 1);
       const uint32_t prow = sm_p + pst * P_STAGE_BYTES + r * 128;
 #pragma unroll
@@ -479,7 +562,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
               }
               uint4 o[4];
 #pragma unroll
-              for (int wi = 0; wi < 4; ++wi) o[wi] = dequant_word4<T>(words[wi], sg, bg);
+              for (int wi = 0; wi < 4; ++wi) o[wi] = dequant_word4<T, PRE>(words[wi], sg, bg);
 #pragma unroll
               for (int wi = 0; wi < 4; ++wi) {
                 const uint32_t chunk = (uint32_t)(c * 4 + wi);  // 8 elements = 16 B of the A row
@@ -657,7 +740,7 @@ static EncodeTiledFn encode_fn() {
 
 static int make_map_2d(CUtensorMap* map, CUtensorMapDataType dt, const void* ptr, uint64_t inner,
                        uint64_t outer, uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer,
-                       CUtensorMapL2promotion promo) {
+                       CUtensorMapL2promotion promo, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return set_error(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
   cuuint64_t dims[2] = {inner, outer};
@@ -665,7 +748,7 @@ static int make_map_2d(CUtensorMap* map, CUtensorMapDataType dt, const void* ptr
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult rc = fn(map, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   swz, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (rc != CUDA_SUCCESS)
     return set_error(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)rc);
   return B200_OK;
@@ -680,19 +763,26 @@ struct HostArgs {
   void* y;
   int M, N, K, group_size, bits, dtype;
   int64_t x_stride, y_stride;
+  bool prepacked;
 };
 
-template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW>
+// Scales/biases can be staged by TMA when their rows are 16-byte multiples and 16-byte aligned.
+static bool sb_tma_ok(const HostArgs& a) {
+  const int64_t row_bytes = (int64_t)(a.K / a.group_size) * 2;
+  return row_bytes % 16 == 0 && (uintptr_t)a.scales % 16 == 0 && (uintptr_t)a.biases % 16 == 0;
+}
+
+template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW, bool SBT = false, bool PRE = false>
 static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
-  constexpr int smem = smem_bytes<NB, PS, NS>();
-  auto kern = qgemm_tc_kernel<T, BITS, G, NB, PS, NS, DQW>;
+  constexpr int smem = smem_bytes<NB, PS, NS, SBT>();
+  auto kern = qgemm_tc_kernel<T, BITS, G, NB, PS, NS, DQW, SBT, PRE>;
   constexpr int KB_PER_P = (1024 / BITS) / KB;
   static bool configured = false;
   if (!configured) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  CUtensorMap w_map, x_map;
+  CUtensorMap w_map, x_map, s_map, b_map;
   const uint64_t words = (uint64_t)a.K * BITS / 32;
   int rc = make_map_2d(&w_map, CU_TENSOR_MAP_DATA_TYPE_UINT32, a.w, words, (uint64_t)a.N, words * 4, 32, ROWS,
                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
@@ -701,6 +791,18 @@ static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
                    a.x, (uint64_t)a.K, (uint64_t)a.M, (uint64_t)a.x_stride * 2, KB, NB,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
   if (rc != B200_OK) return rc;
+  if constexpr (SBT) {
+    const uint64_t groups = (uint64_t)(a.K / a.group_size);
+    rc = make_map_2d(&s_map, CU_TENSOR_MAP_DATA_TYPE_UINT16, a.scales, groups, (uint64_t)a.N, groups * 2, 8, ROWS,
+                     CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc != B200_OK) return rc;
+    rc = make_map_2d(&b_map, CU_TENSOR_MAP_DATA_TYPE_UINT16, a.biases, groups, (uint64_t)a.N, groups * 2, 8, ROWS,
+                     CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc != B200_OK) return rc;
+  } else {
+    s_map = w_map;
+    b_map = w_map;
+  }
   Params p;
   p.scales = reinterpret_cast<const uint16_t*>(a.scales);
   p.biases = reinterpret_cast<const uint16_t*>(a.biases);
@@ -726,13 +828,29 @@ static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, w_map, x_map, p));
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, w_map, x_map, s_map, b_map, p));
   return B200_OK;
 }
 
 // Tuning knobs (b200_set_qlinear_tuning): 0 = heuristic.
 static int g_force_ksplit = 0;
 static int g_force_dqw = 0;
+static int g_variant = 0;  // b200_set_qlinear_variant: 0 = default, 1 = legacy (LDG scales, PS3/NS2)
+
+// M <= 64 weight-streaming configurations: NB batch tile, (PS, NS) ring depths.
+template <typename T, int BITS, int G, int NB, bool PRE>
+static int launch_stream(const HostArgs& a, int ksplit, cudaStream_t st) {
+  constexpr bool kSbtShape = (8 * G) % (1024 / BITS) == 0 && (8 * G) / (1024 / BITS) <= 4;
+  const bool dq8 = g_force_dqw ? g_force_dqw == 8 : true;
+  if constexpr (kSbtShape) {
+    if (g_variant != 1 && sb_tma_ok(a)) {
+      if (g_variant == 2) return launch_cfg<T, BITS, G, NB, 3, 2, 8, true, PRE>(a, ksplit, st);
+      return launch_cfg<T, BITS, G, NB, 2, 3, 8, true, PRE>(a, ksplit, st);
+    }
+  }
+  return dq8 ? launch_cfg<T, BITS, G, NB, 3, 2, 8, false, PRE>(a, ksplit, st)
+             : launch_cfg<T, BITS, G, NB, 3, 2, 4, false, PRE>(a, ksplit, st);
+}
 
 template <typename T, int BITS, int G>
 static int dispatch_g(const HostArgs& a, cudaStream_t st) {
@@ -744,15 +862,20 @@ static int dispatch_g(const HostArgs& a, cudaStream_t st) {
     // K over a cluster until every SM has CTAs streaming, keeping >= 2 packed stages per rank.
     const int sms = sm_count() > 0 ? sm_count() : 148;
     int ksplit = 1;
-    while (ksplit < 8 && tiles * ksplit < 2 * sms && num_kb / (ksplit * 2) >= 2 * KB_PER_P) ksplit *= 2;
+    // (tiles >= sms: every SM already streams; measured best unsplit -- profiles/r01_kernels_v3_sweep.txt)
+    while (tiles < sms && ksplit < 8 && tiles * ksplit < 2 * sms && num_kb / (ksplit * 2) >= 2 * KB_PER_P)
+      ksplit *= 2;
     if (g_force_ksplit > 0) ksplit = g_force_ksplit;
     while (ksplit > 1 && num_kb / ksplit < KB_PER_P) ksplit /= 2;
-    const bool dq8 = g_force_dqw ? g_force_dqw == 8 : true;
     if (a.M <= 16)
-      return dq8 ? launch_cfg<T, BITS, G, 16, 3, 2, 8>(a, ksplit, st)
-                 : launch_cfg<T, BITS, G, 16, 3, 2, 4>(a, ksplit, st);
-    return dq8 ? launch_cfg<T, BITS, G, 64, 3, 2, 8>(a, ksplit, st)
-               : launch_cfg<T, BITS, G, 64, 3, 2, 4>(a, ksplit, st);
+      return a.prepacked ? launch_stream<T, BITS, G, 16, BITS == 4>(a, ksplit, st)
+                         : launch_stream<T, BITS, G, 16, false>(a, ksplit, st);
+    return a.prepacked ? launch_stream<T, BITS, G, 64, BITS == 4>(a, ksplit, st)
+                       : launch_stream<T, BITS, G, 64, false>(a, ksplit, st);
+  }
+  if (a.prepacked && BITS == 4) {
+    if (a.M <= 128) return launch_cfg<T, BITS, G, 128, 3, 3, 8, false, BITS == 4>(a, 1, st);
+    return launch_cfg<T, BITS, G, 256, 2, 3, 8, false, BITS == 4>(a, 1, st);
   }
   if (a.M <= 128) return launch_cfg<T, BITS, G, 128, 3, 3, 8>(a, 1, st);
   return launch_cfg<T, BITS, G, 256, 2, 3, 8>(a, 1, st);
@@ -794,10 +917,16 @@ int qgemm_tc_set_tuning(int ksplit, int dequant_warps) {
   return B200_OK;
 }
 
+int qgemm_tc_set_variant(int v) {
+  if (v < 0 || v > 2) return set_error(B200_ERR_INVALID_ARGUMENT, "qlinear variant must be 0, 1 or 2, got %d", v);
+  qtc::g_variant = v;
+  return B200_OK;
+}
+
 int qgemm_tc_launch(const void* x, const uint32_t* w, const void* scales, const void* biases,
                     const void* bias, void* y, int M, int N, int K, int group_size, int bits, int dtype,
-                    int64_t x_stride, int64_t y_stride, cudaStream_t st) {
-  qtc::HostArgs a{x, w, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride, y_stride};
+                    int64_t x_stride, int64_t y_stride, bool prepacked, cudaStream_t st) {
+  qtc::HostArgs a{x, w, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride, y_stride, prepacked};
   return bits == 4 ? qtc::dispatch<__nv_bfloat16, 4>(a, st) : qtc::dispatch<__nv_bfloat16, 8>(a, st);
 }
 

@@ -20,7 +20,8 @@ bool qgemm_tc_supported(const void* x, const uint32_t* w, int M, int N, int K, i
                         int dtype, int sb_dtype, int64_t x_stride);
 int qgemm_tc_launch(const void* x, const uint32_t* w, const void* scales, const void* biases,
                     const void* bias, void* y, int M, int N, int K, int group_size, int bits, int dtype,
-                    int64_t x_stride, int64_t y_stride, cudaStream_t st);
+                    int64_t x_stride, int64_t y_stride, bool prepacked, cudaStream_t st);
+int qgemm_tc_set_variant(int v);
 
 int qgemm_tc_set_tuning(int ksplit, int dequant_warps);
 
@@ -366,7 +367,7 @@ extern "C" int b200_qlinear(const void* x, const uint32_t* w, const void* scales
     const bool ok = y_stride >= N &&
                     qgemm_tc_supported(x, w, M, N, K, group_size, bits, dtype, sb_dtype, x_stride);
     if (ok) return qgemm_tc_launch(x, w, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride,
-                                   y_stride, st0);
+                                   y_stride, false, st0);
     if (g_qlinear_kernel == 2)
       return set_error(B200_ERR_UNSUPPORTED,
                        "qlinear: tcgen05 kernel does not take dtype=%d sb_dtype=%d K=%d x_stride=%lld",
@@ -383,6 +384,74 @@ extern "C" int b200_qlinear(const void* x, const uint32_t* w, const void* scales
                      : ql::dispatch_tile<__nv_bfloat16, 8>(p, st);
   return bits == 4 ? ql::dispatch_tile<__half, 4>(p, st) : ql::dispatch_tile<__half, 8>(p, st);
 }
+
+// Streaming ("prepacked") weight layout: same shape as the MLX layout, nibbles permuted inside
+// every 32-bit word so that nibbles (i, i+4) hold elements (2i, 2i+1) of the word's 8 elements.
+// The tcgen05 kernel's (x >> 4i) & 0x000F000F extraction then yields adjacent-k pairs directly.
+namespace b200 {
+namespace ql {
+__global__ void prepack_int4_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int64_t n,
+                                    int inverse) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t w = in[i];
+    uint32_t o = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (!inverse) {
+        o |= ((w >> (8 * j)) & 0xFu) << (4 * j);             // element 2j   -> nibble j
+        o |= ((w >> (8 * j + 4)) & 0xFu) << (4 * j + 16);    // element 2j+1 -> nibble j+4
+      } else {
+        o |= ((w >> (4 * j)) & 0xFu) << (8 * j);
+        o |= ((w >> (4 * j + 16)) & 0xFu) << (8 * j + 4);
+      }
+    }
+    out[i] = o;
+  }
+}
+}  // namespace ql
+}  // namespace b200
+
+extern "C" int b200_qlinear_prepack(const uint32_t* w, uint32_t* out, int N, int K, int bits, int inverse,
+                                    void* stream) {
+  using namespace b200;
+  B200_CHECK_ARG(w && out, "qlinear_prepack: null pointer argument");
+  B200_CHECK_ARG(bits == 4 || bits == 8, "qlinear_prepack: bits must be 4 or 8, got %d", bits);
+  B200_CHECK_ARG(N > 0 && K > 0 && (K * bits) % 32 == 0, "qlinear_prepack: bad shape N=%d K=%d", N, K);
+  const int64_t words = (int64_t)N * ((int64_t)K * bits / 32);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (bits == 8) {  // int8 streams in the MLX order already
+    if (w != out) B200_CUDA_OK(cudaMemcpyAsync(out, w, words * 4, cudaMemcpyDeviceToDevice, st));
+    return B200_OK;
+  }
+  const int threads = 256;
+  const int64_t want = (words + threads - 1) / threads;
+  const int blocks = (int)(want < 148 * 16 ? want : 148 * 16);
+  ql::prepack_int4_kernel<<<blocks, threads, 0, st>>>(w, out, words, inverse);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+extern "C" int b200_qlinear_prepacked(const void* x, const uint32_t* wp, const void* scales,
+                                      const void* biases, const void* bias, void* y, int M, int N, int K,
+                                      int group_size, int bits, int dtype, int sb_dtype, int64_t x_stride,
+                                      int64_t y_stride, void* stream) {
+  using namespace b200;
+  int rc = check_quant_args("qlinear_prepacked", N, K, group_size, bits, sb_dtype);
+  if (rc != B200_OK) return rc;
+  B200_CHECK_ARG(M >= 0, "qlinear_prepacked: M must be >= 0, got %d", M);
+  if (M == 0) return B200_OK;
+  B200_CHECK_ARG(x && wp && scales && biases && y, "qlinear_prepacked: null pointer argument");
+  B200_CHECK_ARG(y_stride >= N, "qlinear_prepacked: y_stride (%lld) < N (%d)", (long long)y_stride, N);
+  if (!qgemm_tc_supported(x, wp, M, N, K, group_size, bits, dtype, sb_dtype, x_stride))
+    return set_error(B200_ERR_UNSUPPORTED,
+                     "qlinear_prepacked: the streaming layout is only read by the tcgen05 kernel, which does not "
+                     "take dtype=%d sb_dtype=%d K=%d x_stride=%lld",
+                     dtype, sb_dtype, K, (long long)x_stride);
+  return qgemm_tc_launch(x, wp, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride, y_stride,
+                         true, (cudaStream_t)stream);
+}
+
+extern "C" int b200_set_qlinear_variant(int variant) { return b200::qgemm_tc_set_variant(variant); }
 
 extern "C" int b200_set_qlinear_kernel(int kernel) {
   if (kernel < 0 || kernel > 2)

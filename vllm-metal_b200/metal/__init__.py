@@ -91,6 +91,9 @@ EXPORTED_SYMBOLS = (
     "b200_paged_attention_workspace_bytes",
     "b200_paged_attention",
     "b200_qlinear",
+    "b200_qlinear_prepack",
+    "b200_qlinear_prepacked",
+    "b200_set_qlinear_variant",
     "b200_set_qlinear_kernel",
     "b200_set_qlinear_tuning",
     "b200_dequantize_rows",
@@ -140,6 +143,8 @@ def load_library() -> ctypes.CDLL:
     lib.b200_reshape_and_cache.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i32, vp]
     lib.b200_copy_blocks.argtypes = [vp, vp, vp, vp, i32, i64, i64, vp]
     lib.b200_qlinear.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i64, i64, vp]
+    lib.b200_qlinear_prepacked.argtypes = lib.b200_qlinear.argtypes
+    lib.b200_qlinear_prepack.argtypes = [vp, vp, i32, i32, i32, i32, vp]
     lib.b200_dequantize_rows.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
     lib.b200_rms_norm.argtypes = [vp, vp, vp, vp, i32, i32, i64, i64, i64, f32, i32, vp]
     lib.b200_rope.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i64, i64, i32, vp]
@@ -386,8 +391,10 @@ class _Ops:
 
     # -- MLX-affine quantized linears (mlx_native.py:212-239) -------------------
     def quantized_matmul(self, x, w, scales, biases, transpose: bool = True, group_size: int = 64,
-                         bits: int = 4, bias=None, out=None):
-        """``mx.quantized_matmul(x, w, scales, biases, transpose=True, group_size, bits)``."""
+                         bits: int = 4, bias=None, out=None, prepacked: bool = False):
+        """``mx.quantized_matmul(x, w, scales, biases, transpose=True, group_size, bits)``.
+
+        ``prepacked=True``: ``w`` is in the streaming layout made by ``qlinear_prepack``."""
         if not transpose:
             raise NotImplementedError("only transpose=True (x @ W.T) is on the hot path")
         for n, t in (("x", x), ("w", w), ("scales", scales), ("biases", biases)):
@@ -412,13 +419,32 @@ class _Ops:
         y2 = out.reshape(m, n_out)
         if bias is not None:
             bias = bias.to(dtype=x.dtype).contiguous()
-        rc = self._lib.b200_qlinear(
+        fn = self._lib.b200_qlinear_prepacked if prepacked else self._lib.b200_qlinear
+        rc = fn(
             x2.data_ptr(), w.contiguous().data_ptr(), scales.contiguous().data_ptr(),
             biases.contiguous().data_ptr(), _ptr(bias), y2.data_ptr(), m, n_out, k, group_size, bits,
             _dtype_code("x", x), _dtype_code("scales", scales), x2.stride(0), y2.stride(0), _stream())
         self._check(rc)
         self.launches += 1
         return out.reshape(*lead, n_out)
+
+    def qlinear_prepack(self, w, bits: int = 4, inverse: bool = False, out=None):
+        """Load-time repack of an MLX-layout packed weight into the streaming layout (same shape)."""
+        _require_cuda("w", w)
+        if w.dtype not in (torch.uint32, torch.int32) or w.dim() != 2:
+            raise ValueError("w must be uint32 [N, K*bits/32]")
+        w = w.contiguous()
+        if out is None:
+            out = torch.empty_like(w)
+        n_out, words = w.shape
+        self._check(self._lib.b200_qlinear_prepack(w.data_ptr(), out.data_ptr(), n_out, words * 32 // bits, bits,
+                                                   int(bool(inverse)), _stream()))
+        self.launches += 1
+        return out
+
+    def set_qlinear_variant(self, variant: int = 0) -> None:
+        """Ring configuration of the M <= 64 regime (sweep knob, see the header)."""
+        self._check(self._lib.b200_set_qlinear_variant(int(variant)))
 
     def set_qlinear_kernel(self, kernel: int) -> None:
         """0 = auto, 1 = mma.sync kernel, 2 = tcgen05 kernel (raises if the shape does not qualify)."""

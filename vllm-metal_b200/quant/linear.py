@@ -89,8 +89,30 @@ class QuantizedLinear(nn.Module):
             m.bias.copy_(self.bias)
         return m
 
+    def prepack(self, keep_mlx_layout: bool = True) -> QuantizedLinear:
+        """Load-time transform into the kernel's streaming layout (``b200_qlinear_prepack``).
+        ``weight`` keeps the MLX layout for loaders / LoRA introspection unless
+        ``keep_mlx_layout=False`` (then it is rebuilt on demand by ``mlx_weight()``)."""
+        if self.scales.dtype != torch.bfloat16 or self.in_features % 64:
+            return self  # the streaming layout is only read by the bf16 tcgen05 kernel
+        wp = get_ops().qlinear_prepack(self.weight, self.bits)
+        self.register_buffer("weight_streaming", wp, persistent=False)
+        if not keep_mlx_layout:
+            self.weight = torch.empty((0, self.weight.shape[1]), dtype=torch.int32, device=wp.device)
+        return self
+
+    def mlx_weight(self) -> torch.Tensor:
+        if self.weight.shape[0] or getattr(self, "weight_streaming", None) is None:
+            return self.weight
+        return get_ops().qlinear_prepack(self.weight_streaming, self.bits, inverse=True)
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return get_ops().quantized_matmul(x, self.weight, self.scales, self.biases, transpose=True,
+        wp = getattr(self, "weight_streaming", None)
+        if wp is not None and x.dtype == torch.bfloat16:
+            return get_ops().quantized_matmul(x, wp, self.scales, self.biases, transpose=True,
+                                              group_size=self.group_size, bits=self.bits, bias=self.bias,
+                                              prepacked=True)
+        return get_ops().quantized_matmul(x, self.mlx_weight(), self.scales, self.biases, transpose=True,
                                           group_size=self.group_size, bits=self.bits, bias=self.bias)
 
 
