@@ -367,7 +367,7 @@ def run_b200(args) -> None:
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0,
                          "traffic": None, "bytes_per_launch": alg_bytes, "us_per_launch": attn_ms * 1e3},
-            "roofline_qgemv": {"bound": "hbm", "kernel": "qgemm_mma_kernel (gate_up 28672x4096 int4 g64, M=64)",
+            "roofline_qgemv": {"bound": "hbm", "kernel": "qgemm_tc_kernel, A tile in TMEM (gate_up 28672x4096 int4 g64, M=64)",
                                "achieved": gemv_gbs, "peak": peak, "unit": "GB/s", "frac": gemv_gbs / peak,
                                "bytes_per_launch": gemv_bytes, "us_per_launch": gemv_ms * 1e3},
             "cpu_baseline": cpu,

@@ -188,9 +188,10 @@ int b200_set_qlinear_kernel(int kernel);
  * 1, 2, 4 or 8), `dequant_warps` = 0 (default), 4 or 8.  Process-wide; returns 0 on success. */
 int b200_set_qlinear_tuning(int ksplit, int dequant_warps);
 
-/* Ring-configuration knob of the M <= 64 regime for the sweep (0 = default: TMA-staged
- * scales/biases, packed ring 2 / operand ring 3; 1 = per-thread scale loads, rings 3/2;
- * 2 = TMA-staged scales, rings 3/2).  Process-wide. */
+/* Kernel-variant knob of the M <= 64 regime for the sweep.  0 = default: dequantised A tile in
+ * TENSOR MEMORY (tcgen05.st / TS-form MMA), TMA-staged scales/biases, packed ring 4 / operand
+ * ring 4; 1 = A tile in shared memory, per-thread scale loads, rings 3/2; 2 = A tile in shared
+ * memory, TMA-staged scales, rings 2/3.  Process-wide. */
 int b200_set_qlinear_variant(int variant);
 
 /* Load-time repack into the streaming layout read by b200_qlinear_prepacked: same shape as

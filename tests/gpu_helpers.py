@@ -91,7 +91,8 @@ def oracle_from_model(model, num_blocks, block_size):
     from oracle.decoder import OracleDecoder, QWeight
 
     def qw(m):
-        return QWeight(m.weight.cpu().numpy().view(np.uint32), to_np(m.scales), to_np(m.biases),
+        w = m.mlx_weight() if hasattr(m, "mlx_weight") else m.weight  # MLX layout (undo the load-time prepack)
+        return QWeight(w.cpu().numpy().view(np.uint32), to_np(m.scales), to_np(m.biases),
                        m.group_size, m.bits)
 
     a = model.args

@@ -99,6 +99,26 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uin
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// A operand from TMEM (row m <-> lane m, two K-adjacent 16-bit elements per 32-bit column).
+__device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
+                                              uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// registers -> TMEM: 16 consecutive 32-bit columns of this thread's lane.
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+        "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
@@ -226,9 +246,9 @@ constexpr int SB_STAGE_BYTES = 2 * ROWS * 16;  // 8 groups of scales + 8 of bias
 constexpr int SBS = 2;                         // scale/bias ring depth
 
 // The dynamic shared window is declared __align__(1024) (SWIZZLE_128B stage bases); no slack.
-template <int NB, int PS, int NS, bool SBT>
+template <int NB, int PS, int NS, bool SBT, bool TA>
 constexpr int smem_bytes() {
-  return PS * P_STAGE_BYTES + NS * (A_STAGE_BYTES + NB * 128) + (SBT ? SBS * SB_STAGE_BYTES : 0) + 256;
+  return PS * P_STAGE_BYTES + NS * ((TA ? 0 : A_STAGE_BYTES) + NB * 128) + (SBT ? SBS * SB_STAGE_BYTES : 0) + 256;
 }
 
 __device__ __forceinline__ float4 ld_dsmem_v4(uint32_t local_addr, uint32_t peer) {
@@ -272,7 +292,9 @@ __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[CW]) {
 // T: activation / scale type; BITS: 4|8; G: quantisation group; NB: batch tile (UMMA N);
 // PS/NS: ring depths; SBT: scales/biases staged by TMA (8 groups per stage) instead of per-thread
 // global loads; PRE: packed words are in the prepacked nibble order (see dequant_word4).
-template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW, bool SBT, bool PRE>
+// TA: the dequantised A tile goes to TENSOR MEMORY (tcgen05.st, one lane per weight row) and the MMA
+// reads it from there -- no shared-memory A ring, no swizzle, no generic->async proxy fence.
+template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW, bool SBT, bool PRE, bool TA>
 __global__ void __launch_bounds__((DQW + 3) * 32, NB <= 64 ? 2 : 1)
 qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
                 const __grid_constant__ CUtensorMap s_map, const __grid_constant__ CUtensorMap b_map,
@@ -283,7 +305,13 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   constexpr int KB_PER_P = KPP / KB;      // 4 | 2
   constexpr int CH_PER_KB = KB * BITS / 128;  // 16-byte packed chunks per k block: 2 | 4
   constexpr int B_STAGE_BYTES = NB * 128;
-  constexpr int TMEM_COLS = NB < 32 ? 32 : NB;
+  constexpr int ACC_COLS = NB < 32 ? 32 : NB;
+  constexpr int A_COLS = KB / 2;  // 32-bit TMEM columns of one 64-wide k block of 16-bit values
+  constexpr int TMEM_NEED = ACC_COLS + (TA ? NS * A_COLS : 0);
+  constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128
+                            : TMEM_NEED <= 256 ? 256 : 512;
+  static_assert(TMEM_NEED <= 512, "accumulator + A ring exceed tensor memory");
+  static_assert(!TA || (DQW == 8 && (NB > 64 || TMEM_COLS <= 256)), "TA: 8 dequant warps, two CTAs must fit TMEM");
   constexpr int GPP = KPP / G;  // groups per packed stage (>= 1)
   constexpr int TPR = DQW / 4;                // dequant threads per weight row: 1 | 2
   constexpr int CH_T = CH_PER_KB / TPR;       // packed chunks per thread per k block
@@ -298,7 +326,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   if ((base & 1023u) != 0) __trap();  // SWIZZLE_128B stages need 1 KiB alignment: fail loudly
   const uint32_t sm_p = base;
   const uint32_t sm_a = sm_p + PS * P_STAGE_BYTES;
-  const uint32_t sm_b = sm_a + NS * A_STAGE_BYTES;
+  const uint32_t sm_b = sm_a + (TA ? 0 : NS * A_STAGE_BYTES);
   const uint32_t sm_sb = sm_b + NS * B_STAGE_BYTES;
   const uint32_t sm_bar = sm_sb + (SBT ? SBS * SB_STAGE_BYTES : 0);
   // barriers (8 B each): full_p[PS], empty_p[PS], full_ab[NS], empty_ab[NS], tmem_full,
@@ -395,11 +423,18 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
         const int st = kb % NS;
         mbar_wait(bar_full_ab + 8 * st, (kb / NS) & 1);
         tc_fence_after();
-        const uint64_t da = make_smem_desc(sm_a + st * A_STAGE_BYTES);
         const uint64_t db = make_smem_desc(sm_b + st * B_STAGE_BYTES);
+        if constexpr (TA) {
+          const uint32_t ta = tmem_base + ACC_COLS + st * A_COLS;
 #pragma unroll
-        for (int k = 0; k < KB / 16; ++k)  // +32 B (16 elements) inside the 128 B swizzle row
-          tc_mma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < KB / 16; ++k)  // 16 elements = 8 TMEM columns of A, 32 B of the B row
+            tc_mma_f16_ts(tmem_base, ta + 8 * k, db + 2 * k, idesc, (kb | k) != 0);
+        } else {
+          const uint64_t da = make_smem_desc(sm_a + st * A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < KB / 16; ++k)  // +32 B (16 elements) inside the 128 B swizzle row
+            tc_mma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+        }
         tc_commit(bar_empty_ab + 8 * st);
       }
       tc_commit(bar_tmem_full);
@@ -541,8 +576,10 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
                          : "=r"(pk[cc].x), "=r"(pk[cc].y), "=r"(pk[cc].z), "=r"(pk[cc].w)
                          : "r"(src));
           }
-          mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
+          if constexpr (!TA) mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
           const uint32_t arow = sm_a + st * A_STAGE_BYTES + r * 128;
+          uint32_t av[16];  // TA: this thread's 32 k of the block, in k order
+          (void)av;
 #pragma unroll
           for (int cc = 0; cc < CH_T; ++cc) {
             const int c = hsel * CH_T + cc;
@@ -563,11 +600,19 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
               uint4 o[4];
 #pragma unroll
               for (int wi = 0; wi < 4; ++wi) o[wi] = dequant_word4<T, PRE>(words[wi], sg, bg);
+              if constexpr (TA) {
 #pragma unroll
-              for (int wi = 0; wi < 4; ++wi) {
-                const uint32_t chunk = (uint32_t)(c * 4 + wi);  // 8 elements = 16 B of the A row
-                asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + ((chunk ^ xr) << 4)),
-                             "r"(o[wi].x), "r"(o[wi].y), "r"(o[wi].z), "r"(o[wi].w));
+                for (int wi = 0; wi < 4; ++wi) {
+                  av[wi * 4 + 0] = o[wi].x; av[wi * 4 + 1] = o[wi].y;
+                  av[wi * 4 + 2] = o[wi].z; av[wi * 4 + 3] = o[wi].w;
+                }
+              } else {
+#pragma unroll
+                for (int wi = 0; wi < 4; ++wi) {
+                  const uint32_t chunk = (uint32_t)(c * 4 + wi);  // 8 elements = 16 B of the A row
+                  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + ((chunk ^ xr) << 4)),
+                               "r"(o[wi].x), "r"(o[wi].y), "r"(o[wi].z), "r"(o[wi].w));
+                }
               }
             } else {  // chunk = 4 words x 4 bytes = 16 k
               float sc, bi;
@@ -583,14 +628,27 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
               }
               const uint2 lo0 = dequant_word8<T>(pk[cc].x, sc, bi), lo1 = dequant_word8<T>(pk[cc].y, sc, bi);
               const uint2 hi0 = dequant_word8<T>(pk[cc].z, sc, bi), hi1 = dequant_word8<T>(pk[cc].w, sc, bi);
-              const uint32_t chunk = (uint32_t)(c * 2);
-              asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + ((chunk ^ xr) << 4)),
-                           "r"(lo0.x), "r"(lo0.y), "r"(lo1.x), "r"(lo1.y));
-              asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + (((chunk + 1) ^ xr) << 4)),
-                           "r"(hi0.x), "r"(hi0.y), "r"(hi1.x), "r"(hi1.y));
+              if constexpr (TA) {
+                av[cc * 8 + 0] = lo0.x; av[cc * 8 + 1] = lo0.y; av[cc * 8 + 2] = lo1.x; av[cc * 8 + 3] = lo1.y;
+                av[cc * 8 + 4] = hi0.x; av[cc * 8 + 5] = hi0.y; av[cc * 8 + 6] = hi1.x; av[cc * 8 + 7] = hi1.y;
+              } else {
+                const uint32_t chunk = (uint32_t)(c * 2);
+                asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + ((chunk ^ xr) << 4)),
+                             "r"(lo0.x), "r"(lo0.y), "r"(lo1.x), "r"(lo1.y));
+                asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(arow + (((chunk + 1) ^ xr) << 4)),
+                             "r"(hi0.x), "r"(hi0.y), "r"(hi1.x), "r"(hi1.y));
+              }
             }
           }
-          fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+          if constexpr (TA) {
+            // the math above ran ahead of the ring: only the store waits for the slot
+            mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
+            tc_fence_after();
+            tmem_st16(tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + ACC_COLS + st * A_COLS + hsel * 16, av);
+            tc_fence_before();
+          } else {
+            fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+          }
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_full_ab + 8 * st);
         }
@@ -636,8 +694,8 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
         }
       }
     } else if (epi_active) {
-      // split-K: stage the fp32 partial [NB][128] in our own smem (the A ring is idle now)
-      const uint32_t red = sm_a;
+      // split-K: stage the fp32 partial [NB][128] in our own smem (the operand rings are idle now)
+      const uint32_t red = TA ? sm_p : sm_a;
 #pragma unroll 1
       for (int c0 = ec0; c0 < ec0 + ECOLS; c0 += CW) {
         uint32_t v[CW];
@@ -665,7 +723,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
         // 4 consecutive output features per lane (float4) over all peers' partials through
         // DSMEM, in peer order (deterministic), and writes 8 contiguous bytes per lane.
         const int r4 = lane * 4;
-        const uint32_t red = sm_a;
+        const uint32_t red = TA ? sm_p : sm_a;
         const int cols_owned = NB / ksplit;
         T* yp = reinterpret_cast<T*>(p.y);
         const T* bp = reinterpret_cast<const T*>(p.bias);
@@ -772,10 +830,11 @@ static bool sb_tma_ok(const HostArgs& a) {
   return row_bytes % 16 == 0 && (uintptr_t)a.scales % 16 == 0 && (uintptr_t)a.biases % 16 == 0;
 }
 
-template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW, bool SBT = false, bool PRE = false>
+template <typename T, int BITS, int G, int NB, int PS, int NS, int DQW, bool SBT = false, bool PRE = false,
+          bool TA = false>
 static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
-  constexpr int smem = smem_bytes<NB, PS, NS, SBT>();
-  auto kern = qgemm_tc_kernel<T, BITS, G, NB, PS, NS, DQW, SBT, PRE>;
+  constexpr int smem = smem_bytes<NB, PS, NS, SBT, TA>();
+  auto kern = qgemm_tc_kernel<T, BITS, G, NB, PS, NS, DQW, SBT, PRE, TA>;
   constexpr int KB_PER_P = (1024 / BITS) / KB;
   static bool configured = false;
   if (!configured) {
@@ -835,7 +894,7 @@ static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
 // Tuning knobs (b200_set_qlinear_tuning): 0 = heuristic.
 static int g_force_ksplit = 0;
 static int g_force_dqw = 0;
-static int g_variant = 0;  // b200_set_qlinear_variant: 0 = default, 1 = legacy (LDG scales, PS3/NS2)
+static int g_variant = 0;  // b200_set_qlinear_variant: 0 = A in TMEM, 1 = legacy smem A + LDG scales, 2 = smem A + TMA scales
 
 // M <= 64 weight-streaming configurations: NB batch tile, (PS, NS) ring depths.
 template <typename T, int BITS, int G, int NB, bool PRE>
@@ -844,8 +903,8 @@ static int launch_stream(const HostArgs& a, int ksplit, cudaStream_t st) {
   const bool dq8 = g_force_dqw ? g_force_dqw == 8 : true;
   if constexpr (kSbtShape) {
     if (g_variant != 1 && sb_tma_ok(a)) {
-      if (g_variant == 2) return launch_cfg<T, BITS, G, NB, 3, 2, 8, true, PRE>(a, ksplit, st);
-      return launch_cfg<T, BITS, G, NB, 2, 3, 8, true, PRE>(a, ksplit, st);
+      if (g_variant == 2) return launch_cfg<T, BITS, G, NB, 2, 3, 8, true, PRE, false>(a, ksplit, st);
+      return launch_cfg<T, BITS, G, NB, 4, 4, 8, true, PRE, true>(a, ksplit, st);
     }
   }
   return dq8 ? launch_cfg<T, BITS, G, NB, 3, 2, 8, false, PRE>(a, ksplit, st)

@@ -154,7 +154,7 @@ class Model(nn.Module):
     """``forward(input_ids [T], ctx|meta, kv_cache) -> logits`` for the packed batch."""
 
     def __init__(self, args: ModelArgs, dtype=torch.bfloat16, device="cuda", seed: int = 0,
-                 rank: int = 0, world: int = 1, allreduce=None) -> None:
+                 rank: int = 0, world: int = 1, allreduce=None, prepack: bool = True) -> None:
         super().__init__()
         self.args = args
         self.rank, self.world = rank, world
@@ -170,6 +170,17 @@ class Model(nn.Module):
             self.lm_head = None
         else:
             self.lm_head = _rand_qlinear(args.hidden, args.vocab, args, gen, dtype, device)
+        if prepack:
+            self.prepack()
+
+    def prepack(self) -> None:
+        """Load-time transform of every linear into the streaming layout; the MLX-layout
+        ``weight`` is dropped (rebuilt on demand by ``mlx_weight()``) so the footprint is unchanged."""
+        for m in self.modules():
+            if isinstance(m, QuantizedLinear):
+                m.prepack(keep_mlx_layout=False)
+        if self.lm_head is None:
+            self.embed_tokens.prepack()
 
     def _reduce(self, x: torch.Tensor) -> torch.Tensor:
         if self.world > 1:

@@ -144,6 +144,17 @@ class QuantizedEmbedding(nn.Module):
         return get_ops().dequantize(self.weight, self.scales, self.biases, self.group_size, self.bits,
                                     ids=ids, dtype=self.scales.dtype)
 
+    def prepack(self) -> QuantizedEmbedding:
+        """Streaming-layout copy for the tied lm_head (``as_linear``); the gather keeps the MLX layout."""
+        if self.scales.dtype == torch.bfloat16 and (self.scales.shape[1] * self.group_size) % 64 == 0:
+            self.register_buffer("weight_streaming", get_ops().qlinear_prepack(self.weight, self.bits),
+                                 persistent=False)
+        return self
+
     def as_linear(self, x: torch.Tensor) -> torch.Tensor:
+        wp = getattr(self, "weight_streaming", None)
+        if wp is not None and x.dtype == torch.bfloat16:
+            return get_ops().quantized_matmul(x, wp, self.scales, self.biases, transpose=True,
+                                              group_size=self.group_size, bits=self.bits, prepacked=True)
         return get_ops().quantized_matmul(x, self.weight, self.scales, self.biases, transpose=True,
                                           group_size=self.group_size, bits=self.bits)
