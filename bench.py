@@ -372,10 +372,16 @@ def run_b200(args) -> None:
                                "bytes_per_launch": gemv_bytes, "us_per_launch": gemv_ms * 1e3},
             "cpu_baseline": cpu,
         }
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if world > 1:
+        # NCCL collectives live inside captured CUDA graphs: tearing the communicator down with
+        # those graphs alive can block forever (seen on 2xB200), so every rank syncs and leaves
+        # without running the destructors.
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main() -> None:

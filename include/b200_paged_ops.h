@@ -47,6 +47,13 @@ typedef enum b200_status {
 const char* b200_last_error(void);
 int b200_abi_version(void);
 
+/* Programmatic dependent launch (sm_90+): when enabled (default) every kernel of this library is
+ * launched with cudaLaunchAttributeProgrammaticStreamSerialization, so its prologue overlaps the
+ * previous kernel's tail; each kernel executes griddepcontrol.wait before touching data a
+ * previous kernel produced.  No reference analogue (MLX batches a whole step into one Metal
+ * command buffer, paged_ops.cpp:597-631); 0 restores classic stream order for debugging. */
+int b200_set_pdl(int enabled);
+
 /* Split-KV partition length in tokens.  Reference: PARTITION_SIZE = 512
  * (vllm_metal/metal/constants.py:4, exported at paged_ops.cpp:1619-1622). */
 int b200_partition_size(void);
@@ -193,6 +200,11 @@ int b200_set_qlinear_tuning(int ksplit, int dequant_warps);
  * ring 4; 1 = A tile in shared memory, per-thread scale loads, rings 3/2; 2 = A tile in shared
  * memory, TMA-staged scales, rings 2/3.  Process-wide. */
 int b200_set_qlinear_variant(int variant);
+
+/* Debug/profiling: when `dev_ptr` is non-null every tcgen05 qlinear CTA writes up to 64 x uint64
+ * stamps (%globaltimer: start, setup, dependency met, first weights, dequant done, accumulator
+ * done, epilogue done; cycle counters; per-stage times) at dev_ptr[cta * 64 ...]; null (default) disables it. */
+int b200_set_qlinear_trace(void* dev_ptr);
 
 /* Load-time repack into the streaming layout read by b200_qlinear_prepacked: same shape as
  * `w` ([N, K*bits/32] uint32); for bits == 4 the 8 nibbles of every word are permuted so that

@@ -162,3 +162,59 @@ def test_sdpa_forward_fused_and_unfused_agree(ops):
             sdpa._FUSE_NORM_ROPE_CACHE = True
     assert outs[0][0] == outs[1][0]
     assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
+
+
+@pytest.mark.parametrize("dtype", ["bfloat16", "float16", "float32"])
+@pytest.mark.parametrize("rows,vocab", [(1, 7), (3, 1000), (64, 128256), (5, 151937), (2, 8), (4, 65)])
+def test_argmax_is_exact_with_lowest_index_ties(ops, dtype, rows, vocab):
+    """Greedy top-1 (v1/sampling_batch.py:342-348): bit-exact index, lowest index wins ties."""
+    g = torch.Generator(device="cuda").manual_seed(rows * 131 + vocab)
+    # few distinct values -> many exact ties, also across the cluster's slices
+    x = torch.randint(-3, 4, (rows, vocab), device="cuda", generator=g).to(TORCH_DT[dtype])
+    got = ops.argmax(x).cpu().numpy()
+    want = np.argmax(to_np(x).astype(np.float64), axis=-1)
+    np.testing.assert_array_equal(got, want)
+    x = torch.randn((rows, vocab), device="cuda", generator=g).to(TORCH_DT[dtype])
+    np.testing.assert_array_equal(ops.argmax(x).cpu().numpy(), np.argmax(to_np(x).astype(np.float64), axis=-1))
+
+
+def test_argmax_strided_and_unaligned_rows(ops):
+    g = torch.Generator(device="cuda").manual_seed(9)
+    big = torch.randn((6, 4099), device="cuda", generator=g).bfloat16()
+    view = big[:, 3:4000]  # row starts are not 16-byte aligned, stride != width
+    np.testing.assert_array_equal(ops.argmax(view).cpu().numpy(),
+                                  np.argmax(to_np(view).astype(np.float64), axis=-1))
+
+
+def test_programmatic_dependent_launch_does_not_change_results(ops):
+    """PDL only overlaps prologues with the previous kernel's tail: a chain of dependent kernels
+    must give bit-identical results with it on and off."""
+    g = torch.Generator(device="cuda").manual_seed(4)
+    n, k, m = 512, 1024, 64
+    w = torch.randint(-2**31, 2**31 - 1, (n, k // 8), dtype=torch.int32, device="cuda", generator=g)
+    s = (torch.rand((n, k // 64), device="cuda", generator=g) * 0.01 + 0.001).bfloat16()
+    b = (-8.0 * s.float()).bfloat16()
+    w2 = torch.randint(-2**31, 2**31 - 1, (k, n // 8), dtype=torch.int32, device="cuda", generator=g)
+    s2 = (torch.rand((k, n // 64), device="cuda", generator=g) * 0.01 + 0.001).bfloat16()
+    b2 = (-8.0 * s2.float()).bfloat16()
+    nw = torch.ones((k,), device="cuda", dtype=torch.bfloat16)
+    x0 = torch.randn((m, k), device="cuda", generator=g).bfloat16()
+
+    def chain():
+        x = x0.clone()
+        for _ in range(6):
+            h = ops.rms_norm(x, nw, 1e-6)
+            y = ops.quantized_matmul(h, w, s, b, group_size=64, bits=4)
+            x = ops.quantized_matmul(y, w2, s2, b2, group_size=64, bits=4)
+        return ops.argmax(x), x
+
+    try:
+        ops.set_pdl(False)
+        ids0, x_off = chain()
+        ops.set_pdl(True)
+        ids1, x_on = chain()
+    finally:
+        ops.set_pdl(True)
+    torch.cuda.synchronize()
+    assert torch.equal(x_off, x_on)
+    assert torch.equal(ids0, ids1)

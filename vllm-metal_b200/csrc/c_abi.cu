@@ -15,6 +15,9 @@ int set_error(int code, const char* fmt, ...) {
 
 void clear_error() { g_err[0] = 0; }
 
+static int g_pdl = 1;
+bool pdl_enabled() { return g_pdl != 0; }
+
 int sm_count() {
   static int cached = 0;
   if (cached > 0) return cached;
@@ -31,6 +34,12 @@ int sm_count() {
 extern "C" {
 
 const char* b200_last_error(void) { return b200::g_err; }
+
+// Programmatic dependent launch for every kernel of the step (default on; 0 = classic stream order).
+int b200_set_pdl(int enabled) {
+  b200::g_pdl = enabled ? 1 : 0;
+  return B200_OK;
+}
 
 int b200_abi_version(void) { return B200_ABI_VERSION; }
 

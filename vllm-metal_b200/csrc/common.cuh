@@ -122,4 +122,32 @@ __device__ __forceinline__ uint4 ld_stream_u4(const void* p) {
   return r;
 }
 
+// ---- programmatic dependent launch (PDL) -----------------------------------
+// Every kernel of the decode step is launched with the programmatic-stream-serialization
+// attribute: its CTAs may become resident (barrier init, TMEM alloc, weight prefetch) while the
+// previous kernel in the stream drains, and block in pdl_wait() until that kernel has completed
+// and its writes are visible.  RULE: a kernel launched through launch_pdl() must execute
+// pdl_wait() in every thread before it reads anything a previous kernel wrote and before it
+// writes anything at all.  pdl_trigger() lets the *next* kernel start its prologue.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // c_abi.cu (b200_set_pdl); default on
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 }  // namespace b200

@@ -23,6 +23,8 @@ __global__ void __launch_bounds__(256)
 rms_norm_kernel(const T* __restrict__ x, T* __restrict__ residual, const T* __restrict__ weight,
                 T* __restrict__ out, int dim, int64_t x_stride, int64_t res_stride,
                 int64_t out_stride, float eps) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float red[32];
   const int r = blockIdx.x;
   const T* xr = x + (int64_t)r * x_stride;
@@ -54,6 +56,8 @@ __global__ void __launch_bounds__(1024)
 rms_norm_vec_kernel(const T* __restrict__ x, T* __restrict__ residual, const T* __restrict__ weight,
                     T* __restrict__ out, int dim, int64_t x_stride, int64_t res_stride,
                     int64_t out_stride, float eps) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float red[32];
   const int r = blockIdx.x;
   const int nvec = dim >> 3;
@@ -116,6 +120,8 @@ __global__ void __launch_bounds__(256)
 rope_kernel(T* __restrict__ q, T* __restrict__ k, const int32_t* __restrict__ positions,
             int num_q_heads, int num_kv_heads, int head_dim, int rot_dim, float log2_base,
             int traditional, int64_t q_stride, int64_t k_stride) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.x;
   const float pos = (float)positions[t];
   const int half = rot_dim >> 1;
@@ -139,6 +145,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 silu_mul_kernel(const T* __restrict__ gate_up, T* __restrict__ out, int inter, int64_t in_stride,
                 int64_t out_stride) {
+  pdl_trigger();
+  pdl_wait();
   const int r = blockIdx.y;
   const T* g = gate_up + (int64_t)r * in_stride;
   const T* u = g + inter;
@@ -150,30 +158,54 @@ silu_mul_kernel(const T* __restrict__ gate_up, T* __restrict__ out, int inter, i
   }
 }
 
+// Greedy top-1 per row.  A CLUSTER of kArgmaxSplit CTAs shares one row: each CTA scans its slice
+// with 16-byte loads, the per-CTA winners meet in rank 0's shared memory through DSMEM.  Ties go
+// to the lowest index (mx.argmax / numpy semantics, v1/sampling_batch.py:342-348).
+constexpr int kArgmaxSplit = 8;
+constexpr int kArgmaxThreads = 256;
+
+__device__ __forceinline__ void argmax_take(float& best, int& bi, float v, int i) {
+  if (v > best || (v == best && i < bi)) {
+    best = v;
+    bi = i;
+  }
+}
+
 template <typename T>
-__global__ void __launch_bounds__(1024)
+__global__ void __cluster_dims__(kArgmaxSplit, 1, 1) __launch_bounds__(kArgmaxThreads)
 argmax_kernel(const T* __restrict__ logits, int32_t* __restrict__ out, int vocab, int64_t stride) {
-  __shared__ float sv[32];
-  __shared__ int si[32];
-  const int r = blockIdx.x;
+  pdl_trigger();
+  pdl_wait();
+  __shared__ float sv[kArgmaxThreads / 32];
+  __shared__ int si[kArgmaxThreads / 32];
+  __shared__ float cv[kArgmaxSplit];
+  __shared__ int ci[kArgmaxSplit];
+  const int r = blockIdx.y;
+  const int rank = blockIdx.x;  // == cluster rank (cluster spans x)
   const T* row = logits + (int64_t)r * stride;
   float best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
-    const float v = to_float(row[i]);
-    if (v > best || (v == best && i < bi)) {
-      best = v;
-      bi = i;
+  constexpr int VE = 16 / (int)sizeof(T);
+  // slice boundaries in units of VE elements so vector loads stay aligned
+  const int nvec = vocab / VE;
+  const int v_lo = (int)((int64_t)nvec * rank / kArgmaxSplit), v_hi = (int)((int64_t)nvec * (rank + 1) / kArgmaxSplit);
+  if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+    for (int v = v_lo + threadIdx.x; v < v_hi; v += kArgmaxThreads) {
+      const uint4 raw = ld_stream_u4(reinterpret_cast<const uint4*>(row) + v);
+      const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+      for (int j = 0; j < VE; ++j) argmax_take(best, bi, to_float(e[j]), v * VE + j);
     }
+  } else {
+    for (int i = v_lo * VE + threadIdx.x; i < v_hi * VE; i += kArgmaxThreads) argmax_take(best, bi, to_float(row[i]), i);
   }
+  if (rank == kArgmaxSplit - 1)  // tail that does not fill a vector
+    for (int i = nvec * VE + threadIdx.x; i < vocab; i += kArgmaxThreads) argmax_take(best, bi, to_float(row[i]), i);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, best, o);
     const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-    if (ov > best || (ov == best && oi < bi)) {
-      best = ov;
-      bi = oi;
-    }
+    argmax_take(best, bi, ov, oi);
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (lane == 0) {
@@ -182,19 +214,33 @@ argmax_kernel(const T* __restrict__ logits, int32_t* __restrict__ out, int vocab
   }
   __syncthreads();
   if (warp == 0) {
-    const int nw = (blockDim.x + 31) >> 5;
+    constexpr int nw = kArgmaxThreads / 32;
     best = lane < nw ? sv[lane] : -INFINITY;
     bi = lane < nw ? si[lane] : 0x7fffffff;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const float ov = __shfl_xor_sync(0xffffffffu, best, o);
       const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (ov > best || (ov == best && oi < bi)) {
-        best = ov;
-        bi = oi;
-      }
+      argmax_take(best, bi, ov, oi);
     }
-    if (lane == 0) out[r] = bi == 0x7fffffff ? 0 : bi;
+    if (lane == 0) {
+      // publish into rank 0's cv/ci[rank] through distributed shared memory
+      uint32_t av = (uint32_t)__cvta_generic_to_shared(&cv[rank]), ai = (uint32_t)__cvta_generic_to_shared(&ci[rank]);
+      uint32_t rv, ri;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rv) : "r"(av), "r"(0));
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ri) : "r"(ai), "r"(0));
+      asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(rv), "f"(best) : "memory");
+      asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(ri), "r"(bi) : "memory");
+    }
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (rank == 0 && threadIdx.x == 0) {
+    best = cv[0];
+    bi = ci[0];
+#pragma unroll
+    for (int j = 1; j < kArgmaxSplit; ++j) argmax_take(best, bi, cv[j], ci[j]);
+    out[r] = bi == 0x7fffffff ? 0 : bi;
   }
 }
 
@@ -202,6 +248,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 add_inplace_kernel(T* __restrict__ y, const T* __restrict__ x, int dim, int64_t y_stride,
                    int64_t x_stride) {
+  pdl_trigger();
+  pdl_wait();
   const int r = blockIdx.y;
   T* yr = y + (int64_t)r * y_stride;
   const T* xr = x + (int64_t)r * x_stride;
@@ -214,6 +262,8 @@ __global__ void advance_decode_kernel(int32_t* __restrict__ input_ids, int32_t* 
                                       const int32_t* __restrict__ block_tables,
                                       const int32_t* __restrict__ sampled, int batch, int max_blocks,
                                       int block_size) {
+  pdl_trigger();
+  pdl_wait();
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= batch) return;
   const int pos = positions[r] + 1;
@@ -236,7 +286,7 @@ extern "C" int b200_advance_decode(int32_t* input_ids, int32_t* positions, int32
   B200_CHECK_ARG(batch > 0 && max_blocks > 0 && block_size > 0 && input_ids && positions && seq_lens &&
                      slot_mapping && block_tables && sampled,
                  "advance_decode: bad arguments");
-  advance_decode_kernel<<<(batch + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+  launch_pdl(advance_decode_kernel, dim3((batch + 127) / 128), dim3(128), 0, (cudaStream_t)stream, 
       input_ids, positions, seq_lens, slot_mapping, block_tables, sampled, batch, max_blocks, block_size);
   return check_launch("advance_decode_kernel");
 }
@@ -260,24 +310,24 @@ extern "C" int b200_rms_norm(const void* x, void* residual, const void* weight, 
     if (dtype == B200_BF16) {
       using T = __nv_bfloat16;
       if (nv == 1)
-        rms_norm_vec_kernel<T, 1><<<rows, vt, 0, st>>>((const T*)x, (T*)residual, (const T*)weight, (T*)out,
+        launch_pdl(rms_norm_vec_kernel<T, 1>, dim3(rows), dim3(vt), 0, st, (const T*)x, (T*)residual, (const T*)weight, (T*)out,
                                                         dim, x_stride, res_stride, out_stride, eps);
       else
-        rms_norm_vec_kernel<T, 2><<<rows, vt, 0, st>>>((const T*)x, (T*)residual, (const T*)weight, (T*)out,
+        launch_pdl(rms_norm_vec_kernel<T, 2>, dim3(rows), dim3(vt), 0, st, (const T*)x, (T*)residual, (const T*)weight, (T*)out,
                                                         dim, x_stride, res_stride, out_stride, eps);
     } else {
       using T = __half;
       if (nv == 1)
-        rms_norm_vec_kernel<T, 1><<<rows, vt, 0, st>>>((const T*)x, (T*)residual, (const T*)weight, (T*)out,
+        launch_pdl(rms_norm_vec_kernel<T, 1>, dim3(rows), dim3(vt), 0, st, (const T*)x, (T*)residual, (const T*)weight, (T*)out,
                                                         dim, x_stride, res_stride, out_stride, eps);
       else
-        rms_norm_vec_kernel<T, 2><<<rows, vt, 0, st>>>((const T*)x, (T*)residual, (const T*)weight, (T*)out,
+        launch_pdl(rms_norm_vec_kernel<T, 2>, dim3(rows), dim3(vt), 0, st, (const T*)x, (T*)residual, (const T*)weight, (T*)out,
                                                         dim, x_stride, res_stride, out_stride, eps);
     }
     return check_launch("rms_norm_vec_kernel");
   }
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
-    rms_norm_kernel<T><<<rows, threads, 0, st>>>((const T*)x, (T*)residual, (const T*)weight,
+    launch_pdl(rms_norm_kernel<T>, dim3(rows), dim3(threads), 0, st, (const T*)x, (T*)residual, (const T*)weight,
                                                  (T*)out, dim, x_stride, res_stride, out_stride,
                                                  eps);
     return check_launch("rms_norm_kernel");
@@ -296,7 +346,7 @@ extern "C" int b200_rope(void* q, void* k, const int32_t* positions, int num_tok
   B200_CHECK_ARG(base > 0.f, "rope: base must be positive");
   cudaStream_t st = (cudaStream_t)stream;
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
-    rope_kernel<T><<<num_tokens, 256, 0, st>>>((T*)q, (T*)k, positions, num_q_heads, num_kv_heads,
+    launch_pdl(rope_kernel<T>, dim3(num_tokens), dim3(256), 0, st, (T*)q, (T*)k, positions, num_q_heads, num_kv_heads,
                                                head_dim, rot_dim, log2f(base), traditional,
                                                q_stride, k_stride);
     return check_launch("rope_kernel");
@@ -311,7 +361,7 @@ extern "C" int b200_silu_mul(const void* gate_up, void* out, int rows, int inter
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((inter + 1023) / 1024, rows);
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
-    silu_mul_kernel<T><<<grid, 256, 0, st>>>((const T*)gate_up, (T*)out, inter, in_stride,
+    launch_pdl(silu_mul_kernel<T>, dim3(grid), dim3(256), 0, st, (const T*)gate_up, (T*)out, inter, in_stride,
                                              out_stride);
     return check_launch("silu_mul_kernel");
   });
@@ -324,7 +374,7 @@ extern "C" int b200_argmax(const void* logits, int32_t* out, int rows, int vocab
   B200_CHECK_ARG(rows > 0 && vocab > 0 && logits && out, "argmax: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
-    argmax_kernel<T><<<rows, 1024, 0, st>>>((const T*)logits, out, vocab, stride);
+    launch_pdl(argmax_kernel<T>, dim3(kArgmaxSplit, rows), dim3(kArgmaxThreads), 0, st, (const T*)logits, out, vocab, stride);
     return check_launch("argmax_kernel");
   });
 }
@@ -337,7 +387,7 @@ extern "C" int b200_add_inplace(void* y, const void* x, int rows, int dim, int64
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((dim + 1023) / 1024, rows);
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
-    add_inplace_kernel<T><<<grid, 256, 0, st>>>((T*)y, (const T*)x, dim, y_stride, x_stride);
+    launch_pdl(add_inplace_kernel<T>, dim3(grid), dim3(256), 0, st, (T*)y, (const T*)x, dim, y_stride, x_stride);
     return check_launch("add_inplace_kernel");
   });
 }

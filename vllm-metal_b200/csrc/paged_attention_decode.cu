@@ -102,6 +102,8 @@ struct DecodeParams {
 template <typename T, int D, int STAGES>
 __global__ void __launch_bounds__(kDecodeWarps * 32, (D >= 128 ? 2 : 3))
 paged_decode_mma_kernel(const DecodeParams p) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int ROW_BYTES = D * 2;
   constexpr int CHUNKS = D / 8;               // 16-byte chunks per row
   constexpr int ROWS_PER_INSTR = 32 / CHUNKS;  // rows one warp-wide cp.async covers
@@ -374,7 +376,7 @@ static int launch_one(const DecodeParams& p, dim3 grid, cudaStream_t st) {
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  paged_decode_mma_kernel<T, D, STAGES><<<grid, kDecodeWarps * 32, smem, st>>>(p);
+  launch_pdl(paged_decode_mma_kernel<T, D, STAGES>, dim3(grid), dim3(kDecodeWarps * 32), smem, st, p);
   return check_launch("paged_decode_mma_kernel");
 }
 

@@ -28,6 +28,8 @@ paged_attention_generic_kernel(T* __restrict__ out, const T* __restrict__ query,
                                int64_t out_stride, int64_t kv_block_stride,
                                int64_t kv_token_stride, int64_t kv_head_stride, int64_t num_blocks,
                                float scale, float softcap, SplitWorkspace ws, bool partitioned) {
+  pdl_trigger();
+  pdl_wait();
   const int h = blockIdx.x;
   const int t = blockIdx.y;
   const int part = blockIdx.z;
@@ -157,6 +159,8 @@ split_reduce_kernel(T* __restrict__ out, const int32_t* __restrict__ seq_lens,
                     const int32_t* __restrict__ cu_seqlens_q, const float* __restrict__ sinks,
                     int num_seqs, int num_q_heads, int head_dim, int sliding_window,
                     int64_t out_stride, SplitWorkspace ws) {
+  pdl_trigger();
+  pdl_wait();
   const int h = blockIdx.x, t = blockIdx.y;
   const RowInfo ri = row_info(cu_seqlens_q, seq_lens, num_seqs, t, sliding_window);
   const int eff = ri.eff;
@@ -204,7 +208,7 @@ int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cuda
   if (ws) w = *ws;
   dim3 grid(a.num_q_heads, a.num_q_tokens, ws ? ws->num_partitions : 1);
   return B200_DISPATCH_DTYPE(a.dtype, T, [&]() -> int {
-    paged_attention_generic_kernel<T><<<grid, kGenericWarps * 32, smem, st>>>(
+    launch_pdl(paged_attention_generic_kernel<T>, dim3(grid), dim3(kGenericWarps * 32), smem, st, 
         (T*)a.out, (const T*)a.query, (const T*)a.key_cache, (const T*)a.value_cache,
         a.block_tables, a.seq_lens, a.cu_seqlens_q, a.sinks, a.num_seqs, a.num_q_heads,
         a.num_kv_heads, a.head_dim, shift, a.max_blocks_per_seq, a.sliding_window, a.q_stride,
@@ -217,7 +221,7 @@ int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cuda
 int launch_split_reduce(const b200_paged_attn_args& a, const SplitWorkspace& ws, cudaStream_t st) {
   dim3 grid(a.num_q_heads, a.num_q_tokens);
   return B200_DISPATCH_DTYPE(a.dtype, T, [&]() -> int {
-    split_reduce_kernel<T><<<grid, 128, 0, st>>>((T*)a.out, a.seq_lens, a.cu_seqlens_q, a.sinks,
+    launch_pdl(split_reduce_kernel<T>, dim3(grid), dim3(128), 0, st, (T*)a.out, a.seq_lens, a.cu_seqlens_q, a.sinks,
                                                  a.num_seqs, a.num_q_heads, a.head_dim,
                                                  a.sliding_window, a.out_stride, ws);
     return check_launch("split_reduce_kernel");

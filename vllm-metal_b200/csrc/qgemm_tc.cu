@@ -240,7 +240,23 @@ struct Params {
   int64_t y_stride;
   int num_kb;        // K / 64
   int kb_per_split;  // k blocks per cluster rank
+  unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA (b200_set_qlinear_trace), else null
 };
+
+static unsigned long long* g_trace = nullptr;  // host side: b200_set_qlinear_trace
+
+__device__ __forceinline__ void trace_put(const Params& p, int slot, unsigned long long v) {
+  if (p.trace != nullptr)
+    p.trace[((size_t)(blockIdx.x * gridDim.y + blockIdx.y) * gridDim.z + blockIdx.z) * 64 + slot] = v;
+}
+
+__device__ __forceinline__ void trace_stamp(const Params& p, int slot) {
+  if (p.trace != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[((size_t)(blockIdx.x * gridDim.y + blockIdx.y) * gridDim.z + blockIdx.z) * 64 + slot] = t;
+  }
+}
 
 constexpr int SB_STAGE_BYTES = 2 * ROWS * 16;  // 8 groups of scales + 8 of biases per row
 constexpr int SBS = 2;                         // scale/bias ring depth
@@ -321,6 +337,10 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   static_assert(CH_PER_KB % TPR == 0, "chunks must split evenly over the row's threads");
   static_assert(!SBT || (8 * G) % KPP == 0, "a scale/bias stage must cover whole packed stages");
 
+  // PDL: the next kernel may start its prologue now; OUR weight/scale TMA traffic (constant data)
+  // starts before the previous kernel has finished, only the x producer and the epilogue wait.
+  pdl_trigger();
+  if (threadIdx.x == 0) trace_stamp(p, 0);  // CTA start
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = smem_u32(smem_raw);
   if ((base & 1023u) != 0) __trap();  // SWIZZLE_128B stages need 1 KiB alignment: fail loudly
@@ -378,6 +398,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
+  if (threadIdx.x == 0) trace_stamp(p, 1);  // setup done (barriers, TMEM)
 
   if (warp == W_TMA) {
     // ===== packed-weight TMA producer =====
@@ -398,6 +419,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
           }
         }
         mbar_wait(bar_empty_p + 8 * st, ((ps / PS) & 1) ^ 1);
+        if (ps < 16) trace_stamp(p, 32 + ps);  // issue time of packed stage ps
         mbar_expect_tx(bar_full_p + 8 * st, P_STAGE_BYTES);
         tma_load_2d(sm_p + st * P_STAGE_BYTES, &w_map, bar_full_p + 8 * st,
                     (kb_begin + ps * KB_PER_P) * (KB * BITS / 32), n0);
@@ -407,6 +429,8 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   } else if (warp == W_X) {
     // ===== x tile TMA producer =====
     if (lane == 0) {
+      pdl_wait();  // x is the previous kernel's output
+      trace_stamp(p, 2);  // previous kernel complete
       for (int kb = 0; kb < my_kb; ++kb) {
         const int st = kb % NS;
         mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
@@ -521,9 +545,15 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
     if constexpr (!SBT) {
       if (my_ps > 0) load_sb(0);
     }
+    long long w_full = 0, w_empty = 0, w_sb = 0;
+    const long long c_loop = clock64();
     for (int ps = 0; ps < my_ps; ++ps) {
       const int pst = ps % PS;
-      if constexpr (SBT) load_sb_smem(ps);
+      {
+        const long long c_s = clock64();
+        if constexpr (SBT) load_sb_smem(ps);
+        w_sb += clock64() - c_s;
+      }
       // this stage's scales/biases, broadcast once; then prefetch the next stage's
       // (G == 32 with two threads per row: a thread only ever touches group 2j + hsel of k block j)
       constexpr bool SEL = (G < KB) && (TPR == 2);
@@ -559,7 +589,11 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
       } else {
         if (ps + 1 < my_ps) load_sb(ps + 1);
       }
+      const long long c_a = clock64();
       mbar_wait(bar_full_p + 8 * pst, (ps / PS) & 1);
+      w_full += clock64() - c_a;
+      if (ps == 0 && threadIdx.x == 0) trace_stamp(p, 3);  // first packed stage landed
+      if (ps < 16 && threadIdx.x == 0) trace_stamp(p, 16 + ps);  // dequant sees packed stage ps
       const uint32_t prow = sm_p + pst * P_STAGE_BYTES + r * 128;
 #pragma unroll
       for (int j = 0; j < KB_PER_P; ++j) {
@@ -642,7 +676,9 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
           }
           if constexpr (TA) {
             // the math above ran ahead of the ring: only the store waits for the slot
+            const long long c_e = clock64();
             mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
+            w_empty += clock64() - c_e;
             tc_fence_after();
             tmem_st16(tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + ACC_COLS + st * A_COLS + hsel * 16, av);
             tc_fence_before();
@@ -657,12 +693,21 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
       if (lane == 0) mbar_arrive(bar_empty_p + 8 * pst);
     }
 
+    if (threadIdx.x == 0) {
+      trace_stamp(p, 4);  // dequant done
+      trace_put(p, 8, (unsigned long long)(clock64() - c_loop));
+      trace_put(p, 9, (unsigned long long)w_full);
+      trace_put(p, 10, (unsigned long long)w_empty);
+      trace_put(p, 11, (unsigned long long)w_sb);
+    }
     // ===== epilogue (dequant warps: thread <-> TMEM lane r <-> output feature n0 + r;
     //       with 8 warps the batch columns are split in two halves) =====
     if (my_kb > 0) {
       mbar_wait(bar_tmem_full, 0);
       tc_fence_after();
     }
+    if (threadIdx.x == 0) trace_stamp(p, 5);  // accumulator complete
+    pdl_wait();  // y may still be read by the previous kernel when this rank had no k blocks
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     const int nn = n0 + r;
     constexpr int CW = NB < 32 ? 16 : 32;  // columns per tcgen05.ld
@@ -769,6 +814,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
 
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) trace_stamp(p, 6);  // epilogue (and cluster reduce) done
   if (warp == W_MMA) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS)
@@ -874,19 +920,22 @@ static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
   p.y_stride = a.y_stride;
   p.num_kb = a.K / KB;
   // ranks start on packed-stage (hence group) boundaries
+  p.trace = g_trace;
   p.kb_per_split = ((p.num_kb + ksplit - 1) / ksplit + KB_PER_P - 1) / KB_PER_P * KB_PER_P;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((a.N + ROWS - 1) / ROWS, ksplit, (a.M + NB - 1) / NB);
   cfg.blockDim = dim3((DQW + 3) * 32);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 1;
   attr[0].val.clusterDim.y = ksplit;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, w_map, x_map, s_map, b_map, p));
   return B200_OK;
 }
@@ -975,6 +1024,8 @@ int qgemm_tc_set_tuning(int ksplit, int dequant_warps) {
   qtc::g_force_dqw = dequant_warps;
   return B200_OK;
 }
+
+void qgemm_tc_set_trace(void* dev_ptr) { qtc::g_trace = reinterpret_cast<unsigned long long*>(dev_ptr); }
 
 int qgemm_tc_set_variant(int v) {
   if (v < 0 || v > 2) return set_error(B200_ERR_INVALID_ARGUMENT, "qlinear variant must be 0, 1 or 2, got %d", v);

@@ -22,6 +22,7 @@ int qgemm_tc_launch(const void* x, const uint32_t* w, const void* scales, const 
                     const void* bias, void* y, int M, int N, int K, int group_size, int bits, int dtype,
                     int64_t x_stride, int64_t y_stride, bool prepacked, cudaStream_t st);
 int qgemm_tc_set_variant(int v);
+void qgemm_tc_set_trace(void* dev_ptr);
 
 int qgemm_tc_set_tuning(int ksplit, int dequant_warps);
 
@@ -107,6 +108,8 @@ struct Params {
 template <typename T, int BITS, int MT, int RB>
 __global__ void __launch_bounds__(128)
 qgemm_mma_kernel(const Params p) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int NT = 64 * RB;
   constexpr int U4_PER_ROW = KT * BITS / 128;   // 16-byte vectors of packed words per row-step
   constexpr int ELEMS_PER_U4 = 128 / BITS;      // 32 (int4) | 16 (int8)
@@ -293,7 +296,7 @@ static int launch(const Params& p, cudaStream_t st) {
     configured = true;
   }
   dim3 grid((p.N + NT - 1) / NT, (p.M + MT - 1) / MT);
-  qgemm_mma_kernel<T, BITS, MT, RB><<<grid, 128, smem, st>>>(p);
+  launch_pdl(qgemm_mma_kernel<T, BITS, MT, RB>, dim3(grid), dim3(128), smem, st, p);
   return check_launch("qgemm_mma_kernel");
 }
 
@@ -313,6 +316,8 @@ __global__ void __launch_bounds__(256)
 dequantize_rows_kernel(const uint32_t* __restrict__ w, const void* __restrict__ scales,
                        const void* __restrict__ biases, const int32_t* __restrict__ ids,
                        T* __restrict__ out, int N, int K, int group_size, int sb_dtype) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int PER_WORD = 32 / BITS;
   const int r = blockIdx.x;
   int64_t row = ids ? ids[r] : r;
@@ -392,6 +397,8 @@ namespace b200 {
 namespace ql {
 __global__ void prepack_int4_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int64_t n,
                                     int inverse) {
+  pdl_trigger();
+  pdl_wait();
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const uint32_t w = in[i];
     uint32_t o = 0;
@@ -426,7 +433,7 @@ extern "C" int b200_qlinear_prepack(const uint32_t* w, uint32_t* out, int N, int
   const int threads = 256;
   const int64_t want = (words + threads - 1) / threads;
   const int blocks = (int)(want < 148 * 16 ? want : 148 * 16);
-  ql::prepack_int4_kernel<<<blocks, threads, 0, st>>>(w, out, words, inverse);
+  launch_pdl(ql::prepack_int4_kernel, dim3(blocks), dim3(threads), 0, st, w, out, words, inverse);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }
@@ -449,6 +456,11 @@ extern "C" int b200_qlinear_prepacked(const void* x, const uint32_t* wp, const v
                      dtype, sb_dtype, K, (long long)x_stride);
   return qgemm_tc_launch(x, wp, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride, y_stride,
                          true, (cudaStream_t)stream);
+}
+
+extern "C" int b200_set_qlinear_trace(void* dev_ptr) {
+  b200::qgemm_tc_set_trace(dev_ptr);
+  return B200_OK;
 }
 
 extern "C" int b200_set_qlinear_variant(int variant) { return b200::qgemm_tc_set_variant(variant); }
@@ -476,10 +488,10 @@ extern "C" int b200_dequantize_rows(const uint32_t* w, const void* scales, const
   cudaStream_t st = (cudaStream_t)stream;
   return B200_DISPATCH_DTYPE(out_dtype, T, [&]() -> int {
     if (bits == 4)
-      ql::dequantize_rows_kernel<T, 4><<<num_rows, 256, 0, st>>>(w, scales, biases, ids, (T*)out, N,
+      launch_pdl(ql::dequantize_rows_kernel<T, 4>, dim3(num_rows), dim3(256), 0, st, w, scales, biases, ids, (T*)out, N,
                                                                 K, group_size, sb_dtype);
     else
-      ql::dequantize_rows_kernel<T, 8><<<num_rows, 256, 0, st>>>(w, scales, biases, ids, (T*)out, N,
+      launch_pdl(ql::dequantize_rows_kernel<T, 8>, dim3(num_rows), dim3(256), 0, st, w, scales, biases, ids, (T*)out, N,
                                                                 K, group_size, sb_dtype);
     return check_launch("dequantize_rows_kernel");
   });

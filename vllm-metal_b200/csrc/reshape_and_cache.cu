@@ -16,6 +16,8 @@ reshape_and_cache_kernel(const uint8_t* __restrict__ key, const uint8_t* __restr
                          const int64_t* __restrict__ slot_mapping, int row_bytes, int block_size,
                          int64_t num_slots, int64_t block_stride_bytes,
                          int64_t token_stride_bytes) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.x;
   const int64_t slot = slot_mapping[t];
   if (slot < 0 || slot >= num_slots) return;  // padding (reshape_and_cache.metal:61-65)
@@ -41,6 +43,8 @@ __global__ void __launch_bounds__(256)
 copy_blocks_kernel(uint8_t* __restrict__ key_cache, uint8_t* __restrict__ value_cache,
                    const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
                    int64_t block_bytes, int64_t num_blocks) {
+  pdl_trigger();
+  pdl_wait();
   const int pair = blockIdx.x;
   const int64_t s = src[pair], d = dst[pair];
   if (s < 0 || d < 0 || s >= num_blocks || d >= num_blocks || s == d) return;
@@ -88,10 +92,10 @@ extern "C" int b200_reshape_and_cache(const void* key, const void* value, void* 
   auto* vc8 = (uint8_t*)value_cache;
   const int64_t num_slots = num_blocks * block_size;
   if (vec16)
-    reshape_and_cache_kernel<16><<<grid, 128, 0, st>>>(k8, v8, kc8, vc8, slot_mapping, row_bytes,
+    launch_pdl(reshape_and_cache_kernel<16>, dim3(grid), dim3(128), 0, st, k8, v8, kc8, vc8, slot_mapping, row_bytes,
                                                        block_size, num_slots, bsb, tsb);
   else
-    reshape_and_cache_kernel<2><<<grid, 128, 0, st>>>(k8, v8, kc8, vc8, slot_mapping, row_bytes,
+    launch_pdl(reshape_and_cache_kernel<2>, dim3(grid), dim3(128), 0, st, k8, v8, kc8, vc8, slot_mapping, row_bytes,
                                                       block_size, num_slots, bsb, tsb);
   return check_launch("reshape_and_cache_kernel");
 }
@@ -109,7 +113,7 @@ extern "C" int b200_copy_blocks(void* key_cache, void* value_cache, const int32_
   int z = (int)((block_bytes / 16 + 255) / 256);
   if (z > 64) z = 64;
   dim3 grid(num_pairs, 2, z);
-  copy_blocks_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+  launch_pdl(copy_blocks_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, 
       (uint8_t*)key_cache, (uint8_t*)value_cache, src, dst, block_bytes, num_blocks);
   return check_launch("copy_blocks_kernel");
 }

@@ -31,6 +31,8 @@ norm_rope_cache_kernel(T* __restrict__ q, T* __restrict__ k, const T* __restrict
                        int num_kv_heads, int head_dim, int rot_dim, float log2_base, int traditional,
                        float eps, int64_t q_stride, int64_t k_stride, int64_t v_stride, int block_size,
                        int64_t num_slots, int64_t kv_block_stride, int64_t kv_token_stride) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float rows[RC_WARPS][RC_MAX_D];
   const int t = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -136,7 +138,7 @@ extern "C" int b200_norm_rope_cache(void* q, void* k, const void* v, const void*
   cudaStream_t st = (cudaStream_t)stream;
   const float l2b = rot_dim > 0 ? log2f(base) : 0.f;
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
-    norm_rope_cache_kernel<T><<<num_tokens, RC_WARPS * 32, 0, st>>>(
+    launch_pdl(norm_rope_cache_kernel<T>, dim3(num_tokens), dim3(RC_WARPS * 32), 0, st, 
         (T*)q, (T*)k, (const T*)v, (const T*)q_norm_weight, (const T*)k_norm_weight, positions,
         slot_mapping, (T*)key_cache, (T*)value_cache, num_q_heads, num_kv_heads, head_dim, rot_dim, l2b,
         traditional, eps, q_stride, k_stride, v_stride, block_size, num_blocks * block_size,

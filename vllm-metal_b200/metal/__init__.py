@@ -83,6 +83,7 @@ class PagedAttnArgs(ctypes.Structure):
 EXPORTED_SYMBOLS = (
     "b200_last_error",
     "b200_abi_version",
+    "b200_set_pdl",
     "b200_partition_size",
     "b200_min_decode_grid",
     "b200_sm_count",
@@ -94,6 +95,7 @@ EXPORTED_SYMBOLS = (
     "b200_qlinear_prepack",
     "b200_qlinear_prepacked",
     "b200_set_qlinear_variant",
+    "b200_set_qlinear_trace",
     "b200_set_qlinear_kernel",
     "b200_set_qlinear_tuning",
     "b200_dequantize_rows",
@@ -441,6 +443,15 @@ class _Ops:
                                                    int(bool(inverse)), _stream()))
         self.launches += 1
         return out
+
+    def set_pdl(self, enabled: bool = True) -> None:
+        """Programmatic dependent launch for every kernel of the library (default on)."""
+        self._check(self._lib.b200_set_pdl(int(bool(enabled))))
+
+    def set_qlinear_trace(self, buf=None) -> None:
+        """Per-CTA %globaltimer stamps of the tcgen05 qlinear into an int64 CUDA tensor (None = off)."""
+        self._lib.b200_set_qlinear_trace.argtypes = [ctypes.c_void_p]
+        self._check(self._lib.b200_set_qlinear_trace(None if buf is None else buf.data_ptr()))
 
     def set_qlinear_variant(self, variant: int = 0) -> None:
         """Ring configuration of the M <= 64 regime (sweep knob, see the header)."""
