@@ -245,6 +245,13 @@ struct Params {
 
 static unsigned long long* g_trace = nullptr;  // host side: b200_set_qlinear_trace
 
+// In-loop cycle counters perturb the dequant chain: compiled in only with -DQGEMM_LOOP_TRACE.
+#ifdef QGEMM_LOOP_TRACE
+__device__ __forceinline__ long long lt_clock() { return clock64(); }
+#else
+__device__ __forceinline__ long long lt_clock() { return 0; }
+#endif
+
 __device__ __forceinline__ void trace_put(const Params& p, int slot, unsigned long long v) {
   if (p.trace != nullptr)
     p.trace[((size_t)(blockIdx.x * gridDim.y + blockIdx.y) * gridDim.z + blockIdx.z) * 64 + slot] = v;
@@ -419,7 +426,9 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
           }
         }
         mbar_wait(bar_empty_p + 8 * st, ((ps / PS) & 1) ^ 1);
+#ifdef QGEMM_LOOP_TRACE
         if (ps < 16) trace_stamp(p, 32 + ps);  // issue time of packed stage ps
+#endif
         mbar_expect_tx(bar_full_p + 8 * st, P_STAGE_BYTES);
         tma_load_2d(sm_p + st * P_STAGE_BYTES, &w_map, bar_full_p + 8 * st,
                     (kb_begin + ps * KB_PER_P) * (KB * BITS / 32), n0);
@@ -546,13 +555,13 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
       if (my_ps > 0) load_sb(0);
     }
     long long w_full = 0, w_empty = 0, w_sb = 0;
-    const long long c_loop = clock64();
+    const long long c_loop = lt_clock();
     for (int ps = 0; ps < my_ps; ++ps) {
       const int pst = ps % PS;
       {
-        const long long c_s = clock64();
+        const long long c_s = lt_clock();
         if constexpr (SBT) load_sb_smem(ps);
-        w_sb += clock64() - c_s;
+        w_sb += lt_clock() - c_s;
       }
       // this stage's scales/biases, broadcast once; then prefetch the next stage's
       // (G == 32 with two threads per row: a thread only ever touches group 2j + hsel of k block j)
@@ -589,11 +598,13 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
       } else {
         if (ps + 1 < my_ps) load_sb(ps + 1);
       }
-      const long long c_a = clock64();
+      const long long c_a = lt_clock();
       mbar_wait(bar_full_p + 8 * pst, (ps / PS) & 1);
-      w_full += clock64() - c_a;
+      w_full += lt_clock() - c_a;
       if (ps == 0 && threadIdx.x == 0) trace_stamp(p, 3);  // first packed stage landed
+#ifdef QGEMM_LOOP_TRACE
       if (ps < 16 && threadIdx.x == 0) trace_stamp(p, 16 + ps);  // dequant sees packed stage ps
+#endif
       const uint32_t prow = sm_p + pst * P_STAGE_BYTES + r * 128;
 #pragma unroll
       for (int j = 0; j < KB_PER_P; ++j) {
@@ -676,9 +687,9 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
           }
           if constexpr (TA) {
             // the math above ran ahead of the ring: only the store waits for the slot
-            const long long c_e = clock64();
+            const long long c_e = lt_clock();
             mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
-            w_empty += clock64() - c_e;
+            w_empty += lt_clock() - c_e;
             tc_fence_after();
             tmem_st16(tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + ACC_COLS + st * A_COLS + hsel * 16, av);
             tc_fence_before();
@@ -695,7 +706,7 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
 
     if (threadIdx.x == 0) {
       trace_stamp(p, 4);  // dequant done
-      trace_put(p, 8, (unsigned long long)(clock64() - c_loop));
+      trace_put(p, 8, (unsigned long long)(lt_clock() - c_loop));
       trace_put(p, 9, (unsigned long long)w_full);
       trace_put(p, 10, (unsigned long long)w_empty);
       trace_put(p, 11, (unsigned long long)w_sb);

@@ -80,7 +80,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     out = output_path()
     if not force and out.exists() and not stale_artifacts():
         return out
-    cmd = [find_nvcc(), *NVCC_FLAGS, "-o", str(out), *[str(s) for s in sources()]]
+    extra = os.environ.get("B200_NVCC_EXTRA", "").split()  # tuning experiments (-DQGEMM_...), not for shipping
+    cmd = [find_nvcc(), *NVCC_FLAGS, *extra, "-o", str(out), *[str(s) for s in sources()]]
     proc = subprocess.run(cmd, capture_output=True, text=True)
     log = proc.stdout + proc.stderr
     (_PKG_DIR / "build.log").write_text(" ".join(cmd) + "\n" + log)
