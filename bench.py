@@ -217,9 +217,17 @@ def run_b200(args) -> None:
 
     ops = get_ops()
     a = PRESETS[MODEL]
+    nvl = None
+    if world > 1 and os.environ.get("B200_ALLREDUCE", "nvlink") != "nccl":
+        from vllm_metal_b200.distributed.nvlink_allreduce import NVLinkAllReduce
+
+        nvl = NVLinkAllReduce(device=dev, max_bytes=BATCH * a.hidden * 2)
 
     def allreduce(x):
-        dist.all_reduce(x)
+        if nvl is not None:
+            nvl(x)
+        else:
+            dist.all_reduce(x)
 
     model = Model(a, torch.bfloat16, dev, seed=0, rank=rank, world=world, allreduce=allreduce)
     total = args.warmup + args.steps
@@ -357,6 +365,8 @@ def run_b200(args) -> None:
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": BATCH, "ctx": CTX, "block_size": BLOCK,
                        "parallelism": f"tp{world}", "kv_cache": "bf16",
+                       "allreduce": ("none" if world == 1 else "nvlink one-shot kernel (csrc/nvlink_allreduce.cu)"
+                                     if nvl is not None else "nccl"),
                        "l2_policy": "inputs larger than L2: each step streams the per-rank KV pool "
                                     f"({cache.nbytes / 2**30:.1f} GiB) + {model.weight_bytes() / 2**30:.2f} GiB weights"},
             "e2e": {"value": BATCH * args.steps / (e2e_ms * 1e-3), "unit": "tok/s",

@@ -77,6 +77,28 @@ int b200_advance_decode(int32_t* input_ids, int32_t* positions, int32_t* seq_len
                         const int32_t* sampled, int batch, int max_blocks, int block_size,
                         void* stream);
 
+/* ---- tensor-parallel sum over NVLink peer memory ----------------------
+ * The reference runs single-device (vllm_metal/platform.py:524-529); this is the one exchange
+ * step the head/column sharding of the path adds: y = sum over ranks of the o_proj / down_proj
+ * partial outputs.  One process per GPU; buffers are shared with CUDA IPC.
+ *
+ * b200_ipc_alloc: cudaMalloc + zero `bytes` and export a 64-byte cudaIpcMemHandle_t.
+ * b200_ipc_open : map a peer's handle (lazy peer access); b200_ipc_close / b200_ipc_free undo them.
+ * b200_allreduce_sum: in-place sum of x [numel] of `dtype` over `world` in {2,4,8} ranks.
+ *   symm_ptrs[r] : rank r's staging buffer (2 * half_bytes; own pointer at [rank], peers mapped)
+ *   flag_ptrs[r] : rank r's flag array, uint32 [grid * world], zero-initialised
+ *   epoch        : local uint32 [grid], zero-initialised
+ *   grid         : CTAs; must be identical on every rank and every call using these buffers
+ * Every rank must call it in the same order with the same numel.  Result is bit-identical on
+ * all ranks (fixed rank-order fp32 accumulation, one rounding to `dtype`). */
+int b200_ipc_alloc(int64_t bytes, void** ptr, unsigned char* handle64);
+int b200_ipc_open(const unsigned char* handle64, void** ptr);
+int b200_ipc_close(void* ptr);
+int b200_ipc_free(void* ptr);
+int b200_allreduce_sum(void* x, int64_t numel, int dtype, void* const* symm_ptrs,
+                       void* const* flag_ptrs, void* epoch, int rank, int world,
+                       int64_t half_bytes, int grid, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

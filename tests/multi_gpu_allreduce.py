@@ -1,0 +1,129 @@
+"""Multi-GPU check of the NVLink one-shot all-reduce (run under torchrun on N = 2/4/8 B200s):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+        --master-port 29533 tests/multi_gpu_allreduce.py
+
+Not collected by pytest (needs several GPUs); the driver's single-GPU ``-m gpu`` tier cannot run
+it.  Checks, for several sizes and dtypes: equal to an fp32 sum of the gathered inputs rounded once
+(the kernel's contract), within bf16 tolerance of NCCL's result, bit-identical across ranks,
+identical when replayed from a CUDA graph; then times it against ``dist.all_reduce``.
+"""
+
+from __future__ import annotations
+
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main() -> None:
+    rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    from vllm_metal_b200.distributed.nvlink_allreduce import NVLinkAllReduce
+
+    ar = NVLinkAllReduce(device=dev, max_bytes=1 << 20)
+    ok = True
+    for dtype in (torch.bfloat16, torch.float16, torch.float32):
+        for numel in (8, 4096, 64 * 4096, 64 * 4096 + 8, (1 << 20) // 4):
+            if numel * torch.empty((), dtype=dtype).element_size() > (1 << 20):
+                continue
+            g = torch.Generator(device=dev).manual_seed(1000 * rank + numel)
+            x = torch.randn((numel,), device=dev, generator=g).to(dtype)
+            gathered = [torch.empty_like(x) for _ in range(world)]
+            dist.all_gather(gathered, x)
+            want = torch.zeros((numel,), device=dev, dtype=torch.float32)
+            for t in gathered:  # rank order, fp32, one rounding: the kernel's contract
+                want += t.float()
+            want = want.to(dtype)
+            y = x.clone()
+            for _ in range(3):  # repeated calls exercise both staging halves and the epoch counters
+                y = x.clone()
+                ar(y)
+            torch.cuda.synchronize()
+            if not torch.equal(y, want):
+                ok = False
+                print(f"[rank {rank}] MISMATCH dtype={dtype} numel={numel} max diff "
+                      f"{(y.float() - want.float()).abs().max().item()}", flush=True)
+            ref = x.clone()
+            dist.all_reduce(ref)
+            tol = 1e-5 if dtype == torch.float32 else 3e-2
+            if not torch.allclose(y.float(), ref.float(), atol=tol, rtol=tol):
+                ok = False
+                print(f"[rank {rank}] differs from NCCL dtype={dtype} numel={numel}", flush=True)
+            ys = [torch.empty_like(y) for _ in range(world)]
+            dist.all_gather(ys, y)
+            if not all(torch.equal(ys[0], t) for t in ys):
+                ok = False
+                print(f"[rank {rank}] ranks disagree dtype={dtype} numel={numel}", flush=True)
+    assert ar.calls > 0 and ar.nccl_calls == 0, (ar.calls, ar.nccl_calls)
+
+    # CUDA graph replay + timing at the headline message (64 x 4096 bf16 = 512 KiB)
+    x0 = torch.randn((64, 4096), device=dev).bfloat16()
+    bufs = [x0.clone() for _ in range(16)]
+
+    def timed(fn, label):
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            for b in bufs:
+                fn(b)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=s):
+                for b in bufs:
+                    fn(b)
+            graph.replay()
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20):
+                graph.replay()
+            e1.record()
+            torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / (20 * len(bufs))
+        t = torch.tensor([us], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print(f"{label}: {t.item():.2f} us per 512 KiB all-reduce (graph replay, max over {world} ranks)", flush=True)
+
+    for b in bufs:
+        b.copy_(x0)
+    timed(lambda t: ar(t), "nvlink one-shot")
+    timed(lambda t: dist.all_reduce(t), "nccl")
+
+    # graph-replayed result equals the eager one
+    a = x0.clone()
+    ar(a)
+    b = x0.clone()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        g2 = torch.cuda.CUDAGraph()
+        ar(b.clone())
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g2, stream=s):
+            ar(b)
+        b.copy_(x0)
+        g2.replay()
+        torch.cuda.synchronize()
+    if not torch.equal(a, b):
+        ok = False
+        print(f"[rank {rank}] graph replay differs from eager", flush=True)
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("ALLREDUCE " + ("OK" if flag.item() == 1 else "FAILED"), flush=True)
+    dist.barrier()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    os._exit(0 if flag.item() == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

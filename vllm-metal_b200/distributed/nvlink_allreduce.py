@@ -1,0 +1,102 @@
+"""Tensor-parallel sum over NVLink peer memory (kernel: csrc/nvlink_allreduce.cu).
+
+``torch.distributed`` is the plumbing only (rank/world, one ``all_gather_object`` of the CUDA-IPC
+handles at construction); the per-layer exchange is our own one-shot kernel through peer-mapped
+buffers.  Messages that do not fit the staging buffer or are not 16-byte multiples use
+``dist.all_reduce`` (NCCL) -- a size gate, not a fallback for a missing kernel: the constructor
+raises if the CUDA library or peer access is unavailable.
+"""
+
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+from ..metal import _DTYPE_CODE, get_ops
+
+
+class NVLinkAllReduce:
+    """``ar(x)`` sums ``x`` over the group in place.  Safe inside CUDA-graph capture: pointers are
+    fixed at construction and the call epoch lives in device memory."""
+
+    def __init__(self, group=None, device=None, max_bytes: int = 1 << 20, grid: int = 32) -> None:
+        if not dist.is_initialized():
+            raise RuntimeError("NVLinkAllReduce needs an initialised torch.distributed process group")
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        if self.world not in (2, 4, 8):
+            raise ValueError(f"NVLinkAllReduce: world size must be 2, 4 or 8, got {self.world}")
+        self.device = torch.device(device if device is not None else torch.cuda.current_device())
+        self.ops = get_ops()
+        lib = self.lib = self.ops._lib
+        lib.b200_ipc_alloc.argtypes = [ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p), ctypes.c_char_p]
+        lib.b200_ipc_open.argtypes = [ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]
+        lib.b200_ipc_close.argtypes = [ctypes.c_void_p]
+        lib.b200_ipc_free.argtypes = [ctypes.c_void_p]
+        lib.b200_allreduce_sum.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int,
+                                           ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
+                                           ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int64,
+                                           ctypes.c_int, ctypes.c_void_p]
+        self.half_bytes = (int(max_bytes) + 255) // 256 * 256
+        self.grid = int(grid)
+        with torch.cuda.device(self.device):
+            self._own_symm, h_symm = self._alloc(2 * self.half_bytes)
+            self._own_flags, h_flags = self._alloc(self.grid * self.world * 4)
+            self.epoch = torch.zeros((self.grid,), dtype=torch.int32, device=self.device)
+            handles: list = [None] * self.world
+            dist.all_gather_object(handles, (h_symm, h_flags), group=group)
+            self._opened: list[int] = []
+            symm, flags = [], []
+            for r, (hs, hf) in enumerate(handles):
+                if r == self.rank:
+                    symm.append(self._own_symm)
+                    flags.append(self._own_flags)
+                else:
+                    symm.append(self._open(hs))
+                    flags.append(self._open(hf))
+            self._symm = (ctypes.c_void_p * self.world)(*symm)
+            self._flags = (ctypes.c_void_p * self.world)(*flags)
+            torch.cuda.synchronize(self.device)
+        dist.barrier(group=group)  # every rank has zeroed and mapped everything before the first call
+        self.calls = 0
+        self.nccl_calls = 0
+
+    def _alloc(self, nbytes: int) -> tuple[int, bytes]:
+        ptr = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        self.ops._check(self.lib.b200_ipc_alloc(nbytes, ctypes.byref(ptr), handle))
+        return int(ptr.value), handle.raw
+
+    def _open(self, handle: bytes) -> int:
+        ptr = ctypes.c_void_p()
+        self.ops._check(self.lib.b200_ipc_open(handle, ctypes.byref(ptr)))
+        self._opened.append(int(ptr.value))
+        return int(ptr.value)
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        nbytes = x.numel() * x.element_size()
+        if (not x.is_contiguous()) or nbytes % 16 or x.data_ptr() % 16 or nbytes > self.half_bytes \
+                or x.dtype not in _DTYPE_CODE:
+            dist.all_reduce(x, group=self.group)
+            self.nccl_calls += 1
+            return x
+        rc = self.lib.b200_allreduce_sum(x.data_ptr(), x.numel(), _DTYPE_CODE[x.dtype], self._symm, self._flags,
+                                         self.epoch.data_ptr(), self.rank, self.world, self.half_bytes, self.grid,
+                                         torch.cuda.current_stream().cuda_stream)
+        self.ops._check(rc)
+        self.ops.launches += 1
+        self.calls += 1
+        return x
+
+    def close(self) -> None:
+        torch.cuda.synchronize(self.device)
+        for p in self._opened:
+            self.lib.b200_ipc_close(p)
+        self._opened = []
+        for p in (self._own_symm, self._own_flags):
+            if p:
+                self.lib.b200_ipc_free(p)
+        self._own_symm = self._own_flags = 0

@@ -106,6 +106,11 @@ EXPORTED_SYMBOLS = (
     "b200_argmax",
     "b200_add_inplace",
     "b200_advance_decode",
+    "b200_ipc_alloc",
+    "b200_ipc_open",
+    "b200_ipc_close",
+    "b200_ipc_free",
+    "b200_allreduce_sum",
 )
 
 
