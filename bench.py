@@ -182,7 +182,7 @@ def run_reference(args) -> None:
     sample = (f"each step times 1 of {a.num_layers} layers (attention over 64x{CTX}-token bf16 KV + qkv/o/gate_up/down "
               f"int4 g64 linears at M=64) with the oracle C port; step = {a.num_layers} x layer + lm_head "
               f"(timed once on 1/8 of the vocab rows, x8)")
-    print(json.dumps({
+    _emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "tok/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -382,7 +382,7 @@ def run_b200(args) -> None:
                                "bytes_per_launch": gemv_bytes, "us_per_launch": gemv_ms * 1e3},
             "cpu_baseline": cpu,
         }
-        print(json.dumps(line), flush=True)
+        _emit(json.dumps(line))
     if world > 1:
         # NCCL collectives live inside captured CUDA graphs: tearing the communicator down with
         # those graphs alive can block forever (seen on 2xB200), so every rank syncs and leaves
@@ -394,7 +394,25 @@ def run_b200(args) -> None:
         os._exit(0)
 
 
+_REAL_STDOUT = None
+
+
+def _capture_stdout() -> None:
+    """Everything libraries print to fd 1 (NCCL's version banner, ...) goes to stderr; the one JSON
+    line is written to the real stdout by ``_emit``."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(text: str) -> None:
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (text + "\n").encode())
+
+
 def main() -> None:
+    _capture_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=32)

@@ -46,15 +46,10 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// peer data: bypass L1 (a stale line from an earlier call must never be served)
-__device__ __forceinline__ uint4 ld_peer_u4(const void* p) {
-  uint4 r;
-  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p)
-               : "memory");
-  return r;
-}
+// peer data: streaming load that does not allocate in L1.  L1 is invalidated at every kernel
+// launch, so a line cannot survive from an earlier call; the acquire + __syncthreads below order
+// these loads after the peer's release.
+__device__ __forceinline__ uint4 ld_peer_u4(const void* p) { return ld_stream_u4(p); }
 
 template <typename T>
 __device__ __forceinline__ void accumulate(float (&acc)[16 / sizeof(T)], const uint4& v) {
@@ -77,9 +72,9 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const Param
   uint4* xv = reinterpret_cast<uint4*>(p.x);
   uint4* mine = reinterpret_cast<uint4*>(p.symm[p.rank] + half_off);
 
-  // 1. publish my slice
+  // 1. publish my slice.  No per-thread fence: bar.sync orders every thread's stores before the
+  // signalling threads' st.release.sys, which is cumulative over them (PTX memory model).
   for (int64_t v = lo + threadIdx.x; v < hi; v += kThreads) mine[v] = xv[v];
-  __threadfence_system();
   __syncthreads();
   // 2. + 3. per-CTA flag exchange with every peer
   if (threadIdx.x < WORLD && (int)threadIdx.x != p.rank) {

@@ -21,7 +21,7 @@ class NVLinkAllReduce:
     """``ar(x)`` sums ``x`` over the group in place.  Safe inside CUDA-graph capture: pointers are
     fixed at construction and the call epoch lives in device memory."""
 
-    def __init__(self, group=None, device=None, max_bytes: int = 1 << 20, grid: int = 32) -> None:
+    def __init__(self, group=None, device=None, max_bytes: int = 1 << 20, grid: int = 64) -> None:
         if not dist.is_initialized():
             raise RuntimeError("NVLinkAllReduce needs an initialised torch.distributed process group")
         self.group = group
