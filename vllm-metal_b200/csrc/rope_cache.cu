@@ -47,7 +47,8 @@ norm_rope_cache_kernel(T* __restrict__ q, T* __restrict__ k, const T* __restrict
   const int half = rot_dim >> 1;
   float* row = rows[warp];
   const int total = num_q_heads + 2 * num_kv_heads;
-  for (int h = warp; h < total; h += RC_WARPS) {
+  // heads are spread over gridDim.y CTAs per token so a 64-token decode step fills the machine
+  for (int h = blockIdx.y * RC_WARPS + warp; h < total; h += RC_WARPS * gridDim.y) {
     if (h >= num_q_heads + num_kv_heads) {
       // ---- V head: bit-exact copy into the cache ----
       if (!write_cache) continue;
@@ -138,7 +139,9 @@ extern "C" int b200_norm_rope_cache(void* q, void* k, const void* v, const void*
   cudaStream_t st = (cudaStream_t)stream;
   const float l2b = rot_dim > 0 ? log2f(base) : 0.f;
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
-    launch_pdl(norm_rope_cache_kernel<T>, dim3(num_tokens), dim3(RC_WARPS * 32), 0, st, 
+    const int total_heads = num_q_heads + 2 * num_kv_heads;
+    const int ysplit = num_tokens >= 1024 ? 1 : (total_heads + RC_WARPS - 1) / RC_WARPS;
+    launch_pdl(norm_rope_cache_kernel<T>, dim3(num_tokens, ysplit), dim3(RC_WARPS * 32), 0, st, 
         (T*)q, (T*)k, (const T*)v, (const T*)q_norm_weight, (const T*)k_norm_weight, positions,
         slot_mapping, (T*)key_cache, (T*)value_cache, num_q_heads, num_kv_heads, head_dim, rot_dim, l2b,
         traditional, eps, q_stride, k_stride, v_stride, block_size, num_blocks * block_size,
