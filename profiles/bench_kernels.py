@@ -25,9 +25,12 @@ sys.path.insert(0, ROOT)
 from vllm_metal_b200.metal import get_ops  # noqa: E402
 
 PEAK = 6553.0
+TF_PEAK = 1629.0
 try:
     with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-        PEAK = float(json.load(f)["hbm_gbs"])
+        _p = json.load(f)
+        PEAK = float(_p["hbm_gbs"])
+        TF_PEAK = float(_p.get("bf16_tflops", TF_PEAK))
 except Exception:  # noqa: BLE001
     pass
 
@@ -152,7 +155,9 @@ def main():
                 print(f"   {kname:14s} ERROR {r['error']}")
             else:
                 extra = f" diff {r['max_abs_diff_vs_mma']:.3g}/{r['ref_max']:.3g}" if "ref_max" in r else ""
-                print(f"   {kname:14s} {r['us']:8.1f} us {r['gbs']:8.0f} GB/s ({r['gbs'] / PEAK * 100:5.1f}%){extra}")
+                tf = 2.0 * m * n * k / r["us"] / 1e6  # TFLOP/s: the bound that matters for M >= 256
+                tfs = f" {tf:7.1f} TFLOP/s ({tf / TF_PEAK * 100:4.1f}% of bf16 {TF_PEAK:.0f})" if m >= 128 else ""
+                print(f"   {kname:14s} {r['us']:8.1f} us {r['gbs']:8.0f} GB/s ({r['gbs'] / PEAK * 100:5.1f}%){tfs}{extra}")
         del ws
 
     # ---- the small ops of a decode layer ----
