@@ -5,7 +5,7 @@
 
 Not collected by pytest (needs several GPUs); the driver's single-GPU ``-m gpu`` tier cannot run
 it.  Checks, for several sizes and dtypes: equal to an fp32 sum of the gathered inputs rounded once
-(the kernel's contract), within bf16 tolerance of NCCL's result, bit-identical across ranks,
+(the kernel's contract), within the summation-order error bound of NCCL's result, bit-identical across ranks,
 identical when replayed from a CUDA graph; then times it against ``dist.all_reduce``.
 """
 
@@ -53,8 +53,11 @@ def main() -> None:
                       f"{(y.float() - want.float()).abs().max().item()}", flush=True)
             ref = x.clone()
             dist.all_reduce(ref)
-            tol = 1e-5 if dtype == torch.float32 else 3e-2
-            if not torch.allclose(y.float(), ref.float(), atol=tol, rtol=tol):
+            # NCCL sums in the storage dtype in its own (tree/ring) order: any order is within
+            # (world) roundings of the running partial, each <= eps * sum_r |x_r|
+            eps = {torch.float32: 2.0 ** -23, torch.float16: 2.0 ** -10, torch.bfloat16: 2.0 ** -7}[dtype]
+            bound = world * eps * sum(t.float().abs() for t in gathered) + 1e-6
+            if not bool(((y.float() - ref.float()).abs() <= bound).all()):
                 ok = False
                 print(f"[rank {rank}] differs from NCCL dtype={dtype} numel={numel}", flush=True)
             ys = [torch.empty_like(y) for _ in range(world)]

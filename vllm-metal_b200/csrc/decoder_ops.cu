@@ -151,6 +151,29 @@ silu_mul_kernel(const T* __restrict__ gate_up, T* __restrict__ out, int inter, i
   const T* g = gate_up + (int64_t)r * in_stride;
   const T* u = g + inter;
   T* o = out + (int64_t)r * out_stride;
+  constexpr int VE = 16 / (int)sizeof(T);
+  // 16-byte path when every row segment is aligned (the decode layout: inter % 8 == 0)
+  const bool vec = (inter % VE == 0) && ((reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(u) |
+                                          reinterpret_cast<uintptr_t>(o)) % 16 == 0);
+  if (vec) {
+    const int nvec = inter / VE;
+    for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += gridDim.x * blockDim.x) {
+      const uint4 gv = ld_stream_u4(reinterpret_cast<const uint4*>(g) + v);
+      const uint4 uv = ld_stream_u4(reinterpret_cast<const uint4*>(u) + v);
+      const T* ge = reinterpret_cast<const T*>(&gv);
+      const T* ue = reinterpret_cast<const T*>(&uv);
+      uint4 ov;
+      T* oe = reinterpret_cast<T*>(&ov);
+#pragma unroll
+      for (int i = 0; i < VE; ++i) {
+        const float a = to_float(ge[i]);
+        const float s = a / (1.f + __expf(-a));
+        oe[i] = from_float<T>(to_float(from_float<T>(s)) * to_float(ue[i]));
+      }
+      reinterpret_cast<uint4*>(o)[v] = ov;
+    }
+    return;
+  }
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < inter; i += gridDim.x * blockDim.x) {
     const float a = to_float(g[i]);
     const float s = a / (1.f + __expf(-a));
@@ -359,7 +382,7 @@ extern "C" int b200_silu_mul(const void* gate_up, void* out, int rows, int inter
   if (rows == 0) return B200_OK;
   B200_CHECK_ARG(rows > 0 && inter > 0 && gate_up && out, "silu_mul: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((inter + 1023) / 1024, rows);
+  dim3 grid((inter + 2047) / 2048, rows);  // 256 threads x 8 elements per CTA pass
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
     launch_pdl(silu_mul_kernel<T>, dim3(grid), dim3(256), 0, st, (const T*)gate_up, (T*)out, inter, in_stride,
                                              out_stride);

@@ -982,11 +982,11 @@ static int dispatch_g(const HostArgs& a, cudaStream_t st) {
     const int sms = sm_count() > 0 ? sm_count() : 148;
     int ksplit = 1;
     // (tiles >= sms: every SM already streams; measured best unsplit -- profiles/r01_kernels_v3_sweep.txt)
-    // ... and >= 12 k blocks per rank: below that the per-CTA fill + cluster reduce (~6 us) outweighs
+    // ... and >= 12 k blocks per rank unless the split still leaves SMs idle (TP shards): below that the per-CTA fill + cluster reduce (~6 us) outweighs
     // the extra parallelism, and tiles * ksplit stays within one wave of 2 CTAs/SM
     // (qkv 6144x4096: ksplit 8 = 384 CTAs, two waves, 19.1 us; ksplit 4 = 13.8 us -- r01_kernels_v4 sweep)
     while (tiles < sms && ksplit < 8 && tiles * ksplit < 2 * sms && num_kb / (ksplit * 2) >= 2 * KB_PER_P &&
-           num_kb / (ksplit * 2) >= 12 && tiles * ksplit * 2 <= 2 * sms)
+           tiles * ksplit * 2 <= 2 * sms && (num_kb / (ksplit * 2) >= 12 || tiles * ksplit * 2 <= sms))
       ksplit *= 2;
     if (g_force_ksplit > 0) ksplit = g_force_ksplit;
     while (ksplit > 1 && num_kb / ksplit < KB_PER_P) ksplit /= 2;
