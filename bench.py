@@ -43,6 +43,23 @@ METRIC = "decode tok/s (Llama-3.1-8B int4, bs=64)"
 WORKLOAD = "Llama-3.1-8B affine int4 g64 random-init, paged decode bs=64 ctx 4096 block_size 16 (configs[1])"
 
 
+def _ncu_traffic(summary: str) -> float | None:
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch from a committed
+    ``ncu --set full`` summary under profiles/ (per launch, like ``achieved``); None if absent."""
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, seen = 0.0, 0
+    try:
+        with open(os.path.join(ROOT, "profiles", summary)) as f:
+            for line in f:
+                if line.startswith(("dram__bytes_read.sum", "dram__bytes_write.sum")):
+                    unit = line.split("[")[1].split("]")[0]
+                    total += float(line.split("=")[1]) * scale[unit]
+                    seen += 1
+    except Exception:  # noqa: BLE001
+        return None
+    return total if seen == 2 else None
+
+
 def _peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -376,7 +393,9 @@ def run_b200(args) -> None:
             "roofline": {"bound": "hbm", "kernel": "paged_decode_mma_kernel (+ split_reduce_kernel)",
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0,
-                         "traffic": None, "bytes_per_launch": alg_bytes, "us_per_launch": attn_ms * 1e3},
+                         "traffic": _ncu_traffic("r01_attn_full_summary.txt") if world == 1 else None,
+                         "traffic_source": "profiles/r01_attn_full_summary.txt (ncu --set full, same shape)",
+                         "bytes_per_launch": alg_bytes, "us_per_launch": attn_ms * 1e3},
             "roofline_qgemv": {"bound": "hbm", "kernel": "qgemm_tc_kernel, A tile in TMEM (gate_up 28672x4096 int4 g64, M=64)",
                                "achieved": gemv_gbs, "peak": peak, "unit": "GB/s", "frac": gemv_gbs / peak,
                                "bytes_per_launch": gemv_bytes, "us_per_launch": gemv_ms * 1e3},
