@@ -197,7 +197,7 @@ def test_ops_refuse_cpu_tensors():
 
 def test_oracle_not_imported_by_product():
     """The product package must never import the oracle."""
-    pkg = os.path.join(ROOT, "vllm-metal_b200")
+    pkg = os.path.join(ROOT, "vllm_metal_b200")
     for dirpath, _, files in os.walk(pkg):
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):

@@ -1,12 +1,40 @@
-"""Import alias: the package sources live in ``vllm-metal_b200/`` (a directory
-name Python cannot import); this shim makes them importable as
-``vllm_metal_b200`` without copying anything."""
+"""B200-native decode hot path of vllm-metal, behind the reference's plugin surface.
 
-import os as _os
+Entry points mirror ``vllm_metal/__init__.py:117-145``: ``register()`` is the
+``vllm.platform_plugins`` hook and returns the dotted path of the ``Platform``
+subclass when a CUDA device of compute capability 10.x is present (``None``
+otherwise, so vLLM falls through to its other platforms).  Importing this
+package does not import vLLM or load the CUDA library; ``metal.get_ops()`` does
+the latter on first use and raises if it is missing (no CPU fallback).
+"""
 
-_real = _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "vllm-metal_b200")
-__path__ = [_real]
-__file__ = _os.path.join(_real, "__init__.py")
-with open(__file__) as _f:
-    exec(compile(_f.read(), __file__, "exec"))
-del _os, _f, _real
+from __future__ import annotations
+
+__version__ = "0.1.0"
+
+PLATFORM_CLS = "vllm_metal_b200.platform.B200Platform"
+
+
+def _cuda_sm100_available() -> bool:
+    try:
+        import torch
+
+        if not torch.cuda.is_available():
+            return False
+        major, _ = torch.cuda.get_device_capability(0)
+        return major == 10
+    except Exception:  # noqa: BLE001
+        return False
+
+
+def register() -> str | None:
+    """``vllm.platform_plugins`` entry point (reference ``_register``, __init__.py:117-145)."""
+    return PLATFORM_CLS if _cuda_sm100_available() else None
+
+
+def register_quant_config() -> None:
+    """``vllm.general_plugins`` entry point: registers the marker quantization
+    config (reference gguf/vllm_integration.py:110-118)."""
+    from .quant.vllm_integration import register_mlx_affine_config
+
+    register_mlx_affine_config()

@@ -76,19 +76,54 @@ def find_nvcc() -> str:
     return cand
 
 
+def _file_hash(src: Path, extra: list[str]) -> str:
+    h = hashlib.sha256()
+    h.update(src.read_bytes())
+    for f in sorted(list(CSRC_DIR.glob("*.cuh")) + list(INCLUDE_DIR.glob("*.h"))):
+        h.update(f.read_bytes())
+    h.update(" ".join(NVCC_FLAGS + extra).encode())
+    return h.hexdigest()
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
+    """Compile every ``csrc/*.cu`` to an object (in parallel, cached by content hash under
+    ``build/``) and link them into the one shared library."""
+    from concurrent.futures import ThreadPoolExecutor
+
     out = output_path()
     if not force and out.exists() and not stale_artifacts():
         return out
     extra = os.environ.get("B200_NVCC_EXTRA", "").split()  # tuning experiments (-DQGEMM_...), not for shipping
-    cmd = [find_nvcc(), *NVCC_FLAGS, *extra, "-o", str(out), *[str(s) for s in sources()]]
+    nvcc = find_nvcc()
+    obj_dir = _PKG_DIR / "build"
+    obj_dir.mkdir(exist_ok=True)
+    compile_flags = [f for f in NVCC_FLAGS if f != "--shared"]
+    logs: list[str] = []
+
+    def compile_one(src: Path) -> Path:
+        obj = obj_dir / (src.stem + ".o")
+        tag = obj_dir / (src.stem + ".hash")
+        hv = _file_hash(src, extra)
+        if not force and obj.exists() and tag.exists() and tag.read_text() == hv:
+            return obj
+        cmd = [nvcc, *compile_flags, *extra, "-c", "-o", str(obj), str(src)]
+        proc = subprocess.run(cmd, capture_output=True, text=True)
+        logs.append(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+        if proc.returncode != 0:
+            raise RuntimeError(f"nvcc failed ({proc.returncode}) on {src.name}:\n{(proc.stdout + proc.stderr)[-4000:]}")
+        tag.write_text(hv)
+        return obj
+
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+        objs = list(ex.map(compile_one, sources()))
+    cmd = [nvcc, "--shared", "-o", str(out), *[str(o) for o in objs]]
     proc = subprocess.run(cmd, capture_output=True, text=True)
-    log = proc.stdout + proc.stderr
-    (_PKG_DIR / "build.log").write_text(" ".join(cmd) + "\n" + log)
+    logs.append(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+    (_PKG_DIR / "build.log").write_text("\n".join(logs))
     if proc.returncode != 0:
-        raise RuntimeError(f"nvcc failed ({proc.returncode}):\n{log[-4000:]}")
+        raise RuntimeError(f"link failed ({proc.returncode}):\n{(proc.stdout + proc.stderr)[-4000:]}")
     if verbose:
-        print(log)
+        print("\n".join(logs))
     stamp_path().write_text(source_hash() + "\n")
     return out
 
