@@ -43,6 +43,15 @@ METRIC = "decode tok/s (Llama-3.1-8B int4, bs=64)"
 WORKLOAD = "Llama-3.1-8B affine int4 g64 random-init, paged decode bs=64 ctx 4096 block_size 16 (configs[1])"
 
 
+def base_config(gpus: int) -> dict:
+    """The workload description both arms print (key-identical dicts)."""
+    return {"workload": WORKLOAD, "model": "Llama-3.1-8B (random-init, affine int4 g64 incl. lm_head)",
+            "global_batch": BATCH, "ctx": CTX, "block_size": BLOCK, "kv_cache": "bf16",
+            "parallelism": f"tp{gpus}", "decode_steps_timed": "steps",
+            "l2_policy": "inputs larger than L2: every step streams the whole KV pool (32 GiB over all ranks) "
+                         "and all weights (4.2 GB)"}
+
+
 def _ncu_traffic(summary: str) -> float | None:
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch from a committed
     ``ncu --set full`` summary under profiles/ (per launch, like ``achieved``); None if absent."""
@@ -70,49 +79,97 @@ def _peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons sampled DURING the run (B200_PROFILING.md): an NVML polling
+    thread (5 ms period) started before the warm-up; ``mark()``/``window()`` bracket the timed
+    region on the host clock and only samples inside it are reported.  Falls back to an
+    ``nvidia-smi -lms`` pipe if NVML cannot be loaded."""
 
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int) -> None:
-        self.rows, self.proc, self.index = [], None, index
+        self.index, self.rows, self.proc, self._stop = index, [], None, threading.Event()
+        self.mode, self.max_mhz, self.t0, self.t1 = "none", None, None, None
 
     def start(self):
         try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it is a plain index list
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = self.index
+            if vis and all(v.strip().isdigit() for v in vis.split(",")):
+                phys = int(vis.split(",")[self.index])
+            h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+
+            def poll():
+                while not self._stop.is_set():
+                    try:
+                        mhz = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                        mask = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        self.rows.append((time.perf_counter(), float(mhz), int(mask)))
+                    except Exception:  # noqa: BLE001
+                        pass
+                    time.sleep(0.005)
+
+            threading.Thread(target=poll, daemon=True).start()
+            self.mode = "nvml"
+            return
+        except Exception:  # noqa: BLE001
+            pass
+        try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                  "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
+            self.mode = "nvidia-smi"
         except Exception:  # noqa: BLE001
             self.proc = None
 
     def _pump(self):
-        for line in self.proc.stdout:
-            self.rows.append(line.strip())
-
-    def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            f = [x.strip() for x in r.split(",")]
+        bits = {v: k for k, v in self.REASONS.items()}
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
             if len(f) < 6:
                 continue
             try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
+                mhz, self.max_mhz = float(f[0]), float(f[1])
             except ValueError:
                 continue
+            mask = 0
             for n, v in zip(names, f[2:6], strict=True):
                 if v.lower().startswith("active"):
-                    reasons.add(n)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                    mask |= bits[n]
+            self.rows.append((time.perf_counter(), mhz, mask))
+
+    def mark(self):
+        self.t0 = time.perf_counter()
+
+    def window(self):
+        self.t1 = time.perf_counter()
+
+    def stop(self) -> dict:
+        time.sleep(0.03)
+        self._stop.set()
+        if self.proc is not None:
+            self.proc.terminate()
+        if self.mode == "none":
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampler unavailable"], "samples": 0}
+        inside = [r for r in self.rows if self.t0 is not None and self.t0 <= r[0] <= (self.t1 or 1e30)]
+        rows = inside if inside else self.rows  # never empty-handed: say which set was used
+        sm = sorted(r[1] for r in rows)
+        reasons = set()
+        for r in rows:
+            for bit, name in self.REASONS.items():
+                if r[2] & bit:
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(reasons),
+                "samples": len(inside), "samples_whole_run": len(self.rows), "source": self.mode,
+                "scope": "timed region" if inside else "whole run (no sample fell inside the timed region)"}
 
 
 # ------------------------------------------------------------------ CPU baseline ---
@@ -127,6 +184,8 @@ class CpuSample:
         from vllm_metal_b200.lm.decoder import PRESETS
 
         self.np, self.cport = np, cport
+        # all host cores, whatever OMP_NUM_THREADS the launcher exported (torchrun sets it to 1)
+        cport.set_num_threads(os.cpu_count() or 1)
         a = self.a = PRESETS[MODEL]
         rng = np.random.default_rng(seed)
         self.batch = batch
@@ -203,8 +262,9 @@ def run_reference(args) -> None:
         "impl": "reference", "metric": METRIC, "value": val, "unit": "tok/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "note": "reference native code is Apple/Metal-only (unbuildable here); "
-                   "this arm is the CPU restatement of the same path (oracle C port, OpenMP)"},
+        "config": base_config(args.gpus),
+        "note": "reference native code is Apple/Metal-only (unbuildable here); this arm is the CPU restatement of "
+                "the same path (oracle C port, OpenMP, all host cores on rank 0)",
         "cpu_baseline": {"value": val, "unit": "tok/s", "cores": cs.threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -289,16 +349,18 @@ def run_b200(args) -> None:
     max_len_now = runner.fill_decode(tokens, tables, seq_lens)
     runner.buf.upload()
     bucket_len = max_len_now + total  # same split-KV bucket for the whole run
+    sampler = ClockSampler(local)
+    sampler.start()  # before the warm-up, so the first samples exist when the timed region opens
     for _ in range(args.warmup):
         runner.run_decode(BATCH, bucket_len, advance=True)
-    sampler = ClockSampler(local)
     barrier()
-    sampler.start()
+    sampler.mark()
     e0.record()
     for _ in range(args.steps):
         runner.run_decode(BATCH, bucket_len, advance=True)
     e1.record()
     barrier()
+    sampler.window()
     clocks = sampler.stop()
     dev_ms = e0.elapsed_time(e1)
     if os.environ.get("B200_PROFILE_RANGE"):
@@ -380,12 +442,10 @@ def run_b200(args) -> None:
             "metric": METRIC, "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "global_batch": BATCH, "ctx": CTX, "block_size": BLOCK,
-                       "parallelism": f"tp{world}", "kv_cache": "bf16",
-                       "allreduce": ("none" if world == 1 else "nvlink one-shot kernel (csrc/nvlink_allreduce.cu)"
-                                     if nvl is not None else "nccl"),
-                       "l2_policy": "inputs larger than L2: each step streams the per-rank KV pool "
-                                    f"({cache.nbytes / 2**30:.1f} GiB) + {model.weight_bytes() / 2**30:.2f} GiB weights"},
+            "config": base_config(world),
+            "allreduce": ("none" if world == 1 else "nvlink kernel (csrc/nvlink_allreduce.cu)"
+                          if nvl is not None else "nccl"),
+            "per_rank_resident": f"KV pool {cache.nbytes / 2**30:.1f} GiB + weights {model.weight_bytes() / 2**30:.2f} GiB",
             "e2e": {"value": BATCH * args.steps / (e2e_ms * 1e-3), "unit": "tok/s",
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(per_step_launches * args.steps),

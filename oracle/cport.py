@@ -29,6 +29,13 @@ def num_threads() -> int:
     return int(_build.load().oracle_num_threads())
 
 
+def set_num_threads(n: int) -> int:
+    """Use ``n`` OpenMP threads from now on (torchrun exports OMP_NUM_THREADS=1; the CPU arm of
+    bench.py must not inherit that).  Returns the team size in effect."""
+    _build.load().oracle_set_num_threads(ctypes.c_int(int(n)))
+    return num_threads()
+
+
 def reshape_and_cache(key, value, key_cache, value_cache, slot_mapping):
     lib = _build.load()
     assert key_cache.flags.c_contiguous and value_cache.flags.c_contiguous

@@ -53,6 +53,15 @@ int oracle_num_threads(void) {
 #endif
 }
 
+/* Pin the OpenMP team size (bench.py: all host cores, whatever OMP_NUM_THREADS a launcher injected). */
+void oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 /* cache[slot / bs][slot % bs] = row t; negative slots skipped. row_elems = H_kv * D. */
 void oracle_reshape_and_cache(const uint16_t* key, const uint16_t* value, uint16_t* key_cache,
                               uint16_t* value_cache, const int64_t* slot_mapping, int num_tokens,

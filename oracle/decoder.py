@@ -91,13 +91,20 @@ class OracleDecoder:
     ``sinks`` [H_q] or None, ``window`` int."""
 
     def __init__(self, weights, n_heads, n_kv_heads, head_dim, rms_eps, rope_base, num_blocks,
-                 block_size, dtype="bfloat16", rope_traditional=False):
+                 block_size, dtype="bfloat16", rope_traditional=False, c_attention=False):
         self.w = weights
         self.hq, self.hkv, self.d = n_heads, n_kv_heads, head_dim
         self.eps, self.rope_base, self.trad = rms_eps, rope_base, rope_traditional
         self.dtype = dtype
         self.block_size = block_size
+        # c_attention: cache write + attention through the C restatement (oracle/csrc/oracle_cpu.c, checked
+        # against the NumPy kernel-exact oracle in tests/test_oracle_golden.py) -- same arithmetic, OpenMP speed.
+        self.c_attention = bool(c_attention) and dtype == "bfloat16"
         n_layers = len(weights["layers"])
+        if self.c_attention:
+            self.kc = [np.zeros((num_blocks, block_size, n_kv_heads, head_dim), np.uint16) for _ in range(n_layers)]
+            self.vc = [np.zeros((num_blocks, block_size, n_kv_heads, head_dim), np.uint16) for _ in range(n_layers)]
+            return
         self.kc = [np.zeros((num_blocks, block_size, n_kv_heads, head_dim), np.float32) for _ in range(n_layers)]
         self.vc = [np.zeros((num_blocks, block_size, n_kv_heads, head_dim), np.float32) for _ in range(n_layers)]
 
@@ -130,10 +137,19 @@ class OracleDecoder:
                 k = rms_norm(k, L["k_norm"], self.eps, dt)
             q = rope(q, positions, self.d, self.rope_base, self.trad, dt)
             k = rope(k, positions, self.d, self.rope_base, self.trad, dt)
-            kv_write.reshape_and_cache(k, v, self.kc[li], self.vc[li], slots)
-            a = paged_attention.paged_attention_kernel_exact(
-                q, self.kc[li], self.vc[li], bt, seq_lens, cu, self.d ** -0.5, L.get("window", -1), 0.0,
-                L.get("sinks"), dtype=dt)
+            if self.c_attention:
+                from . import cport
+                from ._numeric import bf16_bits, bf16_from_bits
+
+                cport.reshape_and_cache(bf16_bits(k), bf16_bits(v), self.kc[li], self.vc[li], slots)
+                a = bf16_from_bits(cport.paged_attention(
+                    bf16_bits(q), self.kc[li], self.vc[li], bt, seq_lens, cu, self.d ** -0.5,
+                    L.get("window", -1), 0.0, L.get("sinks")))
+            else:
+                kv_write.reshape_and_cache(k, v, self.kc[li], self.vc[li], slots)
+                a = paged_attention.paged_attention_kernel_exact(
+                    q, self.kc[li], self.vc[li], bt, seq_lens, cu, self.d ** -0.5, L.get("window", -1), 0.0,
+                    L.get("sinks"), dtype=dt)
             a = L["o"].matmul(a.reshape(t, nq), dt)
             if L.get("gate_up") is None:
                 delta = a

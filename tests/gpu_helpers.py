@@ -85,7 +85,7 @@ def assert_close(got: torch.Tensor | np.ndarray, want: np.ndarray, dtype: str, w
 
 # ---------------------------------------------------------------- model level ---
 
-def oracle_from_model(model, num_blocks, block_size):
+def oracle_from_model(model, num_blocks, block_size, c_attention=False):
     """Build an ``oracle.decoder.OracleDecoder`` holding the SAME quantised weights
     as a product ``lm.decoder.Model`` (copied to host; nothing is recomputed)."""
     from oracle.decoder import OracleDecoder, QWeight
@@ -112,4 +112,4 @@ def oracle_from_model(model, num_blocks, block_size):
     weights = dict(embed=qw(model.embed_tokens), lm_head=None if model.lm_head is None else qw(model.lm_head),
                    norm=to_np(model.norm.weight), layers=layers)
     return OracleDecoder(weights, a.n_heads, a.n_kv_heads, a.head_dim, a.rms_eps, a.rope_base, num_blocks,
-                         block_size, "bfloat16")
+                         block_size, "bfloat16", c_attention=c_attention)

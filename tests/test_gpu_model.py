@@ -96,3 +96,58 @@ def test_tiny_gpt_oss_style_sinks_and_window():
 def test_tiny_cuda_graph_decode_matches_oracle():
     exact, near = _run({}, steps=40, prompt_lens=[30, 31, 500], cuda_graph=True)
     assert near <= 0.05 * (exact + near)
+
+
+def _bf16_ulp(x: float) -> float:
+    x = abs(float(x))
+    return 2.0 ** -133 if x == 0.0 else 2.0 ** (int(np.floor(np.log2(x))) - 7)
+
+
+def test_cfg_a_qwen3_0p6b_128_free_running_greedy_steps():
+    """BASELINE configs[0] at its stated size: Qwen3-0.6B shapes (28 layers, hidden 1024, 16q/8kv x 128,
+    vocab 151936, q/k norm, tied int4 g64 head), bs 1, 512-token prompt, block 16, 128 greedy
+    decode steps.  The product runs FREE (CUDA graph, its own tokens fed back, as in
+    /root/reference/tests/test_paged_deterministic.py:50-74); the oracle is stepped along the
+    product's trajectory and must name the same token at every step.  A differing token is only
+    tolerated -- and printed -- when the oracle's own logits of the two candidates are less than
+    one bf16 ulp apart (a tie at the logits' storage precision); no mismatch budget."""
+    from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
+    from vllm_metal_b200.lm.decoder import PRESETS, Model
+    from vllm_metal_b200.v1.model_runner import PagedModelRunner
+
+    args = PRESETS["qwen3-0.6b"]
+    steps, prompt_len, bs = 128, 512, 16
+    model = Model(args, torch.bfloat16, "cuda", seed=0)
+    blocks = (prompt_len + steps + bs) // bs
+    nb = 1 + blocks
+    cache = B200PagedKVCache(args.num_layers, args.n_kv_heads, args.head_dim, nb, bs, torch.bfloat16, "cuda")
+    runner = PagedModelRunner(model, cache, max_batch=1, max_model_len=blocks * bs, use_cuda_graph=True)
+    oracle = oracle_from_model(model, nb, bs)
+    rng = np.random.default_rng(1)  # SURVEY 8(d): token ids seed 1, page permutation seed 2
+    prompt = rng.integers(0, args.vocab, prompt_len).tolist()
+    table = (np.random.default_rng(2).permutation(nb - 1) + 1).tolist()
+
+    got = runner.execute(prompt, [], [(table, prompt_len, 0)])
+    ologits = oracle.forward(prompt, [], [(table, prompt_len, 0)])
+    ties = []
+
+    def check(step, got_tok, ologits):
+        want = int(oracle.greedy(ologits)[0])
+        if got_tok == want:
+            return
+        gap = float(ologits[0, want] - ologits[0, got_tok])
+        ulp = _bf16_ulp(ologits[0, want])
+        print(f"step {step}: product {got_tok} vs oracle {want}, oracle logit gap {gap:.6f} (1 bf16 ulp = {ulp:.6f})")
+        assert gap < ulp, f"step {step}: token {got_tok} != oracle {want}; oracle top-2 gap {gap} >= 1 bf16 ulp {ulp}"
+        ties.append(step)
+
+    check(-1, got[0], ologits)
+    seq_len, cur, tokens = prompt_len, got[0], []
+    for step in range(steps):
+        nxt = runner.decode_step([cur], [table], [seq_len])[0]
+        ologits = oracle.forward([cur], [(table, seq_len)], [])
+        check(step, nxt, ologits)
+        tokens.append(nxt)
+        cur, seq_len = nxt, seq_len + 1
+    assert len(tokens) == steps
+    print(f"cfg a: {steps} free-running greedy steps, {len(ties)} bf16-ulp ties at steps {ties}")

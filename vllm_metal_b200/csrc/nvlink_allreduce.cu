@@ -46,10 +46,18 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// peer data: streaming load that does not allocate in L1.  L1 is invalidated at every kernel
-// launch, so a line cannot survive from an earlier call; the acquire + __syncthreads below order
-// these loads after the peer's release.
-__device__ __forceinline__ uint4 ld_peer_u4(const void* p) { return ld_stream_u4(p); }
+// peer data: a COHERENT 128-bit load (relaxed, system scope).  The staging halves are rewritten by
+// the peers every second call while kernels of this rank may still be resident (PDL), so the
+// non-coherent .nc path -- which presumes the data is read-only for the kernel's lifetime -- is not
+// allowed here; the acquire + __syncthreads below order these loads after the peer's release.
+__device__ __forceinline__ uint4 ld_peer_u4(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
 
 template <typename T>
 __device__ __forceinline__ void accumulate(float (&acc)[16 / sizeof(T)], const uint4& v) {
@@ -65,9 +73,10 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const Param
   constexpr int VE = 16 / (int)sizeof(T);
   const int b = blockIdx.x;
   const uint32_t e = p.epoch[b] + 1u;
-  const int64_t per = (p.nvec + gridDim.x - 1) / gridDim.x;
+  // slices are whole 128-byte lines (8 vectors): no two CTAs ever share a line of a peer's staging buffer
+  const int64_t per = ((p.nvec + gridDim.x - 1) / gridDim.x + 7) / 8 * 8;
   const int64_t lo = b * per;
-  const int64_t hi = lo + per < p.nvec ? lo + per : p.nvec;
+  const int64_t hi = lo + per < p.nvec ? lo + per : p.nvec;  // (lo may exceed nvec: empty slice, flags still exchanged)
   const int64_t half_off = (int64_t)(e & 1u) * p.half_bytes;
   uint4* xv = reinterpret_cast<uint4*>(p.x);
   uint4* mine = reinterpret_cast<uint4*>(p.symm[p.rank] + half_off);

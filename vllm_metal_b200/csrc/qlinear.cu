@@ -337,6 +337,43 @@ dequantize_rows_kernel(const uint32_t* __restrict__ w, const void* __restrict__ 
   }
 }
 
+// ---- fp32 activations: MLX's own factorisation, y = sum_g (s_g * sum_k x_k q_k + b_g * sum_k x_k), all fp32.
+// The reference exercises this only in tests (tests/test_gguf_mlx_native.py:70-86, atol = max|ref| * 4e-6);
+// one warp per output element, lanes stride the row's packed words (coalesced), no tensor cores.
+template <int BITS>
+__global__ void __launch_bounds__(256)
+qgemv_f32_kernel(const float* __restrict__ x, const uint32_t* __restrict__ w, const void* __restrict__ scales,
+                 const void* __restrict__ biases, const float* __restrict__ bias, float* __restrict__ y, int M,
+                 int N, int K, int group_size, int sb_dtype, int64_t x_stride, int64_t y_stride) {
+  pdl_trigger();
+  pdl_wait();
+  constexpr int PER_WORD = 32 / BITS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * (blockDim.x >> 5) + warp;
+  const int m = blockIdx.y;
+  if (n >= N || m >= M) return;
+  const int words = K / PER_WORD, groups = K / group_size;
+  const float* xr = x + (int64_t)m * x_stride;
+  const uint32_t* wr = w + (int64_t)n * words;
+  float acc = 0.f;
+  for (int wi = lane; wi < words; wi += 32) {
+    const uint32_t wd = wr[wi];
+    const int k0 = wi * PER_WORD;
+    const int64_t gi = (int64_t)n * groups + k0 / group_size;
+    const float s = sb_load(scales, gi, sb_dtype), b = sb_load(biases, gi, sb_dtype);
+    float xq = 0.f, xs = 0.f;
+#pragma unroll
+    for (int e = 0; e < PER_WORD; ++e) {
+      const float xv = xr[k0 + e];
+      xq = fmaf(xv, (float)((wd >> (e * BITS)) & ((1u << BITS) - 1u)), xq);
+      xs += xv;
+    }
+    acc += s * xq + b * xs;
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) y[(int64_t)m * y_stride + n] = acc + (bias ? bias[n] : 0.f);
+}
+
 }  // namespace ql
 }  // namespace b200
 
@@ -364,8 +401,23 @@ extern "C" int b200_qlinear(const void* x, const uint32_t* w, const void* scales
   B200_CHECK_ARG(M >= 0, "qlinear: M must be >= 0, got %d", M);
   if (M == 0) return B200_OK;
   B200_CHECK_ARG(x && w && scales && biases && y, "qlinear: null pointer argument");
+  if (dtype == B200_F32) {
+    B200_CHECK_ARG(y_stride >= N && x_stride >= K, "qlinear: bad fp32 strides");
+    cudaStream_t stf = (cudaStream_t)stream;
+    const dim3 grid((N + 7) / 8, M), block(256);
+    const float* xf = reinterpret_cast<const float*>(x);
+    const float* bf = reinterpret_cast<const float*>(bias);
+    float* yf = reinterpret_cast<float*>(y);
+    if (bits == 4)
+      launch_pdl(ql::qgemv_f32_kernel<4>, grid, block, 0, stf, xf, w, scales, biases, bf, yf, M, N, K, group_size,
+                 sb_dtype, x_stride, y_stride);
+    else
+      launch_pdl(ql::qgemv_f32_kernel<8>, grid, block, 0, stf, xf, w, scales, biases, bf, yf, M, N, K, group_size,
+                 sb_dtype, x_stride, y_stride);
+    return check_launch("qgemv_f32_kernel");
+  }
   B200_CHECK_ARG(dtype == B200_BF16 || dtype == B200_F16,
-                 "qlinear: activations must be bf16 or fp16 (dtype code %d)", dtype);
+                 "qlinear: activations must be fp32, bf16 or fp16 (dtype code %d)", dtype);
   B200_CHECK_ARG(K % ql::KT == 0, "qlinear: K (%d) must be a multiple of %d", K, ql::KT);
   cudaStream_t st0 = (cudaStream_t)stream;
   if (g_qlinear_kernel != 1) {
@@ -397,7 +449,8 @@ namespace b200 {
 namespace ql {
 __global__ void prepack_int4_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int64_t n,
                                     int inverse) {
-  pdl_trigger();
+  // no early pdl_trigger(): the quantized GEMM prefetches weights BEFORE its own pdl_wait (they are
+  // constants on the decode path), so a dependent launch must not start until this grid is done
   pdl_wait();
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const uint32_t w = in[i];
@@ -427,7 +480,10 @@ extern "C" int b200_qlinear_prepack(const uint32_t* w, uint32_t* out, int N, int
   const int64_t words = (int64_t)N * ((int64_t)K * bits / 32);
   cudaStream_t st = (cudaStream_t)stream;
   if (bits == 8) {  // int8 streams in the MLX order already
-    if (w != out) B200_CUDA_OK(cudaMemcpyAsync(out, w, words * 4, cudaMemcpyDeviceToDevice, st));
+    if (w != out) {
+      B200_CUDA_OK(cudaMemcpyAsync(out, w, words * 4, cudaMemcpyDeviceToDevice, st));
+      B200_CUDA_OK(cudaStreamSynchronize(st));
+    }
     return B200_OK;
   }
   const int threads = 256;
@@ -435,6 +491,10 @@ extern "C" int b200_qlinear_prepack(const uint32_t* w, uint32_t* out, int N, int
   const int blocks = (int)(want < 148 * 16 ? want : 148 * 16);
   launch_pdl(ql::prepack_int4_kernel, dim3(blocks), dim3(threads), 0, st, w, out, words, inverse);
   B200_CUDA_OK(cudaGetLastError());
+  // load-time call: make the streaming layout stream-complete before any qlinear can prefetch it
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  B200_CUDA_OK(cudaStreamIsCapturing(st, &cap));
+  if (cap == cudaStreamCaptureStatusNone) B200_CUDA_OK(cudaStreamSynchronize(st));
   return B200_OK;
 }
 
