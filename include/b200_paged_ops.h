@@ -229,6 +229,39 @@ int b200_dequantize_rows(const uint32_t* w, const void* scales,
                          int num_rows, int N, int K, int group_size, int bits,
                          int sb_dtype, int out_dtype, void* stream);
 
+/* ---- streaming-layout quantized linear: persistent stream-K kernel (csrc/qgemm_stream.cu) ----------------
+ * The decode-regime (M <= 64) replacement for mx.quantized_matmul as nn.QuantizedLinear calls it
+ * (vllm_metal/gguf/mlx_native.py:212-222, attention/impls/sdpa.py:297-343,739) and, with
+ * epilogue = 1, for the SwiGLU the reference fuses in vllm_metal/compiled_mlp.py:1-22
+ * (y[m,i] = silu(gate[m,i]) * up[m,i], gate|up = rows [0,N/2) | [N/2,N) of the weight).
+ *
+ * b200_qstream_prepack turns an MLX-affine triple (w uint32 [N, K*bits/32], scales/biases [N, K/g]) into
+ * ONE device blob of b200_qstream_blob_bytes(...) bytes: per (256-row super-tile, k-slab) unit the
+ * packed words in the order the kernel's dequant threads read them, followed by fp16 (scale, bias)
+ * pairs.  It is a load-time call and synchronises the stream: the kernel prefetches weights BEFORE its
+ * programmatic-dependency wait, so a blob must be stream-complete before the first b200_qstream_linear
+ * that reads it.  Fails with B200_ERR_UNSUPPORTED when a scale/bias does not fit fp16 (keep the MLX
+ * layout and b200_qlinear then).  b200_qstream_unpack is the bit-exact inverse of the integer part.
+ *
+ * b200_qstream_linear: x [M, K] bf16/fp16 (row stride x_stride elements), y [M, N] (or [M, N/2] with
+ * epilogue = 1), optional dense bias [N] in the x dtype (epilogue 0 only).  `workspace` is
+ * b200_qstream_workspace_bytes() of device memory, ZERO-initialised once by the caller and shared by
+ * all calls on one stream (fp32 partials of super-tiles cut between CTAs + their arrival counters). */
+int64_t b200_qstream_blob_bytes(int N, int K, int bits, int group_size, int swiglu);
+int64_t b200_qstream_workspace_bytes(void);
+int b200_qstream_prepack(const uint32_t* w, const void* scales, const void* biases, void* blob,
+                         int N, int K, int bits, int group_size, int sb_dtype, int swiglu,
+                         void* stream);
+int b200_qstream_unpack(const void* blob, uint32_t* w_out, int N, int K, int bits,
+                        int group_size, int swiglu, void* stream);
+int b200_qstream_linear(const void* x, const void* blob, const void* bias, void* y, int M, int N,
+                        int K, int group_size, int bits, int dtype, int epilogue,
+                        int64_t x_stride, int64_t y_stride, void* workspace,
+                        int64_t workspace_bytes, void* stream);
+/* tuning / tracing knobs (0 / NULL = default) */
+int b200_set_qstream_grid(int grid);
+int b200_set_qstream_trace(void* dev_ptr);
+
 #ifdef __cplusplus
 }
 #endif

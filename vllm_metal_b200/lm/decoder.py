@@ -138,6 +138,8 @@ class MLP(nn.Module):
         self.down_proj = _rand_qlinear(args.intermediate, args.hidden, args, gen, dtype, device).shard_cols(rank, world)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.gate_up_proj.swiglu:  # SiLU * up fused into the gate_up epilogue (streaming layout)
+            return self.down_proj(self.gate_up_proj(x))
         return self.down_proj(get_ops().silu_mul(self.gate_up_proj(x)))
 
 
@@ -177,7 +179,10 @@ class Model(nn.Module):
         """Load-time transform of every linear into the streaming layout; the MLX-layout
         ``weight`` is dropped (rebuilt on demand by ``mlx_weight()``) so the footprint is unchanged."""
         for m in self.modules():
-            if isinstance(m, QuantizedLinear):
+            if isinstance(m, MLP):
+                m.gate_up_proj.prepack(keep_mlx_layout=False, swiglu=True)
+        for m in self.modules():
+            if isinstance(m, QuantizedLinear) and getattr(m, "weight_blob", None) is None:
                 m.prepack(keep_mlx_layout=False)
         if self.lm_head is None:
             self.embed_tokens.prepack()

@@ -79,7 +79,7 @@ class PagedAttnArgs(ctypes.Structure):
 
 
 # Every symbol include/*.h declares; the CPU test-suite checks the library
-# exports all of them (tests/test_abi.py).
+# exports all of them (tests/test_host_logic.py::test_library_exports_every_declared_symbol).
 EXPORTED_SYMBOLS = (
     "b200_last_error",
     "b200_abi_version",
@@ -99,6 +99,13 @@ EXPORTED_SYMBOLS = (
     "b200_set_qlinear_kernel",
     "b200_set_qlinear_tuning",
     "b200_dequantize_rows",
+    "b200_qstream_blob_bytes",
+    "b200_qstream_workspace_bytes",
+    "b200_qstream_prepack",
+    "b200_qstream_unpack",
+    "b200_qstream_linear",
+    "b200_set_qstream_grid",
+    "b200_set_qstream_trace",
     "b200_rms_norm",
     "b200_rope",
     "b200_norm_rope_cache",
@@ -153,6 +160,14 @@ def load_library() -> ctypes.CDLL:
     lib.b200_qlinear_prepacked.argtypes = lib.b200_qlinear.argtypes
     lib.b200_qlinear_prepack.argtypes = [vp, vp, i32, i32, i32, i32, vp]
     lib.b200_dequantize_rows.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
+    lib.b200_qstream_blob_bytes.restype = ctypes.c_int64
+    lib.b200_qstream_blob_bytes.argtypes = [i32, i32, i32, i32, i32]
+    lib.b200_qstream_workspace_bytes.restype = ctypes.c_int64
+    lib.b200_qstream_prepack.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
+    lib.b200_qstream_unpack.argtypes = [vp, vp, i32, i32, i32, i32, i32, vp]
+    lib.b200_qstream_linear.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i64, i64, vp, i64, vp]
+    lib.b200_set_qstream_grid.argtypes = [i32]
+    lib.b200_set_qstream_trace.argtypes = [vp]
     lib.b200_rms_norm.argtypes = [vp, vp, vp, vp, i32, i32, i64, i64, i64, f32, i32, vp]
     lib.b200_rope.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i64, i64, i32, vp]
     lib.b200_norm_rope_cache.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32,
@@ -198,6 +213,7 @@ class _Ops:
     def __init__(self, lib: ctypes.CDLL) -> None:
         self._lib = lib
         self._workspaces: dict[int, list[torch.Tensor]] = {}
+        self._qstream_ws: dict[int, torch.Tensor] = {}
         self.launches = 0  # kernels launched through this object (bench.py's gpu_launches)
 
     # -- error plumbing -----------------------------------------------------
@@ -448,6 +464,80 @@ class _Ops:
                                                    int(bool(inverse)), _stream()))
         self.launches += 1
         return out
+
+    # -- streaming-layout linears: persistent stream-K kernel (csrc/qgemm_stream.cu) -----------
+    def qstream_prepack(self, w, scales, biases, group_size: int = 64, bits: int = 4, swiglu: bool = False):
+        """MLX-affine triple -> the streaming blob (uint8 tensor) read by ``qstream_linear``.
+        Load-time; raises ``ValueError`` when a scale/bias does not fit fp16."""
+        for n, t in (("w", w), ("scales", scales), ("biases", biases)):
+            _require_cuda(n, t)
+        if w.dtype not in (torch.uint32, torch.int32) or w.dim() != 2:
+            raise ValueError("w must be uint32 [N, K*bits/32]")
+        n_out, words = w.shape
+        k = words * 32 // bits
+        if scales.shape != (n_out, k // group_size) or biases.shape != scales.shape or scales.dtype != biases.dtype:
+            raise ValueError(f"scales/biases must be [{n_out}, {k // group_size}] of one dtype")
+        nbytes = self._lib.b200_qstream_blob_bytes(n_out, k, bits, group_size, int(swiglu))
+        if nbytes <= 0:
+            raise ValueError(f"qstream_prepack: unsupported shape N={n_out} K={k} bits={bits} group={group_size}")
+        blob = torch.empty((nbytes,), dtype=torch.uint8, device=w.device)
+        self._check(self._lib.b200_qstream_prepack(
+            w.contiguous().data_ptr(), scales.contiguous().data_ptr(), biases.contiguous().data_ptr(),
+            blob.data_ptr(), n_out, k, bits, group_size, _dtype_code("scales", scales), int(swiglu), _stream()))
+        self.launches += 1
+        return blob
+
+    def qstream_unpack(self, blob, n_out: int, k: int, group_size: int = 64, bits: int = 4, swiglu: bool = False):
+        """The MLX-layout packed words back from a streaming blob (bit-exact)."""
+        _require_cuda("blob", blob)
+        out = torch.empty((n_out, k * bits // 32), dtype=torch.int32, device=blob.device)
+        self._check(self._lib.b200_qstream_unpack(blob.data_ptr(), out.data_ptr(), n_out, k, bits, group_size,
+                                                  int(swiglu), _stream()))
+        self.launches += 1
+        return out
+
+    def _qstream_workspace(self, device: torch.device) -> torch.Tensor:
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        ws = self._qstream_ws.get(idx)
+        if ws is None:
+            with torch.cuda.device(idx):
+                ws = torch.zeros((self._lib.b200_qstream_workspace_bytes(),), dtype=torch.uint8, device=device)
+            self._qstream_ws[idx] = ws
+        return ws
+
+    def qstream_linear(self, x, blob, n_out: int, k: int, group_size: int = 64, bits: int = 4, bias=None,
+                       swiglu: bool = False, out=None):
+        """``x @ W'^T (+ bias)`` over a streaming blob; ``swiglu=True`` returns ``silu(gate) * up``
+        (``[.., n_out / 2]``) from a blob packed with ``swiglu=True``."""
+        _require_cuda("x", x)
+        _require_cuda("blob", blob)
+        if x.shape[-1] != k:
+            raise ValueError(f"x last dim {x.shape[-1]} != K={k}")
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, k)
+        if x2.stride(1) != 1:
+            x2 = x2.contiguous()
+        m = x2.shape[0]
+        cols = n_out // 2 if swiglu else n_out
+        if out is None:
+            out = torch.empty((m, cols), dtype=x.dtype, device=x.device)
+        y2 = out.reshape(m, cols)
+        if bias is not None:
+            bias = bias.to(dtype=x.dtype).contiguous()
+        ws = self._qstream_workspace(x.device)
+        rc = self._lib.b200_qstream_linear(
+            x2.data_ptr(), blob.data_ptr(), _ptr(bias), y2.data_ptr(), m, n_out, k, group_size, bits,
+            _dtype_code("x", x), int(swiglu), x2.stride(0), y2.stride(0), ws.data_ptr(), ws.numel(), _stream())
+        self._check(rc)
+        self.launches += 1
+        return out.reshape(*lead, cols)
+
+    def set_qstream_grid(self, grid: int = 0) -> None:
+        """Force the persistent grid of the stream-K kernel (0 = heuristic); sweep/test knob."""
+        self._check(self._lib.b200_set_qstream_grid(int(grid)))
+
+    def set_qstream_trace(self, buf=None) -> None:
+        self._check(self._lib.b200_set_qstream_trace(None if buf is None else buf.data_ptr()))
 
     def set_pdl(self, enabled: bool = True) -> None:
         """Programmatic dependent launch for every kernel of the library (default on)."""

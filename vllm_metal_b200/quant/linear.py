@@ -34,6 +34,7 @@ class QuantizedLinear(nn.Module):
             self.register_buffer("bias", torch.zeros((out_features,), dtype=dtype, device=device))
         else:
             self.bias = None
+        self.swiglu = False
 
     @property
     def in_features(self) -> int:
@@ -89,29 +90,41 @@ class QuantizedLinear(nn.Module):
             m.bias.copy_(self.bias)
         return m
 
-    def prepack(self, keep_mlx_layout: bool = True) -> QuantizedLinear:
-        """Load-time transform into the kernel's streaming layout (``b200_qlinear_prepack``).
+    def prepack(self, keep_mlx_layout: bool = True, swiglu: bool = False) -> QuantizedLinear:
+        """Load-time transform into the streaming blob of the persistent stream-K kernel
+        (``b200_qstream_prepack``).  ``swiglu=True``: rows are ``[gate; up]`` and the call returns
+        ``silu(gate) * up`` (``[.., out_features / 2]``), the fusion of the reference's compiled_mlp.py.
         ``weight`` keeps the MLX layout for loaders / LoRA introspection unless
-        ``keep_mlx_layout=False`` (then it is rebuilt on demand by ``mlx_weight()``)."""
-        if self.scales.dtype != torch.bfloat16 or self.in_features % 64:
-            return self  # the streaming layout is only read by the bf16 tcgen05 kernel
-        wp = get_ops().qlinear_prepack(self.weight, self.bits)
-        self.register_buffer("weight_streaming", wp, persistent=False)
+        ``keep_mlx_layout=False`` (then ``mlx_weight()`` rebuilds it bit-exactly from the blob)."""
+        if self.scales.dtype not in (torch.bfloat16, torch.float16):
+            return self
+        try:
+            blob = get_ops().qstream_prepack(self.weight, self.scales, self.biases, self.group_size, self.bits, swiglu)
+        except ValueError:
+            return self  # a scale/bias outside fp16: stay on the MLX-layout kernels
+        self.register_buffer("weight_blob", blob, persistent=False)
+        self.swiglu = bool(swiglu)
         if not keep_mlx_layout:
-            self.weight = torch.empty((0, self.weight.shape[1]), dtype=torch.int32, device=wp.device)
+            self.weight = torch.empty((0, self.weight.shape[1]), dtype=torch.int32, device=blob.device)
         return self
 
     def mlx_weight(self) -> torch.Tensor:
-        if self.weight.shape[0] or getattr(self, "weight_streaming", None) is None:
+        if self.weight.shape[0] or getattr(self, "weight_blob", None) is None:
             return self.weight
-        return get_ops().qlinear_prepack(self.weight_streaming, self.bits, inverse=True)
+        return get_ops().qstream_unpack(self.weight_blob, self.out_features, self.in_features, self.group_size,
+                                        self.bits, self.swiglu)
+
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        # checkpoints always carry the MLX layout, whatever the resident layout is
+        super()._save_to_state_dict(destination, prefix, keep_vars)
+        if prefix + "weight" in destination and destination[prefix + "weight"].shape[0] == 0:
+            destination[prefix + "weight"] = self.mlx_weight()
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        wp = getattr(self, "weight_streaming", None)
-        if wp is not None and x.dtype == torch.bfloat16:
-            return get_ops().quantized_matmul(x, wp, self.scales, self.biases, transpose=True,
-                                              group_size=self.group_size, bits=self.bits, bias=self.bias,
-                                              prepacked=True)
+        blob = getattr(self, "weight_blob", None)
+        if blob is not None and x.dtype in (torch.bfloat16, torch.float16):
+            return get_ops().qstream_linear(x, blob, self.out_features, self.in_features, self.group_size, self.bits,
+                                            bias=self.bias, swiglu=self.swiglu)
         return get_ops().quantized_matmul(x, self.mlx_weight(), self.scales, self.biases, transpose=True,
                                           group_size=self.group_size, bits=self.bits, bias=self.bias)
 
@@ -145,16 +158,19 @@ class QuantizedEmbedding(nn.Module):
                                     ids=ids, dtype=self.scales.dtype)
 
     def prepack(self) -> QuantizedEmbedding:
-        """Streaming-layout copy for the tied lm_head (``as_linear``); the gather keeps the MLX layout."""
-        if self.scales.dtype == torch.bfloat16 and (self.scales.shape[1] * self.group_size) % 64 == 0:
-            self.register_buffer("weight_streaming", get_ops().qlinear_prepack(self.weight, self.bits),
-                                 persistent=False)
+        """Streaming blob for the tied lm_head (``as_linear``); the row gather keeps the MLX layout."""
+        if self.scales.dtype in (torch.bfloat16, torch.float16):
+            try:
+                blob = get_ops().qstream_prepack(self.weight, self.scales, self.biases, self.group_size, self.bits)
+            except ValueError:
+                return self
+            self.register_buffer("weight_blob", blob, persistent=False)
         return self
 
     def as_linear(self, x: torch.Tensor) -> torch.Tensor:
-        wp = getattr(self, "weight_streaming", None)
-        if wp is not None and x.dtype == torch.bfloat16:
-            return get_ops().quantized_matmul(x, wp, self.scales, self.biases, transpose=True,
-                                              group_size=self.group_size, bits=self.bits, prepacked=True)
+        blob = getattr(self, "weight_blob", None)
+        n, k = self.scales.shape[0], self.scales.shape[1] * self.group_size
+        if blob is not None and x.dtype in (torch.bfloat16, torch.float16):
+            return get_ops().qstream_linear(x, blob, n, k, self.group_size, self.bits)
         return get_ops().quantized_matmul(x, self.weight, self.scales, self.biases, transpose=True,
                                           group_size=self.group_size, bits=self.bits)
