@@ -243,8 +243,12 @@ int b200_dequantize_rows(const uint32_t* w, const void* scales,
  * that reads it.  Fails with B200_ERR_UNSUPPORTED when a scale/bias does not fit fp16 (keep the MLX
  * layout and b200_qlinear then).  b200_qstream_unpack is the bit-exact inverse of the integer part.
  *
- * b200_qstream_linear: x [M, K] bf16/fp16 (row stride x_stride elements), y [M, N] (or [M, N/2] with
- * epilogue = 1), optional dense bias [N] in the x dtype (epilogue 0 only).  `workspace` is
+ * b200_qstream_linear: x [M, K] of x_dtype fp16 or bf16 (row stride x_stride elements), y [M, N] (or
+ * [M, N/2] with epilogue = 1) of `dtype` (bf16/fp16), optional dense bias [N] in `dtype` (epilogue 0 only).
+ * The tensor-core operands are fp16 x fp16 (tcgen05 kind::f16 faults on mixed fp16/bf16 operands, and the
+ * dequantised weights need fp16's 11 significant bits): a bf16 x is first copied to fp16 inside the
+ * workspace (exact below 65504 in magnitude, saturating above; M * K <= 4 Mi elements), so producers that
+ * can emit fp16 directly save that launch.  `workspace` is
  * b200_qstream_workspace_bytes() of device memory, ZERO-initialised once by the caller and shared by
  * all calls on one stream (fp32 partials of super-tiles cut between CTAs + their arrival counters). */
 int64_t b200_qstream_blob_bytes(int N, int K, int bits, int group_size, int swiglu);
@@ -255,9 +259,11 @@ int b200_qstream_prepack(const uint32_t* w, const void* scales, const void* bias
 int b200_qstream_unpack(const void* blob, uint32_t* w_out, int N, int K, int bits,
                         int group_size, int swiglu, void* stream);
 int b200_qstream_linear(const void* x, const void* blob, const void* bias, void* y, int M, int N,
-                        int K, int group_size, int bits, int dtype, int epilogue,
+                        int K, int group_size, int bits, int x_dtype, int dtype, int epilogue,
                         int64_t x_stride, int64_t y_stride, void* workspace,
                         int64_t workspace_bytes, void* stream);
+/* bf16 [rows, cols] (row stride x_stride elements) -> contiguous fp16, saturating at +-65504; cols % 8 == 0. */
+int b200_cast_bf16_to_f16(const void* x, void* y, int rows, int cols, int64_t x_stride, void* stream);
 /* tuning / tracing knobs (0 / NULL = default) */
 int b200_set_qstream_grid(int grid);
 int b200_set_qstream_trace(void* dev_ptr);

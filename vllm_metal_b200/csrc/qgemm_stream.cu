@@ -47,6 +47,7 @@ constexpr int THREADS = (DQ_WARPS + 3 + EPI_WARPS) * 32;  // 736
 constexpr int W_PACKED_BYTES = 2 * 2 * 2 * TILE_ROWS * 16;  // 16 KiB of packed words per unit
 constexpr int EPI_PLAIN = 0, EPI_SWIGLU = 1;
 constexpr int STAGE_M = 64;             // output rows staged per epilogue pass
+constexpr int64_t X16_BYTES = 8ll << 20; // workspace region holding the fp16 copy of a bf16 x (M * K <= 4 Mi elements)
 
 template <int BITS>
 struct Geo {
@@ -74,7 +75,7 @@ struct Params {
   int super_tiles, slabs;  // T2, S
   int m_tiles;
   int64_t y_stride;
-  int x_fp16;              // B operand format: 1 = fp16, 0 = bf16
+  int y_fp16;              // output / bias / SwiGLU rounding dtype: 1 = fp16, 0 = bf16 (x, the B operand, is always fp16)
   unsigned long long* trace;
 };
 
@@ -278,8 +279,8 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
   } else if (warp == W_MMA) {
     // ===== MMA issuer: D[128 x NB] (+)= A[128 x 16] (TMEM, fp16) * B[16 x NB] (smem), two tiles per slab =====
     if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | (0u << 7) | ((p.x_fp16 ? 0u : 1u) << 10) | ((uint32_t)(NB >> 3) << 17) |
-                             ((uint32_t)(TILE_ROWS >> 4) << 24);
+      // fp16 A (TMEM) x fp16 B (smem) -> fp32: kind::f16 faults on mixed fp16/bf16 operands (measured)
+      constexpr uint32_t idesc = make_idesc(0, TILE_ROWS, NB);
       int i = 0, seg = 0;
       long long v = v_begin;
       while (v < v_end) {
@@ -459,7 +460,7 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
 #pragma unroll
               for (int q = 0; q < 16; ++q) {
                 float g, u;
-                if (p.x_fp16) {
+                if (p.y_fp16) {
                   g = __half2float(__float2half_rn(a0[q]));
                   u = __half2float(__float2half_rn(a1[q]));
                   const float sl = __half2float(__float2half_rn(g / (1.f + __expf(-g))));
@@ -479,7 +480,7 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
               float bias0 = 0.f, bias1 = 0.f;
               if (p.bias != nullptr) {
                 const int n0 = n_base + r, n1 = n_base + TILE_ROWS + r;
-                if (p.x_fp16) {
+                if (p.y_fp16) {
                   if (n0 < p.N) bias0 = __half2float(reinterpret_cast<const __half*>(p.bias)[n0]);
                   if (n1 < p.N) bias1 = __half2float(reinterpret_cast<const __half*>(p.bias)[n1]);
                 } else {
@@ -490,7 +491,7 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
 #pragma unroll
               for (int q = 0; q < 16; ++q) {
                 unsigned short o0, o1;
-                if (p.x_fp16) {
+                if (p.y_fp16) {
                   const __half h0 = __float2half_rn(a0[q] + bias0), h1 = __float2half_rn(a1[q] + bias1);
                   o0 = *reinterpret_cast<const unsigned short*>(&h0);
                   o1 = *reinterpret_cast<const unsigned short*>(&h1);
@@ -678,6 +679,32 @@ __global__ void qstream_unpack_kernel(const PackParams p, uint32_t* out) {
   }
 }
 
+// bf16 -> fp16 for the B operand.  Exact for every bf16 whose magnitude is a normal fp16 (8 significant bits fit
+// in 11); magnitudes above 65504 saturate (bf16 activations of that size do not occur after a norm / SwiGLU; the
+// reference would carry them, this path clamps -- stated in DESIGN.md), below 2^-24 round to zero.
+__global__ void cast_bf16_f16_sat_kernel(const __nv_bfloat16* __restrict__ x, __half* __restrict__ y, int rows, int cols,
+                                         int64_t x_stride) {
+  pdl_trigger();
+  pdl_wait();
+  const int vec_per_row = cols >> 3;
+  const int64_t total = (int64_t)rows * vec_per_row;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / vec_per_row), c = (int)(i % vec_per_row) * 8;
+    const uint4 v = *reinterpret_cast<const uint4*>(x + (int64_t)r * x_stride + c);
+    const __nv_bfloat162* b2 = reinterpret_cast<const __nv_bfloat162*>(&v);
+    uint4 o;
+    __half2* h2 = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float2 f = __bfloat1622float2(b2[q]);
+      f.x = fminf(fmaxf(f.x, -65504.f), 65504.f);
+      f.y = fminf(fmaxf(f.y, -65504.f), 65504.f);
+      h2[q] = __floats2half2_rn(f.x, f.y);
+    }
+    *reinterpret_cast<uint4*>(y + (int64_t)r * cols + c) = o;
+  }
+}
+
 // ----------------------------------------------------------------- host side ----
 struct HostArgs {
   const void* x;
@@ -706,8 +733,8 @@ static int launch_cfg(const HostArgs& a, cudaStream_t st) {
     configured_dev[dev] = 1;
   }
   CUtensorMap x_map;
-  int rc = make_map_2d(&x_map, a.dtype == B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
-                       a.x, (uint64_t)a.K, (uint64_t)a.M, (uint64_t)a.x_stride * 2, 64, NB,
+  int rc = make_map_2d(&x_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, a.x, (uint64_t)a.K, (uint64_t)a.M,
+                       (uint64_t)a.x_stride * 2, 64, NB,
                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
   if (rc != B200_OK) return rc;
   Params p;
@@ -724,7 +751,7 @@ static int launch_cfg(const HostArgs& a, cudaStream_t st) {
   p.slabs = (a.K + Geo<BITS>::KS - 1) / Geo<BITS>::KS;
   p.m_tiles = (a.M + NB - 1) / NB;
   p.y_stride = a.y_stride;
-  p.x_fp16 = a.dtype == B200_F16 ? 1 : 0;
+  p.y_fp16 = a.dtype == B200_F16 ? 1 : 0;
   p.trace = g_trace;
   const long long V = (long long)p.super_tiles * p.slabs * p.m_tiles;
   const int sms = sm_count() > 0 ? sm_count() : 148;
@@ -802,8 +829,23 @@ int64_t b200_qstream_blob_bytes(int N, int K, int bits, int group_size, int swig
 
 int64_t b200_qstream_workspace_bytes(void) {
   const int sms = b200::sm_count() > 0 ? b200::sm_count() : 148;
-  // [2 slots per CTA][2 tiles][128 rows][NB <= 64] fp32, + 1 MiB of tile counters at the end
-  return (int64_t)sms * 2 * 2 * b200::qs::TILE_ROWS * 64 * 4 + (1 << 20);
+  // [2 slots per CTA][2 tiles][128 rows][NB <= 64] fp32 | fp16 copy of a bf16 x | 1 MiB of tile counters at the end
+  return (int64_t)sms * 2 * 2 * b200::qs::TILE_ROWS * 64 * 4 + b200::qs::X16_BYTES + (1 << 20);
+}
+
+int b200_cast_bf16_to_f16(const void* x, void* y, int rows, int cols, int64_t x_stride, void* stream) {
+  using namespace b200;
+  B200_CHECK_ARG(rows >= 0 && cols >= 0 && cols % 8 == 0, "cast_bf16_to_f16: cols (%d) must be a multiple of 8", cols);
+  if (rows == 0 || cols == 0) return B200_OK;
+  B200_CHECK_ARG(x && y, "cast_bf16_to_f16: null pointer argument");
+  B200_CHECK_ARG(((uintptr_t)x % 16) == 0 && ((uintptr_t)y % 16) == 0 && (x_stride * 2) % 16 == 0 && x_stride >= cols,
+                 "cast_bf16_to_f16: rows must be 16-byte aligned");
+  const int64_t vecs = (int64_t)rows * (cols / 8);
+  int grid = (int)((vecs + 255) / 256);
+  if (grid > 148 * 8) grid = 148 * 8;
+  B200_CUDA_OK(launch_pdl(qs::cast_bf16_f16_sat_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream,
+                          reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__half*>(y), rows, cols, x_stride));
+  return B200_OK;
 }
 
 int b200_qstream_prepack(const uint32_t* w, const void* scales, const void* biases, void* blob, int N, int K,
@@ -852,13 +894,14 @@ int b200_qstream_unpack(const void* blob, uint32_t* w_out, int N, int K, int bit
 }
 
 int b200_qstream_linear(const void* x, const void* blob, const void* bias, void* y, int M, int N, int K,
-                        int group_size, int bits, int dtype, int epilogue, int64_t x_stride, int64_t y_stride,
-                        void* workspace, int64_t workspace_bytes, void* stream) {
+                        int group_size, int bits, int x_dtype, int dtype, int epilogue, int64_t x_stride,
+                        int64_t y_stride, void* workspace, int64_t workspace_bytes, void* stream) {
   using namespace b200;
   B200_CHECK_ARG(M >= 0, "qstream_linear: M must be >= 0, got %d", M);
   if (M == 0) return B200_OK;
   B200_CHECK_ARG(x && blob && y && workspace, "qstream_linear: null pointer argument");
-  B200_CHECK_ARG(dtype == B200_BF16 || dtype == B200_F16, "qstream_linear: activations must be bf16 or fp16");
+  B200_CHECK_ARG(dtype == B200_BF16 || dtype == B200_F16, "qstream_linear: y must be bf16 or fp16");
+  B200_CHECK_ARG(x_dtype == B200_BF16 || x_dtype == B200_F16, "qstream_linear: x must be bf16 or fp16");
   B200_CHECK_ARG(epilogue == qs::EPI_PLAIN || epilogue == qs::EPI_SWIGLU, "qstream_linear: bad epilogue %d", epilogue);
   B200_CHECK_ARG(!(epilogue == qs::EPI_SWIGLU && bias), "qstream_linear: SwiGLU epilogue takes no dense bias");
   qs::PackParams pp{};
@@ -871,7 +914,18 @@ int b200_qstream_linear(const void* x, const void* blob, const void* bias, void*
   B200_CHECK_ARG(((uintptr_t)blob % 16) == 0 && ((uintptr_t)workspace % 16) == 0, "qstream_linear: blob/workspace alignment");
   B200_CHECK_ARG(tc::encode_fn() != nullptr, "qstream_linear: cuTensorMapEncodeTiled unavailable");
   const int64_t counter_bytes = 1 << 20;
-  B200_CHECK_ARG(workspace_bytes > counter_bytes, "qstream_linear: workspace too small");
+  B200_CHECK_ARG(workspace_bytes > counter_bytes + qs::X16_BYTES, "qstream_linear: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  uint8_t* x16 = reinterpret_cast<uint8_t*>(workspace) + (workspace_bytes - counter_bytes - qs::X16_BYTES);
+  if (x_dtype == B200_BF16) {
+    // the tensor cores take fp16 x fp16 only (A is dequantised to fp16): stage an fp16 copy of x
+    B200_CHECK_ARG((int64_t)M * K * 2 <= qs::X16_BYTES,
+                   "qstream_linear: bf16 x of %d x %d exceeds the staging region; pass fp16 (b200_cast_bf16_to_f16)", M, K);
+    rc = b200_cast_bf16_to_f16(x, x16, M, K, x_stride, stream);
+    if (rc != B200_OK) return rc;
+    x = x16;
+    x_stride = K;
+  }
   const int nb = M <= 16 ? 16 : M <= 32 ? 32 : 64;  // M > 64: 64-row m tiles, weights re-streamed per tile
   B200_CHECK_ARG((int64_t)pp.super_tiles * ((M + nb - 1) / nb) * 4 <= counter_bytes,
                  "qstream_linear: too many (m tile, super-tile) pairs for the counters");
@@ -881,7 +935,7 @@ int b200_qstream_linear(const void* x, const void* blob, const void* bias, void*
   a.bias = bias;
   a.y = y;
   a.workspace = reinterpret_cast<float*>(workspace);
-  a.workspace_bytes = (size_t)(workspace_bytes - counter_bytes);
+  a.workspace_bytes = (size_t)(workspace_bytes - counter_bytes - qs::X16_BYTES);
   a.counters = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(workspace) + (workspace_bytes - counter_bytes));
   a.M = M;
   a.N = N;
@@ -892,7 +946,6 @@ int b200_qstream_linear(const void* x, const void* blob, const void* bias, void*
   a.epi = epilogue;
   a.x_stride = x_stride;
   a.y_stride = y_stride;
-  cudaStream_t st = (cudaStream_t)stream;
   return bits == 4 ? qs::dispatch_g<4>(a, st) : qs::dispatch_g<8>(a, st);
 }
 

@@ -104,6 +104,7 @@ EXPORTED_SYMBOLS = (
     "b200_qstream_prepack",
     "b200_qstream_unpack",
     "b200_qstream_linear",
+    "b200_cast_bf16_to_f16",
     "b200_set_qstream_grid",
     "b200_set_qstream_trace",
     "b200_rms_norm",
@@ -165,7 +166,8 @@ def load_library() -> ctypes.CDLL:
     lib.b200_qstream_workspace_bytes.restype = ctypes.c_int64
     lib.b200_qstream_prepack.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     lib.b200_qstream_unpack.argtypes = [vp, vp, i32, i32, i32, i32, i32, vp]
-    lib.b200_qstream_linear.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i64, i64, vp, i64, vp]
+    lib.b200_qstream_linear.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, vp, i64, vp]
+    lib.b200_cast_bf16_to_f16.argtypes = [vp, vp, i32, i32, i64, vp]
     lib.b200_set_qstream_grid.argtypes = [i32]
     lib.b200_set_qstream_trace.argtypes = [vp]
     lib.b200_rms_norm.argtypes = [vp, vp, vp, vp, i32, i32, i64, i64, i64, f32, i32, vp]
@@ -506,9 +508,10 @@ class _Ops:
         return ws
 
     def qstream_linear(self, x, blob, n_out: int, k: int, group_size: int = 64, bits: int = 4, bias=None,
-                       swiglu: bool = False, out=None):
+                       swiglu: bool = False, out=None, out_dtype: torch.dtype | None = None):
         """``x @ W'^T (+ bias)`` over a streaming blob; ``swiglu=True`` returns ``silu(gate) * up``
-        (``[.., n_out / 2]``) from a blob packed with ``swiglu=True``."""
+        (``[.., n_out / 2]``) from a blob packed with ``swiglu=True``.  ``x`` may be fp16 while the result
+        is bf16 (``out_dtype``): the kernel's operands are fp16, a bf16 ``x`` is staged as fp16 first."""
         _require_cuda("x", x)
         _require_cuda("blob", blob)
         if x.shape[-1] != k:
@@ -520,17 +523,31 @@ class _Ops:
         m = x2.shape[0]
         cols = n_out // 2 if swiglu else n_out
         if out is None:
-            out = torch.empty((m, cols), dtype=x.dtype, device=x.device)
+            out = torch.empty((m, cols), dtype=out_dtype or x.dtype, device=x.device)
         y2 = out.reshape(m, cols)
         if bias is not None:
-            bias = bias.to(dtype=x.dtype).contiguous()
+            bias = bias.to(dtype=out.dtype).contiguous()
+        if x2.dtype == torch.bfloat16 and m * k * 2 > (8 << 20):
+            x2 = self.cast_f16(x2)  # larger than the in-workspace staging region
         ws = self._qstream_workspace(x.device)
         rc = self._lib.b200_qstream_linear(
             x2.data_ptr(), blob.data_ptr(), _ptr(bias), y2.data_ptr(), m, n_out, k, group_size, bits,
-            _dtype_code("x", x), int(swiglu), x2.stride(0), y2.stride(0), ws.data_ptr(), ws.numel(), _stream())
+            _dtype_code("x", x2), _dtype_code("out", out), int(swiglu), x2.stride(0), y2.stride(0), ws.data_ptr(),
+            ws.numel(), _stream())
         self._check(rc)
-        self.launches += 1
+        self.launches += 2 if x2.dtype == torch.bfloat16 else 1
         return out.reshape(*lead, cols)
+
+    def cast_f16(self, x):
+        """bf16 ``[rows, cols]`` -> contiguous fp16, saturating at +-65504 (the stream-K kernel's operand type)."""
+        _require_cuda("x", x)
+        if x.dtype != torch.bfloat16 or x.dim() != 2 or x.stride(1) != 1:
+            raise ValueError("cast_f16 takes a 2-D bf16 tensor with unit inner stride")
+        y = torch.empty(x.shape, dtype=torch.float16, device=x.device)
+        self._check(self._lib.b200_cast_bf16_to_f16(x.data_ptr(), y.data_ptr(), x.shape[0], x.shape[1], x.stride(0),
+                                                    _stream()))
+        self.launches += 1
+        return y
 
     def set_qstream_grid(self, grid: int = 0) -> None:
         """Force the persistent grid of the stream-K kernel (0 = heuristic); sweep/test knob."""
