@@ -76,9 +76,14 @@ def main():
     ap.add_argument("--shapes", default="")
     ap.add_argument("--legacy", action="store_true")
     ap.add_argument("--trace", action="store_true")
+    ap.add_argument("--no-pdl", action="store_true")
+    ap.add_argument("--x16", action="store_true", help="fp16 x (no staging cast launch)")
+    ap.add_argument("--units", type=int, default=0, help="with --trace: print CTA 0's first N per-unit pipeline stamps")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     ops = get_ops()
+    if args.no_pdl:
+        ops.set_pdl(False)
     gen = torch.Generator(device="cuda").manual_seed(0)
     bits, shapes = MODELS[args.model]
     m, g = args.m, args.group
@@ -98,6 +103,8 @@ def main():
             if args.legacy and len(mlx) < copies:
                 mlx.append((w, s, b))
         x = torch.randn((m, k), device="cuda", generator=gen).bfloat16()
+        if args.x16:
+            x = x.half()
         n_out = n // 2 if swiglu else n
         y = torch.empty((m, n_out), device="cuda", dtype=torch.bfloat16)
         nbytes = n * k * (bits / 8 + 4 / g) + m * (k + n_out) * 2
@@ -115,19 +122,38 @@ def main():
             row["legacy_us"] = us
             line += f" round-1 kernel: {us:7.2f} us ({(n * k * (bits / 8 + 4 / g) + m * (k + n) * 2) / us / 1e3 / PEAK:4.2f})"
         if args.trace:
-            tr = torch.zeros((148 * 16,), dtype=torch.int64, device="cuda")
+            tr = torch.zeros((148 * 16 + 64 * 8,), dtype=torch.int64, device="cuda")
             ops.set_qstream_trace(tr)
+            flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
             ops.qstream_linear(x, blobs[0], n, k, g, bits, swiglu=bool(swiglu), out=y)
+            e1.record()
             torch.cuda.synchronize()
+            line += f"\n             single cold launch (events, incl. cast): {e0.elapsed_time(e1) * 1e3:.2f} us"
+            del flush
             ops.set_qstream_trace(None)
-            t = tr.view(148, 16).cpu()
+            units = tr[148 * 16:].view(64, 8).cpu()
+            t = tr[:148 * 16].view(148, 16).cpu()
             act = t[:, 0] > 0
             t0 = t[act, 0].min()
-            rel = (t[act][:, :5] - t0).float() / 1e3
+            rel = (t[act][:, :11] - t0).float() / 1e3
             line += (f"\n             trace (us, mean/max over {int(act.sum())} CTAs): start {rel[:, 0].mean():.2f}/{rel[:, 0].max():.2f}"
                      f" setup {rel[:, 1].mean():.2f}/{rel[:, 1].max():.2f} x-ready {rel[:, 2].mean():.2f}/{rel[:, 2].max():.2f}"
-                     f" dequant-done {rel[:, 3].mean():.2f}/{rel[:, 3].max():.2f} end {rel[:, 4].mean():.2f}/{rel[:, 4].max():.2f}")
+                     f" first-w {rel[:, 5].mean():.2f}/{rel[:, 5].max():.2f} epi-pdl {rel[:, 9].mean():.2f}/{rel[:, 9].max():.2f}"
+                     f" dequant-done {rel[:, 3].mean():.2f}/{rel[:, 3].max():.2f} mma-done {rel[:, 6].mean():.2f}/{rel[:, 6].max():.2f}"
+                     f" first-acc {rel[:, 7].mean():.2f}/{rel[:, 7].max():.2f} epi-done {rel[:, 8].mean():.2f}/{rel[:, 8].max():.2f}"
+                     f" finish-done {rel[:, 10].mean():.2f}/{rel[:, 10].max():.2f}")
         print(line, flush=True)
+        if args.trace and args.units:
+            c0 = int(units[0, 0])
+            print("             CTA 0 per-unit SM clocks since its first w_full: w_full | math done | a_empty | STTM+arrive || a_full(mma) | committed")
+            for i in range(min(args.units, 64)):
+                u = units[i]
+                if int(u[0]) == 0:
+                    break
+                print(f"             unit {i:2d}: {int(u[0]) - c0:7d} {int(u[1]) - c0:7d} {int(u[2]) - c0:7d} {int(u[5]) - c0:7d} || {int(u[3]) - c0:7d} {int(u[4]) - c0:7d}")
         res["shapes"][name] = row
         del blobs, mlx
         torch.cuda.empty_cache()

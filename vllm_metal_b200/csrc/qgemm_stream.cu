@@ -69,7 +69,7 @@ struct Params {
   const void* bias;        // dense [N] in the x dtype, or null (EPI_PLAIN only)
   void* y;
   float* workspace;        // [2 * grid][2][128][NB] fp32 partial accumulators
-  int* counters;           // [m_tiles * super_tiles], zero between launches
+  int* counters;           // arrivals [m_tiles * super_tiles] | finished [..] at +2^17 ints; zero between launches
   int M, N, K;             // N = weight rows (2*I for SwiGLU)
   int n_out;               // output columns: N, or I for SwiGLU
   int super_tiles, slabs;  // T2, S
@@ -146,6 +146,56 @@ __device__ __forceinline__ void trace_stamp(const Params& p, int slot) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     p.trace[(size_t)blockIdx.x * 16 + slot] = t;
+  }
+}
+
+// fine-grained pipeline trace of CTA 0 (SM clock): event e of unit i at trace[148 * 16 + i * 8 + e], i < 64
+__device__ __forceinline__ void unit_stamp(const Params& p, int i, int e) {
+  if (p.trace != nullptr && blockIdx.x == 0 && i < 64) {
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
+    p.trace[148 * 16 + i * 8 + e] = (unsigned long long)t;
+  }
+}
+
+
+__device__ __forceinline__ int ld_acquire_gpu(const int* ptr) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(ptr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint16_t to_out16(float v, int fp16) {
+  if (fp16) {
+    const __half h = __float2half_rn(v);
+    return *reinterpret_cast<const uint16_t*>(&h);
+  }
+  const __nv_bfloat16 h = __float2bfloat16_rn(v);
+  return *reinterpret_cast<const uint16_t*>(&h);
+}
+__device__ __forceinline__ float round_out(float v, int fp16) {
+  return fp16 ? __half2float(__float2half_rn(v)) : __bfloat162float(__float2bfloat16_rn(v));
+}
+// gate and up are rounded to the activation dtype first, as the unfused sequence stores them
+// (oracle/decoder.py silu_mul: silu rounded, then the product rounded)
+__device__ __forceinline__ uint16_t swiglu_out(float gate, float up, int fp16) {
+  const float g = round_out(gate, fp16), u = round_out(up, fp16);
+  const float sl = round_out(g / (1.f + __expf(-g)), fp16);
+  return to_out16(sl * u, fp16);
+}
+__device__ __forceinline__ float load_bias(const Params& p, int n) {
+  if (p.bias == nullptr || n >= p.N) return 0.f;
+  return p.y_fp16 ? __half2float(reinterpret_cast<const __half*>(p.bias)[n])
+                  : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[n]);
+}
+// four consecutive outputs n..n+3 of one y row
+__device__ __forceinline__ void store_out4(uint16_t* yrow, int n, int n_out, const uint16_t (&o)[4], bool vec_ok) {
+  if (n >= n_out) return;
+  if (vec_ok && n + 4 <= n_out) {
+    *reinterpret_cast<uint2*>(yrow + n) = make_uint2((uint32_t)o[0] | ((uint32_t)o[1] << 16), (uint32_t)o[2] | ((uint32_t)o[3] << 16));
+  } else {
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (n + q < n_out) yrow[n + q] = o[q];
   }
 }
 
@@ -246,74 +296,111 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
   const uint32_t tmem_base = *tmem_ptr_gen;
   if (threadIdx.x == 0) trace_stamp(p, 1);
 
+  // The three single-issuer roles run their loops with the WHOLE warp (uniform control flow, uniform operands)
+  // and issue under elect_one(): see tcgen05.cuh.
+  const int vb = (int)v_begin, ve = (int)v_end, Ui = (int)U;
   if (warp == W_WPROD) {
     // ===== weight blobs: one bulk copy per unit; constants, so no pdl_wait (see b200_qstream header note) =====
-    if (lane == 0) {
-      int i = 0;
-      for (long long v = v_begin; v < v_end; ++v, ++i) {
-        const int st = i % WST;
-        mbar_wait(bar_w_empty + 8 * st, ((i / WST) & 1) ^ 1);
+    int st = 0;
+    uint32_t ph = 1;
+    int u = vb % Ui;
+    for (int v = vb; v < ve; ++v) {
+      mbar_wait(bar_w_empty + 8 * st, ph);
+#ifdef QS_ABL_NO_W
+      if (v - vb >= WST) {
+        if (elect_one()) mbar_arrive(bar_w_full + 8 * st);
+      } else
+#endif
+      if (elect_one()) {
         mbar_expect_tx(bar_w_full + 8 * st, WB);
-        bulk_load(sm_w + st * WB, p.blob + (size_t)(v % U) * WB, WB, bar_w_full + 8 * st);
+        bulk_load(sm_w + st * WB, p.blob + (size_t)u * WB, WB, bar_w_full + 8 * st);
       }
+      __syncwarp();
+      if (++u == Ui) u = 0;
+      if (++st == WST) { st = 0; ph ^= 1; }
     }
-    __syncwarp();
   } else if (warp == W_XPROD) {
     // ===== x tiles (B operand): [NB rows x KS k], 128B-swizzled K-major, through the tensor map =====
-    if (lane == 0) {
-      pdl_wait();  // x is the previous kernel's output
-      trace_stamp(p, 2);
-      int i = 0;
-      for (long long v = v_begin; v < v_end; ++v, ++i) {
-        const int st = i % XST;
-        const int mt = (int)(v / U);
-        const int j = (int)((v % U) % p.slabs);
-        mbar_wait(bar_x_empty + 8 * st, ((i / XST) & 1) ^ 1);
+    pdl_wait();  // x is the previous kernel's output
+    if (lane == 0) trace_stamp(p, 2);
+    int st = 0;
+    uint32_t ph = 1;
+    int mt = vb / Ui;
+    int j = (vb % Ui) % p.slabs, T = (vb % Ui) / p.slabs;
+    for (int v = vb; v < ve; ++v) {
+      mbar_wait(bar_x_empty + 8 * st, ph);
+#ifdef QS_ABL_NO_X
+      if (v - vb >= XST) {
+        if (elect_one()) mbar_arrive(bar_x_full + 8 * st);
+      } else
+#endif
+      if (elect_one()) {
         mbar_expect_tx(bar_x_full + 8 * st, XB);
 #pragma unroll
         for (int b = 0; b < XBOXES; ++b)
           tma_load_2d(sm_x + st * XB + b * (NB * 128), &x_map, bar_x_full + 8 * st, j * KS + b * 64, mt * NB);
       }
+      __syncwarp();
+      if (++j == p.slabs) {
+        j = 0;
+        if (++T == p.super_tiles) { T = 0; ++mt; }
+      }
+      if (++st == XST) { st = 0; ph ^= 1; }
     }
-    __syncwarp();
   } else if (warp == W_MMA) {
     // ===== MMA issuer: D[128 x NB] (+)= A[128 x 16] (TMEM, fp16) * B[16 x NB] (smem), two tiles per slab =====
-    if (lane == 0) {
-      // fp16 A (TMEM) x fp16 B (smem) -> fp32: kind::f16 faults on mixed fp16/bf16 operands (measured)
-      constexpr uint32_t idesc = make_idesc(0, TILE_ROWS, NB);
-      int i = 0, seg = 0;
-      long long v = v_begin;
-      while (v < v_end) {
-        const long long tile_id = v / p.slabs;
-        const long long seg_end = min((tile_id + 1) * (long long)p.slabs, v_end);
-        const int buf = seg % ACC_BUFS;
-        mbar_wait(bar_acc_empty + 8 * buf, ((seg / ACC_BUFS) & 1) ^ 1);
+    // fp16 A (TMEM) x fp16 B (smem) -> fp32: kind::f16 faults on mixed fp16/bf16 operands (measured)
+    constexpr uint32_t idesc = make_idesc(0, TILE_ROWS, NB);
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);  // warp-uniform for ptxas
+    int xs = 0, as = 0, seg = 0;
+    uint32_t xph = 0, aph = 0;
+    int v = vb;
+    while (v < ve) {
+      const int tile_id = v / p.slabs;
+      const int seg_end = min((tile_id + 1) * p.slabs, ve);
+      const int buf = seg % ACC_BUFS;
+      mbar_wait(bar_acc_empty + 8 * buf, ((seg / ACC_BUFS) & 1) ^ 1);
+      uint32_t acc = 0;  // the first k step of a segment overwrites the accumulator (both tiles)
+      for (; v < seg_end; ++v) {
+        mbar_wait(bar_x_full + 8 * xs, xph);
+        mbar_wait(bar_a_full + 8 * as, aph);
+#ifdef QS_UNIT_TRACE
+        if (lane == 0) unit_stamp(p, v - vb, 3);
+#endif
         tc_fence_after();
-        bool first = true;
-        for (; v < seg_end; ++v, ++i) {
-          const int xs = i % XST, as = i % AS;
-          mbar_wait(bar_x_full + 8 * xs, (i / XST) & 1);
-          mbar_wait(bar_a_full + 8 * as, (i / AS) & 1);
-          tc_fence_after();
+        if (elect_one()) {
+          const uint64_t db0 = make_smem_desc(sm_x + xs * XB);
 #pragma unroll
           for (int t = 0; t < 2; ++t) {
-            const uint32_t d = tmem_base + TM_ACC + (buf * 2 + t) * ACC_COLS;
-            const uint32_t a = tmem_base + TM_A + (as * 2 + t) * A_COLS;
+            const uint32_t d = tb + TM_ACC + (buf * 2 + t) * ACC_COLS;
+            const uint32_t a = tb + TM_A + (as * 2 + t) * A_COLS;
 #pragma unroll
             for (int k = 0; k < MMAS; ++k) {
-              const uint64_t db = make_smem_desc(sm_x + xs * XB + (k >> 2) * (NB * 128)) + 2 * (k & 3);
-              tc_mma_f16_ts(d, a + 8 * k, db, idesc, (first && k == 0) ? 0u : 1u);
+              // k-step inside a 128B swizzle atom: +32 B (>>4 = 2); next atom (64 k): + NB * 128 B
+              const uint64_t db = db0 + (uint64_t)((k >> 2) * ((NB * 128) >> 4) + 2 * (k & 3));
+#ifndef QS_ABL_NO_MMA
+              tc_mma_f16_ts(d, a + 8 * k, db, idesc, k == 0 ? acc : 1u);
+#else
+              (void)d; (void)a; (void)db;
+#endif
             }
           }
-          first = false;
           tc_commit(bar_x_empty + 8 * xs);
           tc_commit(bar_a_empty + 8 * as);
         }
-        tc_commit(bar_acc_full + 8 * buf);
-        ++seg;
+        __syncwarp();
+        acc = 1u;
+#ifdef QS_UNIT_TRACE
+        if (lane == 0) unit_stamp(p, v - vb, 4);
+#endif
+        if (++xs == XST) { xs = 0; xph ^= 1; }
+        if (++as == AS) { as = 0; aph ^= 1; }
       }
+      if (elect_one()) tc_commit(bar_acc_full + 8 * buf);
+      __syncwarp();
+      ++seg;
     }
-    __syncwarp();
+    if (lane == 0) trace_stamp(p, 6);
   } else if (warp < DQ_WARPS) {
     // ===== dequant: thread = (tile t, k-half h, row r); 32 B packed -> KT fp16 -> TMEM =====
     const int th = warp >> 2;                 // t * 2 + h
@@ -327,6 +414,10 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
     for (long long v = v_begin; v < v_end; ++v, ++i) {
       const int ws = i % WST, as = i % AS;
       mbar_wait(bar_w_full + 8 * ws, (i / WST) & 1);
+      if (i == 0 && threadIdx.x == 0) trace_stamp(p, 5);
+#ifdef QS_UNIT_TRACE
+      if (threadIdx.x == 0) unit_stamp(p, i, 0);
+#endif
       const uint32_t wbase = sm_w + ws * WB;
       uint4 pk0, pk1;
       asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pk0.x), "=r"(pk0.y), "=r"(pk0.z), "=r"(pk0.w) : "r"(wbase + w_off0));
@@ -339,58 +430,77 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_w_empty + 8 * ws);
       const uint32_t words[8] = {pk0.x, pk0.y, pk0.z, pk0.w, pk1.x, pk1.y, pk1.z, pk1.w};
+      __half2 s2[NG], b2[NG];
+#pragma unroll
+      for (int g = 0; g < NG; ++g) {
+        s2[g] = u32_as_h2(__byte_perm(sb[g], 0, 0x1010));
+        b2[g] = u32_as_h2(__byte_perm(sb[g], 0, 0x3232));
+      }
       uint32_t av[KT / 2];
+#ifdef QS_ABL_NO_MATH
+#pragma unroll
+      for (int q = 0; q < KT / 2; ++q) av[q] = words[q & 7] ^ sb[0];
+      if (false)
+#endif
       if constexpr (BITS == 4) {
 #pragma unroll
-        for (int wi = 0; wi < 8; ++wi) {
-          const uint32_t e = sb[NG == 2 ? (wi >> 2) : 0];
-          const __half2 s2 = u32_as_h2(__byte_perm(e, 0, 0x1010));
-          const __half2 b2 = u32_as_h2(__byte_perm(e, 0, 0x3232));
-          dequant_word4(words[wi], s2, b2, av + 4 * wi);
-        }
+        for (int wi = 0; wi < 8; ++wi) dequant_word4(words[wi], s2[NG == 2 ? (wi >> 2) : 0], b2[NG == 2 ? (wi >> 2) : 0], av + 4 * wi);
       } else {
 #pragma unroll
-        for (int wi = 0; wi < 8; ++wi) {
-          const uint32_t e = sb[NG == 2 ? (wi >> 2) : 0];
-          const __half2 s2 = u32_as_h2(__byte_perm(e, 0, 0x1010));
-          const __half2 b2 = u32_as_h2(__byte_perm(e, 0, 0x3232));
-          dequant_word8(words[wi], s2, b2, av + 2 * wi);
-        }
+        for (int wi = 0; wi < 8; ++wi) dequant_word8(words[wi], s2[NG == 2 ? (wi >> 2) : 0], b2[NG == 2 ? (wi >> 2) : 0], av + 2 * wi);
       }
       // the math ran ahead of the ring: only the TMEM store waits for the slot (MMA of slab i - AS done)
+#ifdef QS_UNIT_TRACE
+      if (threadIdx.x == 0) unit_stamp(p, i, 1);
+#endif
       mbar_wait(bar_a_empty + 8 * as, ((i / AS) & 1) ^ 1);
+#ifdef QS_UNIT_TRACE
+      if (threadIdx.x == 0) unit_stamp(p, i, 2);
+#endif
       tc_fence_after();
       const uint32_t taddr = tmem_base + lane_addr + TM_A + (as * 2 + t) * A_COLS + h * (KT / 2);
+#ifndef QS_ABL_NO_STTM
       if constexpr (BITS == 4) tmem_st32(taddr, av); else tmem_st16(taddr, av);
+#else
+      if (av[0] == 0x12345678u && av[KT / 2 - 1] == 0x9abcdef0u) tmem_st16(taddr, reinterpret_cast<const uint32_t(&)[16]>(av));
+#endif
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_a_full + 8 * as);
+#ifdef QS_UNIT_TRACE
+      if (threadIdx.x == 0) unit_stamp(p, i, 5);
+#endif
     }
     if (threadIdx.x == 0) trace_stamp(p, 3);
   } else {
     // ===== epilogue warps: TMEM lane quarter = warp % 4; thread <-> weight row r of both tiles =====
-    const int ew = warp - W_EPI;               // 0..3: which staged rows this warp stores
     const int r = (warp & 3) * 32 + lane;
+    const int ew = warp & 3;
     const int et = threadIdx.x - W_EPI * 32;   // 0..127
     const uint32_t lane_addr = ((uint32_t)((warp & 3) * 32) << 16);
+    constexpr int OUT_COLS = EPI == EPI_SWIGLU ? TILE_ROWS : SUPER_ROWS;
+    uint16_t* yp = reinterpret_cast<uint16_t*>(p.y);
     pdl_wait();  // y, the workspace and the counters may still be in use by the previous kernel
+    if (et == 0) trace_stamp(p, 9);
+    int pend_tile[2];   // super-tiles this CTA holds a piece of (cut by a CTA boundary): finished after the stream
+    int npend = 0;
     int seg = 0;
-    long long v = v_begin;
-    while (v < v_end) {
-      const long long tile_id = v / p.slabs;  // mt * super_tiles + T
-      const int j0 = (int)(v - tile_id * p.slabs);
-      const long long seg_end = min((tile_id + 1) * (long long)p.slabs, v_end);
-      const int j1 = (int)(seg_end - tile_id * p.slabs);
-      const int mt = (int)(tile_id / p.super_tiles), T = (int)(tile_id % p.super_tiles);
+    int v = (int)v_begin;
+    const int ve = (int)v_end;
+    while (v < ve) {
+      const int tile_id = v / p.slabs;  // mt * super_tiles + T
+      const int j0 = v - tile_id * p.slabs;
+      const int seg_end = min((tile_id + 1) * p.slabs, ve);
+      const int j1 = seg_end - tile_id * p.slabs;
+      const int mt = tile_id / p.super_tiles, T = tile_id % p.super_tiles;
       const int buf = seg % ACC_BUFS;
       const bool whole = (j0 == 0 && j1 == p.slabs);
       mbar_wait(bar_acc_full + 8 * buf, (seg / ACC_BUFS) & 1);
+      if (seg == 0 && et == 0) trace_stamp(p, 7);
       tc_fence_after();
       const uint32_t acc0 = tmem_base + lane_addr + TM_ACC + (buf * 2) * ACC_COLS;
-      bool finish = whole;
-      int c_first = 0, nseg = 1;
       if (!whole) {
-        // park the fp32 partial, then find out whether every other piece of this super-tile is in
+        // park the fp32 partial as [tile t][column c][row r] (coalesced both here and in the finish), publish it
         float* slot = p.workspace + ((size_t)(2 * blockIdx.x + (j0 == 0 ? 1 : 0)) * 2 * TILE_ROWS) * NB;
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
@@ -398,11 +508,8 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
           for (int c0 = 0; c0 < NB; c0 += 16) {
             uint32_t vv[16];
             tmem_ld<16>(acc0 + t * ACC_COLS + c0, vv);
-            float4* dst = reinterpret_cast<float4*>(slot + ((size_t)t * TILE_ROWS + r) * NB + c0);
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
-              __stcg(dst + q, make_float4(__uint_as_float(vv[4 * q]), __uint_as_float(vv[4 * q + 1]),
-                                          __uint_as_float(vv[4 * q + 2]), __uint_as_float(vv[4 * q + 3])));
+            for (int q = 0; q < 16; ++q) __stcg(slot + ((size_t)(t * NB + c0 + q)) * TILE_ROWS + r, __uint_as_float(vv[q]));
           }
         }
         tc_fence_before();
@@ -410,28 +517,16 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
         if (lane == 0) mbar_arrive(bar_acc_empty + 8 * buf);
         __threadfence();
         named_bar_sync(1, EPI_WARPS * 32);
-        const long long v_first = tile_id * p.slabs;
-        c_first = cta_of(v_first, V, P);
-        nseg = cta_of(v_first + p.slabs - 1, V, P) - c_first + 1;
-        if (et == 0) {
-          const int old = atomicAdd(p.counters + tile_id, 1);
-          *flag_gen = (old == nseg - 1) ? 1 : 0;
-          if (old == nseg - 1) p.counters[tile_id] = 0;  // re-arm for the next launch (graph replay)
-        }
-        named_bar_sync(1, EPI_WARPS * 32);
-        finish = (*flag_gen != 0);
-        if (finish) __threadfence();
-        named_bar_sync(1, EPI_WARPS * 32);  // flag consumed before the next segment may overwrite it
-      }
-      if (finish) {
+        if (et == 0) atomicAdd(p.counters + tile_id, 1);
+        pend_tile[npend++] = tile_id;
+      } else {
         const int n_base = EPI == EPI_SWIGLU ? T * TILE_ROWS : T * SUPER_ROWS;  // first output column of this tile
-        constexpr int OUT_COLS = EPI == EPI_SWIGLU ? TILE_ROWS : SUPER_ROWS;
         for (int mh = 0; mh < NB; mh += STAGE_M) {
           constexpr int MH = NB < STAGE_M ? NB : STAGE_M;
 #pragma unroll 1
           for (int c0 = mh; c0 < mh + MH; c0 += 16) {
             float a0[16], a1[16];
-            if (whole) {
+            {
               uint32_t vv[16];
               tmem_ld<16>(acc0 + c0, vv);
 #pragma unroll
@@ -439,74 +534,24 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
               tmem_ld<16>(acc0 + ACC_COLS + c0, vv);
 #pragma unroll
               for (int q = 0; q < 16; ++q) a1[q] = __uint_as_float(vv[q]);
-            } else {
-#pragma unroll
-              for (int q = 0; q < 16; ++q) a0[q] = a1[q] = 0.f;
-              for (int sgi = 0; sgi < nseg; ++sgi) {  // k order: deterministic whatever the arrival order
-                const float* slot = p.workspace + ((size_t)(2 * (c_first + sgi) + (sgi == 0 ? 1 : 0)) * 2 * TILE_ROWS) * NB;
-                const float4* s0 = reinterpret_cast<const float4*>(slot + (size_t)r * NB + c0);
-                const float4* s1 = reinterpret_cast<const float4*>(slot + ((size_t)TILE_ROWS + r) * NB + c0);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  const float4 u0 = __ldcg(s0 + q), u1 = __ldcg(s1 + q);
-                  a0[4 * q] += u0.x; a0[4 * q + 1] += u0.y; a0[4 * q + 2] += u0.z; a0[4 * q + 3] += u0.w;
-                  a1[4 * q] += u1.x; a1[4 * q + 1] += u1.y; a1[4 * q + 2] += u1.z; a1[4 * q + 3] += u1.w;
-                }
-              }
             }
             if constexpr (EPI == EPI_SWIGLU) {
-              // gate and up are rounded to the activation dtype first, as the unfused sequence stores them
-              // (oracle/decoder.py silu_mul: silu rounded, then the product rounded)
 #pragma unroll
               for (int q = 0; q < 16; ++q) {
-                float g, u;
-                if (p.y_fp16) {
-                  g = __half2float(__float2half_rn(a0[q]));
-                  u = __half2float(__float2half_rn(a1[q]));
-                  const float sl = __half2float(__float2half_rn(g / (1.f + __expf(-g))));
-                  const __half o = __float2half_rn(sl * u);
-                  asm volatile("st.shared.u16 [%0], %1;" ::"r"(sm_stage + (uint32_t)(((c0 - mh + q) * OUT_COLS + r) * 2)),
-                               "h"(*reinterpret_cast<const unsigned short*>(&o)) : "memory");
-                } else {
-                  g = __bfloat162float(__float2bfloat16_rn(a0[q]));
-                  u = __bfloat162float(__float2bfloat16_rn(a1[q]));
-                  const float sl = __bfloat162float(__float2bfloat16_rn(g / (1.f + __expf(-g))));
-                  const __nv_bfloat16 o = __float2bfloat16_rn(sl * u);
-                  asm volatile("st.shared.u16 [%0], %1;" ::"r"(sm_stage + (uint32_t)(((c0 - mh + q) * OUT_COLS + r) * 2)),
-                               "h"(*reinterpret_cast<const unsigned short*>(&o)) : "memory");
-                }
+                const uint16_t o = swiglu_out(a0[q], a1[q], p.y_fp16);
+                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sm_stage + (uint32_t)(((c0 - mh + q) * OUT_COLS + r) * 2)), "h"(o) : "memory");
               }
             } else {
-              float bias0 = 0.f, bias1 = 0.f;
-              if (p.bias != nullptr) {
-                const int n0 = n_base + r, n1 = n_base + TILE_ROWS + r;
-                if (p.y_fp16) {
-                  if (n0 < p.N) bias0 = __half2float(reinterpret_cast<const __half*>(p.bias)[n0]);
-                  if (n1 < p.N) bias1 = __half2float(reinterpret_cast<const __half*>(p.bias)[n1]);
-                } else {
-                  if (n0 < p.N) bias0 = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[n0]);
-                  if (n1 < p.N) bias1 = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[n1]);
-                }
-              }
+              const float bias0 = load_bias(p, n_base + r), bias1 = load_bias(p, n_base + TILE_ROWS + r);
 #pragma unroll
               for (int q = 0; q < 16; ++q) {
-                unsigned short o0, o1;
-                if (p.y_fp16) {
-                  const __half h0 = __float2half_rn(a0[q] + bias0), h1 = __float2half_rn(a1[q] + bias1);
-                  o0 = *reinterpret_cast<const unsigned short*>(&h0);
-                  o1 = *reinterpret_cast<const unsigned short*>(&h1);
-                } else {
-                  const __nv_bfloat16 h0 = __float2bfloat16_rn(a0[q] + bias0), h1 = __float2bfloat16_rn(a1[q] + bias1);
-                  o0 = *reinterpret_cast<const unsigned short*>(&h0);
-                  o1 = *reinterpret_cast<const unsigned short*>(&h1);
-                }
                 const uint32_t row = sm_stage + (uint32_t)((c0 - mh + q) * OUT_COLS * 2);
-                asm volatile("st.shared.u16 [%0], %1;" ::"r"(row + (uint32_t)(r * 2)), "h"(o0) : "memory");
-                asm volatile("st.shared.u16 [%0], %1;" ::"r"(row + (uint32_t)((TILE_ROWS + r) * 2)), "h"(o1) : "memory");
+                asm volatile("st.shared.u16 [%0], %1;" ::"r"(row + (uint32_t)(r * 2)), "h"(to_out16(a0[q] + bias0, p.y_fp16)) : "memory");
+                asm volatile("st.shared.u16 [%0], %1;" ::"r"(row + (uint32_t)((TILE_ROWS + r) * 2)), "h"(to_out16(a1[q] + bias1, p.y_fp16)) : "memory");
               }
             }
           }
-          if (whole && mh + STAGE_M >= NB) {  // last TMEM read of this buffer: give it back to the MMA warp
+          if (mh + STAGE_M >= NB) {  // last TMEM read of this buffer: give it back to the MMA warp
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_acc_empty + 8 * buf);
@@ -515,7 +560,6 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
           // staged [MH rows][OUT_COLS] -> y, one 16-byte vector per lane; a warp covers 512 B of a row
           {
             constexpr int VEC_PER_ROW = OUT_COLS / 8;
-            uint16_t* yp = reinterpret_cast<uint16_t*>(p.y);
             const bool vec_ok = (p.y_stride % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15) == 0);
             for (int idx = et; idx < MH * VEC_PER_ROW; idx += EPI_WARPS * 32) {
               const int mr = idx / VEC_PER_ROW, vc = idx % VEC_PER_ROW;
@@ -540,7 +584,86 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
       v = seg_end;
       ++seg;
     }
-    (void)ew;
+    if (et == 0) trace_stamp(p, 8);
+
+    // ----- finish the cut super-tiles: the CTAs that hold pieces of one split its columns between them; each
+    // waits until every piece is published, then adds them in k ORDER (deterministic whatever the timing).
+    // Lane l owns rows 4l..4l+3 (16-byte loads of the [t][c][r] partials), warp w takes every 4th column. -----
+    int* done = p.counters + (1 << 17);
+    for (int pi = 0; pi < npend; ++pi) {
+      const int tile_id = pend_tile[pi];
+      const int mt = tile_id / p.super_tiles, T = tile_id % p.super_tiles;
+      const long long v_first = (long long)tile_id * p.slabs;
+      const int c_first = cta_of(v_first, V, P);
+      const int nseg = cta_of(v_first + p.slabs - 1, V, P) - c_first + 1;
+      const int s_me = blockIdx.x - c_first;
+      const int mvalid = min(NB, p.M - mt * NB);
+      const int ca = s_me * mvalid / nseg, cb = (s_me + 1) * mvalid / nseg;
+      if (cb > ca) {
+        if (et == 0) {
+          uint32_t spins = 0;
+          while (ld_acquire_gpu(p.counters + tile_id) < nseg) {
+            if (++spins > (1u << 26)) __trap();
+          }
+        }
+        named_bar_sync(1, EPI_WARPS * 32);
+        __threadfence();
+        const int n_base = EPI == EPI_SWIGLU ? T * TILE_ROWS : T * SUPER_ROWS;
+        const bool vec_ok = (p.y_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 7) == 0);
+        for (int c = ca + ew; c < cb; c += EPI_WARPS) {
+          float a[2][4];
+#pragma unroll
+          for (int t = 0; t < 2; ++t)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) a[t][q] = 0.f;
+          for (int s0 = 0; s0 < nseg; s0 += 8) {
+            float4 pv[2][8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const int sgi = s0 + q;
+              const float* slot = p.workspace + ((size_t)(2 * (c_first + sgi) + (sgi == 0 ? 1 : 0)) * 2 * TILE_ROWS) * NB;
+#pragma unroll
+              for (int t = 0; t < 2; ++t)
+                pv[t][q] = sgi < nseg ? __ldcg(reinterpret_cast<const float4*>(slot + ((size_t)(t * NB + c)) * TILE_ROWS + 4 * lane))
+                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+#pragma unroll
+              for (int t = 0; t < 2; ++t) {
+                a[t][0] += pv[t][q].x; a[t][1] += pv[t][q].y; a[t][2] += pv[t][q].z; a[t][3] += pv[t][q].w;
+              }
+          }
+          const int m = mt * NB + c;
+          uint16_t* yrow = yp + (int64_t)m * p.y_stride;
+          if constexpr (EPI == EPI_SWIGLU) {
+            const int n = n_base + 4 * lane;
+            uint16_t o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) o[q] = swiglu_out(a[0][q], a[1][q], p.y_fp16);
+            store_out4(yrow, n, p.n_out, o, vec_ok);
+          } else {
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+              const int n = n_base + t * TILE_ROWS + 4 * lane;
+              uint16_t o[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) o[q] = to_out16(a[t][q] + load_bias(p, n + q), p.y_fp16);
+              store_out4(yrow, n, p.n_out, o, vec_ok);
+            }
+          }
+        }
+      }
+      named_bar_sync(1, EPI_WARPS * 32);
+      if (et == 0) {
+        const int old = atomicAdd(done + tile_id, 1);
+        if (old == nseg - 1) {  // every piece holder is past its reads: re-arm for the next launch (graph replay)
+          p.counters[tile_id] = 0;
+          done[tile_id] = 0;
+        }
+      }
+    }
+    if (et == 0) trace_stamp(p, 10);
   }
 
   tc_fence_before();
@@ -927,7 +1050,7 @@ int b200_qstream_linear(const void* x, const void* blob, const void* bias, void*
     x_stride = K;
   }
   const int nb = M <= 16 ? 16 : M <= 32 ? 32 : 64;  // M > 64: 64-row m tiles, weights re-streamed per tile
-  B200_CHECK_ARG((int64_t)pp.super_tiles * ((M + nb - 1) / nb) * 4 <= counter_bytes,
+  B200_CHECK_ARG((int64_t)pp.super_tiles * ((M + nb - 1) / nb) <= (1 << 17),
                  "qstream_linear: too many (m tile, super-tile) pairs for the counters");
   qs::HostArgs a;
   a.x = x;

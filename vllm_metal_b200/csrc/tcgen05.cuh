@@ -23,16 +23,18 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
 }
-// try_wait with a suspend-time hint: the hardware parks the thread until the phase completes or
-// the hint (ns) expires, so a waiting warp costs almost no issue slots.
+// try_wait WITHOUT a suspend-time hint.  With a hint ptxas emits TRYWAIT + NANOSLEEP.SYNCS <hint>, and the
+// wake-up out of that sleep costs ~0.5-1 us per hand-off (measured: a pipeline doing nothing but mbarrier
+// hand-offs ran at 0.78 us per stage, profiles/r02_qstream_ablation.txt); the bare form spins on the
+// hardware's own short bounded wait.
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(bar), "r"(parity), "r"(20000u)
+      : "r"(bar), "r"(parity)
       : "memory");
   return ok != 0;
 }
@@ -40,7 +42,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 22)) __trap();  // a protocol bug must fault, not hang the box
+    if (++spins > (1u << 26)) __trap();  // a protocol bug must fault, not hang the box
   }
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
@@ -91,6 +93,18 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16
         "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
       : "memory");
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+// One lane of a converged warp.  Code under `if (elect_one())` keeps warp-uniform operands (descriptors, tensor
+// memory addresses) in uniform registers; the same code under `if (lane == 0)` makes ptxas wrap every
+// tcgen05.mma / TMA in an ELECT + 4x R2UR waterfall loop (~80 cycles per MMA issue, measured).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");

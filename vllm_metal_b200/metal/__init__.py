@@ -136,13 +136,18 @@ def load_library() -> ctypes.CDLL:
     if os.environ.get("VLLM_METAL_BUILD_FROM_SOURCE", "0") not in ("", "0"):
         build()
     so = output_path()
+    override = os.environ.get("B200_PAGED_OPS_LIB")  # tuning experiments only (profiles/build_variants.sh)
+    if override:
+        from pathlib import Path
+
+        so = Path(override)
     if not so.exists():
         raise RuntimeError(
             f"Prebuilt native extension not found at {so}. Run "
             f"`python -m vllm_metal_b200.metal.build` (needs nvcc) or set "
             f"VLLM_METAL_BUILD_FROM_SOURCE=1; there is no CPU fallback."
         )
-    stale = stale_artifacts()
+    stale = [] if override else stale_artifacts()
     if stale:
         raise RuntimeError(
             f"Prebuilt CUDA artifacts are stale vs the current sources "
