@@ -138,13 +138,14 @@ def main():
             t = tr[:148 * 16].view(148, 16).cpu()
             act = t[:, 0] > 0
             t0 = t[act, 0].min()
-            rel = (t[act][:, :11] - t0).float() / 1e3
+            rel = (t[act][:, :14] - t0).float() / 1e3
             line += (f"\n             trace (us, mean/max over {int(act.sum())} CTAs): start {rel[:, 0].mean():.2f}/{rel[:, 0].max():.2f}"
                      f" setup {rel[:, 1].mean():.2f}/{rel[:, 1].max():.2f} x-ready {rel[:, 2].mean():.2f}/{rel[:, 2].max():.2f}"
                      f" first-w {rel[:, 5].mean():.2f}/{rel[:, 5].max():.2f} epi-pdl {rel[:, 9].mean():.2f}/{rel[:, 9].max():.2f}"
                      f" dequant-done {rel[:, 3].mean():.2f}/{rel[:, 3].max():.2f} mma-done {rel[:, 6].mean():.2f}/{rel[:, 6].max():.2f}"
                      f" first-acc {rel[:, 7].mean():.2f}/{rel[:, 7].max():.2f} epi-done {rel[:, 8].mean():.2f}/{rel[:, 8].max():.2f}"
-                     f" finish-done {rel[:, 10].mean():.2f}/{rel[:, 10].max():.2f}")
+                     f" peers-in {rel[:, 11].mean():.2f}/{rel[:, 11].max():.2f} fetched0 {rel[:, 12].mean():.2f}/{rel[:, 12].max():.2f}"
+                     f" fetched1 {rel[:, 13].mean():.2f}/{rel[:, 13].max():.2f} finish-done {rel[:, 10].mean():.2f}/{rel[:, 10].max():.2f}")
         print(line, flush=True)
         if args.trace and args.units:
             c0 = int(units[0, 0])

@@ -254,11 +254,10 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
   const uint32_t bar_a_full = bar_x_empty + 8 * XST, bar_a_empty = bar_a_full + 8 * AS;
   const uint32_t bar_acc_full = bar_a_empty + 8 * AS, bar_acc_empty = bar_acc_full + 8 * 2;
   const uint32_t tmem_ptr_addr = bar_acc_empty + 8 * 2;
-  const uint32_t flag_addr = tmem_ptr_addr + 8;
-  static_assert(8 * (2 * WST + 2 * XST + 2 * AS + 4) + 16 <= 1024, "barrier block overflow");
+  const uint32_t bar_fix = tmem_ptr_addr + 8;  // 2 single-use barriers of the split finish
+  static_assert(8 * (2 * WST + 2 * XST + 2 * AS + 4) + 8 + 16 <= 1024, "barrier block overflow");
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(gen + (tmem_ptr_addr - base));
-  volatile int* flag_gen = reinterpret_cast<volatile int*>(gen + (flag_addr - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int P = gridDim.x;
@@ -282,6 +281,7 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_acc_full + 8 * i, 1);
       mbar_init(bar_acc_empty + 8 * i, EPI_WARPS);
+      mbar_init(bar_fix + 8 * i, 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -305,7 +305,7 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
     uint32_t ph = 1;
     int u = vb % Ui;
     for (int v = vb; v < ve; ++v) {
-      mbar_wait(bar_w_empty + 8 * st, ph);
+      mbar_wait_parked(bar_w_empty + 8 * st, ph);
 #ifdef QS_ABL_NO_W
       if (v - vb >= WST) {
         if (elect_one()) mbar_arrive(bar_w_full + 8 * st);
@@ -328,7 +328,7 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
     int mt = vb / Ui;
     int j = (vb % Ui) % p.slabs, T = (vb % Ui) / p.slabs;
     for (int v = vb; v < ve; ++v) {
-      mbar_wait(bar_x_empty + 8 * st, ph);
+      mbar_wait_parked(bar_x_empty + 8 * st, ph);
 #ifdef QS_ABL_NO_X
       if (v - vb >= XST) {
         if (elect_one()) mbar_arrive(bar_x_full + 8 * st);
@@ -482,8 +482,6 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
     uint16_t* yp = reinterpret_cast<uint16_t*>(p.y);
     pdl_wait();  // y, the workspace and the counters may still be in use by the previous kernel
     if (et == 0) trace_stamp(p, 9);
-    int pend_tile[2];   // super-tiles this CTA holds a piece of (cut by a CTA boundary): finished after the stream
-    int npend = 0;
     int seg = 0;
     int v = (int)v_begin;
     const int ve = (int)v_end;
@@ -495,7 +493,7 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
       const int mt = tile_id / p.super_tiles, T = tile_id % p.super_tiles;
       const int buf = seg % ACC_BUFS;
       const bool whole = (j0 == 0 && j1 == p.slabs);
-      mbar_wait(bar_acc_full + 8 * buf, (seg / ACC_BUFS) & 1);
+      mbar_wait_parked(bar_acc_full + 8 * buf, (seg / ACC_BUFS) & 1);
       if (seg == 0 && et == 0) trace_stamp(p, 7);
       tc_fence_after();
       const uint32_t acc0 = tmem_base + lane_addr + TM_ACC + (buf * 2) * ACC_COLS;
@@ -518,7 +516,6 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
         __threadfence();
         named_bar_sync(1, EPI_WARPS * 32);
         if (et == 0) atomicAdd(p.counters + tile_id, 1);
-        pend_tile[npend++] = tile_id;
       } else {
         const int n_base = EPI == EPI_SWIGLU ? T * TILE_ROWS : T * SUPER_ROWS;  // first output column of this tile
         for (int mh = 0; mh < NB; mh += STAGE_M) {
@@ -586,53 +583,101 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
     }
     if (et == 0) trace_stamp(p, 8);
 
-    // ----- finish the cut super-tiles: the CTAs that hold pieces of one split its columns between them; each
-    // waits until every piece is published, then adds them in k ORDER (deterministic whatever the timing).
-    // Lane l owns rows 4l..4l+3 (16-byte loads of the [t][c][r] partials), warp w takes every 4th column. -----
-    int* done = p.counters + (1 << 17);
+  }
+
+  // ----- finish the cut super-tiles (dequant + epilogue warps, 640 threads).  The CTAs that hold pieces of one
+  // split its (valid) columns between them; each waits until every piece is published, pulls ITS columns of
+  // every piece into the (now idle) weight ring with bulk copies -- all in flight at once -- and adds them in
+  // k ORDER: deterministic whatever the timing.  Lane l owns rows 4l..4l+3, each warp takes every 20th column. -----
+  if (warp < DQ_WARPS || warp >= W_EPI) {
+    constexpr int FIN_WARPS = DQ_WARPS + EPI_WARPS, FIN_THREADS = FIN_WARPS * 32;
+    const int wj = warp < DQ_WARPS ? warp : DQ_WARPS + (warp - W_EPI);
+    const bool leader = threadIdx.x == W_EPI * 32;  // the thread that published this CTA's pieces
+    uint16_t* yp = reinterpret_cast<uint16_t*>(p.y);
+    const int vb = (int)v_begin, ve = (int)v_end;
+    int pend_tile[2];
+    int npend = 0;
+    if (ve > vb) {
+      const int t_first = vb / p.slabs, t_last = (ve - 1) / p.slabs;
+      const int end_first = min((t_first + 1) * p.slabs, ve);
+      if (!(vb == t_first * p.slabs && end_first == (t_first + 1) * p.slabs)) pend_tile[npend++] = t_first;
+      if (t_last != t_first && ve != (t_last + 1) * p.slabs) pend_tile[npend++] = t_last;
+    }
+    int f_cfirst[2], f_nseg[2], f_ca[2], f_cb[2];
+    uint32_t f_off[2];
+#pragma unroll
+    for (int pi = 0; pi < 2; ++pi) {
+      f_cfirst[pi] = f_nseg[pi] = f_ca[pi] = f_cb[pi] = 0;
+      if (pi < npend) {
+        const int tile_id = pend_tile[pi];
+        const int mt = tile_id / p.super_tiles;
+        const long long v_first = (long long)tile_id * p.slabs;
+        f_cfirst[pi] = cta_of(v_first, V, P);
+        f_nseg[pi] = cta_of(v_first + p.slabs - 1, V, P) - f_cfirst[pi] + 1;
+        const int s_me = blockIdx.x - f_cfirst[pi];
+        const int mvalid = min(NB, p.M - mt * NB);
+        f_ca[pi] = s_me * mvalid / f_nseg[pi];
+        f_cb[pi] = (s_me + 1) * mvalid / f_nseg[pi];
+      }
+    }
+    f_off[0] = 0;
+    f_off[1] = (uint32_t)(f_nseg[0] * 2 * (f_cb[0] - f_ca[0]) * TILE_ROWS * 4);
+    // both fetches in flight together when they fit the ring, else one after the other
+    const bool together = npend == 2 && f_off[1] + (uint32_t)(f_nseg[1] * 2 * (f_cb[1] - f_ca[1]) * TILE_ROWS * 4) <= (uint32_t)(WST * WB);
+    if (!together) f_off[1] = 0;
+    auto fetch = [&](int pi) {  // leader only
+      const int ncol = f_cb[pi] - f_ca[pi];
+      if (ncol <= 0) return;
+      uint32_t spins = 0;
+      while (ld_acquire_gpu(p.counters + pend_tile[pi]) < f_nseg[pi]) {
+        if (++spins > (1u << 26)) __trap();
+      }
+      if (pi == 0) trace_stamp(p, 11);
+      asm volatile("fence.proxy.async;" ::: "memory");  // peers' generic-proxy stores -> this thread's bulk reads
+      const uint32_t bytes = (uint32_t)(ncol * TILE_ROWS * 4);
+      mbar_expect_tx(bar_fix + 8 * pi, bytes * 2 * f_nseg[pi]);
+      for (int sgi = 0; sgi < f_nseg[pi]; ++sgi) {
+        const float* slot = p.workspace + ((size_t)(2 * (f_cfirst[pi] + sgi) + (sgi == 0 ? 1 : 0)) * 2 * TILE_ROWS) * NB;
+#pragma unroll
+        for (int t = 0; t < 2; ++t)
+          bulk_load(sm_w + f_off[pi] + (uint32_t)(sgi * 2 + t) * bytes, slot + (size_t)(t * NB + f_ca[pi]) * TILE_ROWS, bytes,
+                    bar_fix + 8 * pi);
+      }
+    };
+    if (leader) {
+      if (npend > 0) fetch(0);
+      if (together) fetch(1);
+    }
     for (int pi = 0; pi < npend; ++pi) {
       const int tile_id = pend_tile[pi];
       const int mt = tile_id / p.super_tiles, T = tile_id % p.super_tiles;
-      const long long v_first = (long long)tile_id * p.slabs;
-      const int c_first = cta_of(v_first, V, P);
-      const int nseg = cta_of(v_first + p.slabs - 1, V, P) - c_first + 1;
-      const int s_me = blockIdx.x - c_first;
-      const int mvalid = min(NB, p.M - mt * NB);
-      const int ca = s_me * mvalid / nseg, cb = (s_me + 1) * mvalid / nseg;
+      const int ca = f_ca[pi], cb = f_cb[pi], nseg = f_nseg[pi];
+      if (pi == 1 && !together) {
+        named_bar_sync(2, FIN_THREADS);  // ring reads of piece 0 are over
+        if (leader) fetch(1);
+      }
       if (cb > ca) {
-        if (et == 0) {
-          uint32_t spins = 0;
-          while (ld_acquire_gpu(p.counters + tile_id) < nseg) {
-            if (++spins > (1u << 26)) __trap();
-          }
-        }
-        named_bar_sync(1, EPI_WARPS * 32);
-        __threadfence();
+        mbar_wait_parked(bar_fix + 8 * pi, 0);
+        if (leader) trace_stamp(p, 12 + pi);
         const int n_base = EPI == EPI_SWIGLU ? T * TILE_ROWS : T * SUPER_ROWS;
         const bool vec_ok = (p.y_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 7) == 0);
-        for (int c = ca + ew; c < cb; c += EPI_WARPS) {
+        const uint32_t col_bytes = TILE_ROWS * 4, piece_bytes = (uint32_t)(cb - ca) * col_bytes;
+        for (int c = ca + wj; c < cb; c += FIN_WARPS) {
           float a[2][4];
 #pragma unroll
           for (int t = 0; t < 2; ++t)
 #pragma unroll
             for (int q = 0; q < 4; ++q) a[t][q] = 0.f;
-          for (int s0 = 0; s0 < nseg; s0 += 8) {
-            float4 pv[2][8];
+          const uint32_t src0 = sm_w + f_off[pi] + (uint32_t)(c - ca) * col_bytes + lane * 16;
+          for (int sgi = 0; sgi < nseg; ++sgi) {
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const int sgi = s0 + q;
-              const float* slot = p.workspace + ((size_t)(2 * (c_first + sgi) + (sgi == 0 ? 1 : 0)) * 2 * TILE_ROWS) * NB;
-#pragma unroll
-              for (int t = 0; t < 2; ++t)
-                pv[t][q] = sgi < nseg ? __ldcg(reinterpret_cast<const float4*>(slot + ((size_t)(t * NB + c)) * TILE_ROWS + 4 * lane))
-                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int t = 0; t < 2; ++t) {
+              float4 pv;
+              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                           : "=f"(pv.x), "=f"(pv.y), "=f"(pv.z), "=f"(pv.w)
+                           : "r"(src0 + (uint32_t)(sgi * 2 + t) * piece_bytes));
+              a[t][0] += pv.x; a[t][1] += pv.y; a[t][2] += pv.z; a[t][3] += pv.w;
             }
-#pragma unroll
-            for (int q = 0; q < 8; ++q)
-#pragma unroll
-              for (int t = 0; t < 2; ++t) {
-                a[t][0] += pv[t][q].x; a[t][1] += pv[t][q].y; a[t][2] += pv[t][q].z; a[t][3] += pv[t][q].w;
-              }
           }
           const int m = mt * NB + c;
           uint16_t* yrow = yp + (int64_t)m * p.y_stride;
@@ -654,16 +699,21 @@ qgemm_stream_kernel(const __grid_constant__ CUtensorMap x_map, const Params p) {
           }
         }
       }
-      named_bar_sync(1, EPI_WARPS * 32);
-      if (et == 0) {
-        const int old = atomicAdd(done + tile_id, 1);
-        if (old == nseg - 1) {  // every piece holder is past its reads: re-arm for the next launch (graph replay)
-          p.counters[tile_id] = 0;
-          done[tile_id] = 0;
+    }
+    if (npend > 0) {
+      named_bar_sync(2, FIN_THREADS);  // every reader of the pieces is done
+      if (leader) {
+        int* done = p.counters + (1 << 17);
+        for (int pi = 0; pi < npend; ++pi) {
+          const int old = atomicAdd(done + pend_tile[pi], 1);
+          if (old == f_nseg[pi] - 1) {  // every piece holder is past its reads: re-arm for the next launch (graph replay)
+            p.counters[pend_tile[pi]] = 0;
+            done[pend_tile[pi]] = 0;
+          }
         }
+        trace_stamp(p, 10);
       }
     }
-    if (et == 0) trace_stamp(p, 10);
   }
 
   tc_fence_before();
