@@ -20,10 +20,12 @@ extern "C" {
 /* out[r,:] = x[r,:] * rsqrt(mean(x[r,:]^2) + eps) * weight   (mx.fast.rms_norm).
  * If `residual` != NULL: residual[r,:] += x[r,:] first (in place, rounded to
  * `dtype`), and the norm is taken of the updated residual (fused
- * add + norm used between decoder sub-blocks).  `weight` may be NULL (=1). */
+ * add + norm used between decoder sub-blocks).  `weight` may be NULL (=1).
+ * out_dtype = dtype, or B200_F16 with dtype = B200_BF16: the bf16-rounded result stored as fp16
+ * (exact below 65504, saturating) -- the operand type of b200_qstream_linear, saving its staging cast. */
 int b200_rms_norm(const void* x, void* residual, const void* weight, void* out,
                   int rows, int dim, int64_t x_stride, int64_t res_stride,
-                  int64_t out_stride, float eps, int dtype, void* stream);
+                  int64_t out_stride, float eps, int dtype, int out_dtype, void* stream);
 
 /* In-place rotary embedding of q [T, Hq, D] and k [T, Hk, D] (k may be NULL)
  * at per-token positions (int32 [T]); the first rot_dim dims of each head are

@@ -55,7 +55,7 @@ template <typename T, int NV>
 __global__ void __launch_bounds__(1024)
 rms_norm_vec_kernel(const T* __restrict__ x, T* __restrict__ residual, const T* __restrict__ weight,
                     T* __restrict__ out, int dim, int64_t x_stride, int64_t res_stride,
-                    int64_t out_stride, float eps) {
+                    int64_t out_stride, float eps, int out_f16) {
   pdl_trigger();
   pdl_wait();
   __shared__ float red[32];
@@ -108,6 +108,11 @@ rms_norm_vec_kernel(const T* __restrict__ x, T* __restrict__ residual, const T* 
       } else {
 #pragma unroll
         for (int e = 0; e < 8; ++e) ce[e] = from_float<T>(v[j][e] * inv);
+      }
+      if (out_f16) {  // the value rounded to T, stored as fp16 (exact below 65504, saturating): the stream-K GEMM's x
+        __half* he = reinterpret_cast<__half*>(&c);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) he[e] = __float2half_rn(fminf(fmaxf(to_float(ce[e]), -65504.f), 65504.f));
       }
       orow[i] = c;
     }
@@ -316,10 +321,12 @@ extern "C" int b200_advance_decode(int32_t* input_ids, int32_t* positions, int32
 
 extern "C" int b200_rms_norm(const void* x, void* residual, const void* weight, void* out,
                              int rows, int dim, int64_t x_stride, int64_t res_stride,
-                             int64_t out_stride, float eps, int dtype, void* stream) {
+                             int64_t out_stride, float eps, int dtype, int out_dtype, void* stream) {
   using namespace b200;
   if (rows == 0) return B200_OK;
   B200_CHECK_ARG(rows > 0 && dim > 0 && x && out, "rms_norm: bad arguments");
+  const int out_f16 = (out_dtype == B200_F16 && dtype == B200_BF16) ? 1 : 0;
+  B200_CHECK_ARG(out_dtype == dtype || out_f16, "rms_norm: out dtype must be the input dtype, or fp16 for bf16 input");
   cudaStream_t st = (cudaStream_t)stream;
   const int threads = dim >= 1024 ? 256 : (dim >= 256 ? 128 : 32);
   const bool aligned = dim % 8 == 0 && dtype != B200_F32 && x_stride % 8 == 0 && res_stride % 8 == 0 &&
@@ -334,21 +341,22 @@ extern "C" int b200_rms_norm(const void* x, void* residual, const void* weight, 
       using T = __nv_bfloat16;
       if (nv == 1)
         launch_pdl(rms_norm_vec_kernel<T, 1>, dim3(rows), dim3(vt), 0, st, (const T*)x, (T*)residual, (const T*)weight, (T*)out,
-                                                        dim, x_stride, res_stride, out_stride, eps);
+                                                        dim, x_stride, res_stride, out_stride, eps, out_f16);
       else
         launch_pdl(rms_norm_vec_kernel<T, 2>, dim3(rows), dim3(vt), 0, st, (const T*)x, (T*)residual, (const T*)weight, (T*)out,
-                                                        dim, x_stride, res_stride, out_stride, eps);
+                                                        dim, x_stride, res_stride, out_stride, eps, out_f16);
     } else {
       using T = __half;
       if (nv == 1)
         launch_pdl(rms_norm_vec_kernel<T, 1>, dim3(rows), dim3(vt), 0, st, (const T*)x, (T*)residual, (const T*)weight, (T*)out,
-                                                        dim, x_stride, res_stride, out_stride, eps);
+                                                        dim, x_stride, res_stride, out_stride, eps, out_f16);
       else
         launch_pdl(rms_norm_vec_kernel<T, 2>, dim3(rows), dim3(vt), 0, st, (const T*)x, (T*)residual, (const T*)weight, (T*)out,
-                                                        dim, x_stride, res_stride, out_stride, eps);
+                                                        dim, x_stride, res_stride, out_stride, eps, out_f16);
     }
     return check_launch("rms_norm_vec_kernel");
   }
+  B200_CHECK_ARG(!out_f16, "rms_norm: fp16 output needs the vectorised path (dim %% 8 == 0, 512 <= dim <= 16384, aligned rows)");
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
     launch_pdl(rms_norm_kernel<T>, dim3(rows), dim3(threads), 0, st, (const T*)x, (T*)residual, (const T*)weight,
                                                  (T*)out, dim, x_stride, res_stride, out_stride,

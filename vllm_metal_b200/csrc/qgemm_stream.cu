@@ -76,6 +76,7 @@ struct Params {
   int m_tiles;
   int64_t y_stride;
   int y_fp16;              // output / bias / SwiGLU rounding dtype: 1 = fp16, 0 = bf16 (x, the B operand, is always fp16)
+  int y_store_f16;         // with y_fp16 = 0: store the bf16-rounded result as fp16 (saturating) for a following qstream
   unsigned long long* trace;
 };
 
@@ -164,16 +165,21 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* ptr) {
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(ptr) : "memory");
   return v;
 }
+// fp16: 0 = bf16, 1 = fp16, 2 = rounded to bf16 then stored as fp16 (exact below 65504, saturating)
 __device__ __forceinline__ uint16_t to_out16(float v, int fp16) {
-  if (fp16) {
+  if (fp16 == 1) {
     const __half h = __float2half_rn(v);
     return *reinterpret_cast<const uint16_t*>(&h);
   }
   const __nv_bfloat16 h = __float2bfloat16_rn(v);
+  if (fp16 == 2) {
+    const __half g = __float2half_rn(fminf(fmaxf(__bfloat162float(h), -65504.f), 65504.f));
+    return *reinterpret_cast<const uint16_t*>(&g);
+  }
   return *reinterpret_cast<const uint16_t*>(&h);
 }
 __device__ __forceinline__ float round_out(float v, int fp16) {
-  return fp16 ? __half2float(__float2half_rn(v)) : __bfloat162float(__float2bfloat16_rn(v));
+  return fp16 == 1 ? __half2float(__float2half_rn(v)) : __bfloat162float(__float2bfloat16_rn(v));
 }
 // gate and up are rounded to the activation dtype first, as the unfused sequence stores them
 // (oracle/decoder.py silu_mul: silu rounded, then the product rounded)
@@ -184,7 +190,7 @@ __device__ __forceinline__ uint16_t swiglu_out(float gate, float up, int fp16) {
 }
 __device__ __forceinline__ float load_bias(const Params& p, int n) {
   if (p.bias == nullptr || n >= p.N) return 0.f;
-  return p.y_fp16 ? __half2float(reinterpret_cast<const __half*>(p.bias)[n])
+  return p.y_fp16 == 1 ? __half2float(reinterpret_cast<const __half*>(p.bias)[n])
                   : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[n]);
 }
 // four consecutive outputs n..n+3 of one y row
@@ -887,7 +893,7 @@ struct HostArgs {
   float* workspace;
   size_t workspace_bytes;
   int* counters;
-  int M, N, K, group, bits, dtype, epi;
+  int M, N, K, group, bits, dtype, epi, store_f16;
   int64_t x_stride, y_stride;
 };
 
@@ -924,13 +930,22 @@ static int launch_cfg(const HostArgs& a, cudaStream_t st) {
   p.slabs = (a.K + Geo<BITS>::KS - 1) / Geo<BITS>::KS;
   p.m_tiles = (a.M + NB - 1) / NB;
   p.y_stride = a.y_stride;
-  p.y_fp16 = a.dtype == B200_F16 ? 1 : 0;
+  p.y_fp16 = a.dtype == B200_F16 ? 1 : (a.store_f16 ? 2 : 0);
+  p.y_store_f16 = a.store_f16;
   p.trace = g_trace;
   const long long V = (long long)p.super_tiles * p.slabs * p.m_tiles;
   const int sms = sm_count() > 0 ? sm_count() : 148;
-  // every CTA streams >= 4 slabs (a CTA's fixed cost is ~2 slabs' worth), at most one CTA per SM
-  long long grid = V / 4;
-  if (grid > sms) grid = sms;
+  // Persistent grid.  Few super-tiles (T < SMs): cut every tile into the same number s of equal k pieces
+  // (grid = T * s): each CTA then holds ONE piece, and the finish is one exchange.  Otherwise (or when that
+  // would idle > 15% of the SMs) plain stream-K over all SMs.  Every CTA keeps >= 2 slabs.
+  const long long tiles = (long long)p.super_tiles * p.m_tiles;
+  long long grid = sms;
+  if (tiles < sms) {
+    long long s = sms / tiles;
+    if (s > p.slabs / 2) s = p.slabs / 2 > 0 ? p.slabs / 2 : 1;
+    if (tiles * s * 100 >= (long long)sms * 85 || V / 2 < sms) grid = tiles * s;
+  }
+  if (grid > V / 2) grid = V / 2;
   if (grid < 1) grid = 1;
   if (g_force_grid > 0) grid = g_force_grid < V ? g_force_grid : V;
   B200_CHECK_ARG((size_t)grid * 2 * 2 * TILE_ROWS * NB * sizeof(float) <= a.workspace_bytes,
@@ -1075,7 +1090,10 @@ int b200_qstream_linear(const void* x, const void* blob, const void* bias, void*
   B200_CHECK_ARG(x && blob && y && workspace, "qstream_linear: null pointer argument");
   B200_CHECK_ARG(dtype == B200_BF16 || dtype == B200_F16, "qstream_linear: y must be bf16 or fp16");
   B200_CHECK_ARG(x_dtype == B200_BF16 || x_dtype == B200_F16, "qstream_linear: x must be bf16 or fp16");
-  B200_CHECK_ARG(epilogue == qs::EPI_PLAIN || epilogue == qs::EPI_SWIGLU, "qstream_linear: bad epilogue %d", epilogue);
+  B200_CHECK_ARG(epilogue >= 0 && epilogue <= 3, "qstream_linear: bad epilogue %d", epilogue);
+  const int store_f16 = (epilogue & 2) ? 1 : 0;  // bf16-rounded values stored as fp16 (feeds the next qstream_linear)
+  epilogue &= 1;
+  B200_CHECK_ARG(!(store_f16 && dtype != B200_BF16), "qstream_linear: the fp16-store flag applies to bf16 results");
   B200_CHECK_ARG(!(epilogue == qs::EPI_SWIGLU && bias), "qstream_linear: SwiGLU epilogue takes no dense bias");
   qs::PackParams pp{};
   int rc = qs::fill_pack(pp, N, K, bits, group_size, epilogue == qs::EPI_SWIGLU);
@@ -1117,6 +1135,7 @@ int b200_qstream_linear(const void* x, const void* blob, const void* bias, void*
   a.bits = bits;
   a.dtype = dtype;
   a.epi = epilogue;
+  a.store_f16 = store_f16;
   a.x_stride = x_stride;
   a.y_stride = y_stride;
   return bits == 4 ? qs::dispatch_g<4>(a, st) : qs::dispatch_g<8>(a, st);

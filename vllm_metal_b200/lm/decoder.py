@@ -80,8 +80,10 @@ class RMSNorm(nn.Module):
         self.register_buffer("weight", torch.ones(dims, dtype=dtype, device=device))
         self.eps = eps
 
-    def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None) -> torch.Tensor:
-        return get_ops().rms_norm(x, self.weight, self.eps, residual=residual)
+    def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None, out_f16: bool = False) -> torch.Tensor:
+        """``out_f16``: the (bf16-rounded) result stored as fp16, the operand type of the stream-K linears."""
+        f16 = out_f16 and x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0 and 512 <= x.shape[-1] <= 16384
+        return get_ops().rms_norm(x, self.weight, self.eps, residual=residual, out_dtype=torch.float16 if f16 else None)
 
 
 def _rand_qlinear(in_f, out_f, args: ModelArgs, gen, dtype, device, std=0.02) -> QuantizedLinear:
@@ -139,7 +141,8 @@ class MLP(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.gate_up_proj.swiglu:  # SiLU * up fused into the gate_up epilogue (streaming layout)
-            return self.down_proj(self.gate_up_proj(x))
+            f16 = getattr(self.down_proj, "weight_blob", None) is not None
+            return self.down_proj(self.gate_up_proj(x, out_f16=f16))
         return self.down_proj(get_ops().silu_mul(self.gate_up_proj(x)))
 
 
@@ -172,6 +175,7 @@ class Model(nn.Module):
             self.lm_head = None
         else:
             self.lm_head = _rand_qlinear(args.hidden, args.vocab, args, gen, dtype, device)
+        self._f16_acts = False
         if prepack:
             self.prepack()
 
@@ -186,6 +190,10 @@ class Model(nn.Module):
                 m.prepack(keep_mlx_layout=False)
         if self.lm_head is None:
             self.embed_tokens.prepack()
+        # norms feed the stream-K linears fp16 directly (their operand type) when every consumer is one
+        self._f16_acts = all(getattr(m, "weight_blob", None) is not None for m in self.modules()
+                             if isinstance(m, QuantizedLinear)) and (
+            self.lm_head is not None or getattr(self.embed_tokens, "weight_blob", None) is not None)
 
     def _reduce(self, x: torch.Tensor) -> torch.Tensor:
         if self.world > 1:
@@ -196,14 +204,15 @@ class Model(nn.Module):
         h = self.embed_tokens(input_ids)  # residual stream [T, hidden]
         delta = None
         for i, layer in enumerate(self.layers):
-            x = layer.input_layernorm(h if delta is None else delta, residual=None if delta is None else h)
+            x = layer.input_layernorm(h if delta is None else delta, residual=None if delta is None else h,
+                                      out_f16=self._f16_acts)
             a = self._reduce(sdpa_forward(layer.self_attn, x, ctx, kv_cache, i, meta=meta))
             if layer.mlp is None:
                 delta = a
                 continue
-            x = layer.post_attention_layernorm(a, residual=h)  # h += a; x = norm(h)
+            x = layer.post_attention_layernorm(a, residual=h, out_f16=self._f16_acts)  # h += a; x = norm(h)
             delta = self._reduce(layer.mlp(x))
-        x = self.norm(delta, residual=h) if delta is not None else self.norm(h)
+        x = self.norm(delta, residual=h, out_f16=self._f16_acts) if delta is not None else self.norm(h, out_f16=self._f16_acts)
         if logits_rows is not None:
             x = x.index_select(0, logits_rows)
         return self.embed_tokens.as_linear(x) if self.lm_head is None else self.lm_head(x)

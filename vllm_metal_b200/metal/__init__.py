@@ -175,7 +175,7 @@ def load_library() -> ctypes.CDLL:
     lib.b200_cast_bf16_to_f16.argtypes = [vp, vp, i32, i32, i64, vp]
     lib.b200_set_qstream_grid.argtypes = [i32]
     lib.b200_set_qstream_trace.argtypes = [vp]
-    lib.b200_rms_norm.argtypes = [vp, vp, vp, vp, i32, i32, i64, i64, i64, f32, i32, vp]
+    lib.b200_rms_norm.argtypes = [vp, vp, vp, vp, i32, i32, i64, i64, i64, f32, i32, i32, vp]
     lib.b200_rope.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i64, i64, i32, vp]
     lib.b200_norm_rope_cache.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32,
                                          f32, i64, i64, i64, i32, i64, i64, i64, i32, vp]
@@ -513,10 +513,12 @@ class _Ops:
         return ws
 
     def qstream_linear(self, x, blob, n_out: int, k: int, group_size: int = 64, bits: int = 4, bias=None,
-                       swiglu: bool = False, out=None, out_dtype: torch.dtype | None = None):
+                       swiglu: bool = False, out=None, out_dtype: torch.dtype | None = None,
+                       round_dtype: torch.dtype | None = None):
         """``x @ W'^T (+ bias)`` over a streaming blob; ``swiglu=True`` returns ``silu(gate) * up``
         (``[.., n_out / 2]``) from a blob packed with ``swiglu=True``.  ``x`` may be fp16 while the result
-        is bf16 (``out_dtype``): the kernel's operands are fp16, a bf16 ``x`` is staged as fp16 first."""
+        is bf16 (``out_dtype``): the kernel's operands are fp16, a bf16 ``x`` is staged as fp16 first.
+        ``out_dtype=float16, round_dtype=bfloat16``: the bf16 result stored as fp16 (feeds the next call)."""
         _require_cuda("x", x)
         _require_cuda("blob", blob)
         if x.shape[-1] != k:
@@ -530,15 +532,19 @@ class _Ops:
         if out is None:
             out = torch.empty((m, cols), dtype=out_dtype or x.dtype, device=x.device)
         y2 = out.reshape(m, cols)
+        rdt = round_dtype or out.dtype
+        store_f16 = rdt == torch.bfloat16 and out.dtype == torch.float16
+        if rdt != out.dtype and not store_f16:
+            raise ValueError(f"unsupported rounding/storage dtypes {rdt} / {out.dtype}")
         if bias is not None:
-            bias = bias.to(dtype=out.dtype).contiguous()
+            bias = bias.to(dtype=rdt).contiguous()
         if x2.dtype == torch.bfloat16 and m * k * 2 > (8 << 20):
             x2 = self.cast_f16(x2)  # larger than the in-workspace staging region
         ws = self._qstream_workspace(x.device)
         rc = self._lib.b200_qstream_linear(
             x2.data_ptr(), blob.data_ptr(), _ptr(bias), y2.data_ptr(), m, n_out, k, group_size, bits,
-            _dtype_code("x", x2), _dtype_code("out", out), int(swiglu), x2.stride(0), y2.stride(0), ws.data_ptr(),
-            ws.numel(), _stream())
+            _dtype_code("x", x2), _DTYPE_CODE[rdt], int(swiglu) | (2 if store_f16 else 0), x2.stride(0), y2.stride(0),
+            ws.data_ptr(), ws.numel(), _stream())
         self._check(rc)
         self.launches += 2 if x2.dtype == torch.bfloat16 else 1
         return out.reshape(*lead, cols)
@@ -607,18 +613,21 @@ class _Ops:
         return out if shape is None else out.reshape(*shape, k)
 
     # -- neighbours of the hot path (include/b200_decoder_ops.h) ----------------
-    def rms_norm(self, x, weight, eps: float, residual=None, out=None):
-        """``mx.fast.rms_norm``; with ``residual`` does ``residual += x`` first (in place)."""
+    def rms_norm(self, x, weight, eps: float, residual=None, out=None, out_dtype: torch.dtype | None = None):
+        """``mx.fast.rms_norm``; with ``residual`` does ``residual += x`` first (in place).
+        ``out_dtype=torch.float16`` on bf16 input stores the bf16-rounded result as fp16 (the stream-K GEMM's
+        operand type)."""
         _require_cuda("x", x)
         dim = x.shape[-1]
         x2 = x.reshape(-1, dim)
         if out is None:
-            out = torch.empty_like(x2)
+            out = torch.empty(x2.shape, dtype=out_dtype or x.dtype, device=x.device)
         o2 = out.reshape(-1, dim)
         r2 = None if residual is None else residual.reshape(-1, dim)
         rc = self._lib.b200_rms_norm(
             x2.data_ptr(), _ptr(r2), _ptr(weight), o2.data_ptr(), x2.shape[0], dim, x2.stride(0),
-            0 if r2 is None else r2.stride(0), o2.stride(0), float(eps), _dtype_code("x", x), _stream())
+            0 if r2 is None else r2.stride(0), o2.stride(0), float(eps), _dtype_code("x", x), _dtype_code("out", out),
+            _stream())
         self._check(rc)
         self.launches += 1
         return out.reshape(x.shape)

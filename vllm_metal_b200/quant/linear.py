@@ -120,11 +120,18 @@ class QuantizedLinear(nn.Module):
         if prefix + "weight" in destination and destination[prefix + "weight"].shape[0] == 0:
             destination[prefix + "weight"] = self.mlx_weight()
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, out_f16: bool = False) -> torch.Tensor:
+        """``x`` in the module dtype, or fp16 (the stream-K kernel's operand type: a bf16 ``x`` is staged as fp16
+        by one extra launch, so producers that can emit fp16 do).  ``out_f16``: a bf16 module stores its
+        (bf16-rounded) result as fp16 for a following QuantizedLinear."""
         blob = getattr(self, "weight_blob", None)
         if blob is not None and x.dtype in (torch.bfloat16, torch.float16):
+            dt = self.scales.dtype
             return get_ops().qstream_linear(x, blob, self.out_features, self.in_features, self.group_size, self.bits,
-                                            bias=self.bias, swiglu=self.swiglu)
+                                            bias=self.bias, swiglu=self.swiglu,
+                                            out_dtype=torch.float16 if out_f16 else dt, round_dtype=dt)
+        if x.dtype != self.scales.dtype:
+            x = x.to(self.scales.dtype)
         return get_ops().quantized_matmul(x, self.mlx_weight(), self.scales, self.biases, transpose=True,
                                           group_size=self.group_size, bits=self.bits, bias=self.bias)
 
@@ -171,6 +178,8 @@ class QuantizedEmbedding(nn.Module):
         blob = getattr(self, "weight_blob", None)
         n, k = self.scales.shape[0], self.scales.shape[1] * self.group_size
         if blob is not None and x.dtype in (torch.bfloat16, torch.float16):
-            return get_ops().qstream_linear(x, blob, n, k, self.group_size, self.bits)
+            return get_ops().qstream_linear(x, blob, n, k, self.group_size, self.bits, out_dtype=self.scales.dtype)
+        if x.dtype != self.scales.dtype:
+            x = x.to(self.scales.dtype)
         return get_ops().quantized_matmul(x, self.weight, self.scales, self.biases, transpose=True,
                                           group_size=self.group_size, bits=self.bits)
