@@ -179,10 +179,14 @@ int b200_paged_attention(const b200_paged_attn_args* args, void* stream);
  *   y[m,n] = sum_k x[m,k] * (scales[n,k/g] * q[n,k] + biases[n,k/g]) (+ bias[n])
  * fp32 accumulation, one rounding to `dtype`.  bits in {4, 8}; group_size in
  * {32, 64, 128}; K % group_size == 0.
+ * x_dtype = dtype, or B200_F16 with dtype = B200_BF16: the tcgen05 kernels multiply fp16 x by weights
+ * dequantised to fp16 (bf16 would cost 3 significant bits of s*q+b and kind::f16 does not mix the two),
+ * so bf16 callers stage x through b200_cast_bf16_to_f16 (or have the producer emit fp16); with a bf16 x
+ * b200_qlinear runs the mma.sync kernel.
  * --------------------------------------------------------------------------- */
 int b200_qlinear(const void* x, const uint32_t* w, const void* scales,
                  const void* biases, const void* bias, void* y, int M, int N,
-                 int K, int group_size, int bits, int dtype, int sb_dtype,
+                 int K, int group_size, int bits, int x_dtype, int dtype, int sb_dtype,
                  int64_t x_stride, int64_t y_stride, void* stream);
 
 /* Test / tuning knob: which kernel b200_qlinear runs.  0 = auto (tcgen05 + TMEM + TMA kernel
@@ -219,7 +223,7 @@ int b200_qlinear_prepack(const uint32_t* w, uint32_t* out, int N, int K, int bit
  * tcgen05 kernel reads this layout: shapes it does not take fail with B200_ERR_UNSUPPORTED. */
 int b200_qlinear_prepacked(const void* x, const uint32_t* wp, const void* scales,
                            const void* biases, const void* bias, void* y, int M, int N,
-                           int K, int group_size, int bits, int dtype, int sb_dtype,
+                           int K, int group_size, int bits, int x_dtype, int dtype, int sb_dtype,
                            int64_t x_stride, int64_t y_stride, void* stream);
 
 /* out[r, :] = dequantize(row ids[r]) for r in [0, num_rows); ids == NULL means

@@ -109,8 +109,12 @@ def test_cfg_a_qwen3_0p6b_128_free_running_greedy_steps():
     decode steps.  The product runs FREE (CUDA graph, its own tokens fed back, as in
     /root/reference/tests/test_paged_deterministic.py:50-74); the oracle is stepped along the
     product's trajectory and must name the same token at every step.  A differing token is only
-    tolerated -- and printed -- when the oracle's own logits of the two candidates are less than
-    one bf16 ulp apart (a tie at the logits' storage precision); no mismatch budget."""
+    tolerated -- and printed -- when the oracle's own logits of the two candidates are AT MOST one
+    bf16 ulp apart: logits are stored in bf16, the product accumulates in another order (tensor-core
+    tiles, stream-K pieces) than the oracle's fp32 loop, so either candidate's logit may round one
+    ulp the other way -- a tie at the logits' storage precision.  With random-init weights and a
+    151936-way argmax such ties do occur (the vocabulary's top two logits are routinely 0-1 ulp
+    apart); anything wider fails.  No mismatch budget."""
     from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
     from vllm_metal_b200.lm.decoder import PRESETS, Model
     from vllm_metal_b200.v1.model_runner import PagedModelRunner
@@ -138,7 +142,7 @@ def test_cfg_a_qwen3_0p6b_128_free_running_greedy_steps():
         gap = float(ologits[0, want] - ologits[0, got_tok])
         ulp = _bf16_ulp(ologits[0, want])
         print(f"step {step}: product {got_tok} vs oracle {want}, oracle logit gap {gap:.6f} (1 bf16 ulp = {ulp:.6f})")
-        assert gap < ulp, f"step {step}: token {got_tok} != oracle {want}; oracle top-2 gap {gap} >= 1 bf16 ulp {ulp}"
+        assert gap <= ulp, f"step {step}: token {got_tok} != oracle {want}; oracle top-2 gap {gap} > 1 bf16 ulp {ulp}"
         ties.append(step)
 
     check(-1, got[0], ologits)

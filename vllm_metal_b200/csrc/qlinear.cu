@@ -16,7 +16,7 @@
 namespace b200 {
 
 // qgemm_tc.cu: tcgen05 / TMEM / TMA path
-bool qgemm_tc_supported(const void* x, const uint32_t* w, int M, int N, int K, int group_size, int bits,
+bool qgemm_tc_supported(const void* x, const uint32_t* w, int M, int N, int K, int group_size, int bits, int x_dtype,
                         int dtype, int sb_dtype, int64_t x_stride);
 int qgemm_tc_launch(const void* x, const uint32_t* w, const void* scales, const void* biases,
                     const void* bias, void* y, int M, int N, int K, int group_size, int bits, int dtype,
@@ -393,7 +393,7 @@ static int check_quant_args(const char* what, int N, int K, int group_size, int 
 
 extern "C" int b200_qlinear(const void* x, const uint32_t* w, const void* scales,
                             const void* biases, const void* bias, void* y, int M, int N, int K,
-                            int group_size, int bits, int dtype, int sb_dtype, int64_t x_stride,
+                            int group_size, int bits, int x_dtype, int dtype, int sb_dtype, int64_t x_stride,
                             int64_t y_stride, void* stream) {
   using namespace b200;
   int rc = check_quant_args("qlinear", N, K, group_size, bits, sb_dtype);
@@ -401,6 +401,8 @@ extern "C" int b200_qlinear(const void* x, const uint32_t* w, const void* scales
   B200_CHECK_ARG(M >= 0, "qlinear: M must be >= 0, got %d", M);
   if (M == 0) return B200_OK;
   B200_CHECK_ARG(x && w && scales && biases && y, "qlinear: null pointer argument");
+  B200_CHECK_ARG(x_dtype == dtype || (x_dtype == B200_F16 && dtype == B200_BF16),
+                 "qlinear: x dtype %d with result dtype %d (x must match, or be fp16 for bf16 results)", x_dtype, dtype);
   if (dtype == B200_F32) {
     B200_CHECK_ARG(y_stride >= N && x_stride >= K, "qlinear: bad fp32 strides");
     cudaStream_t stf = (cudaStream_t)stream;
@@ -422,13 +424,14 @@ extern "C" int b200_qlinear(const void* x, const uint32_t* w, const void* scales
   cudaStream_t st0 = (cudaStream_t)stream;
   if (g_qlinear_kernel != 1) {
     const bool ok = y_stride >= N &&
-                    qgemm_tc_supported(x, w, M, N, K, group_size, bits, dtype, sb_dtype, x_stride);
+                    qgemm_tc_supported(x, w, M, N, K, group_size, bits, x_dtype, dtype, sb_dtype, x_stride);
     if (ok) return qgemm_tc_launch(x, w, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride,
                                    y_stride, false, st0);
-    if (g_qlinear_kernel == 2)
+    if (g_qlinear_kernel == 2 || x_dtype != dtype)
       return set_error(B200_ERR_UNSUPPORTED,
-                       "qlinear: tcgen05 kernel does not take dtype=%d sb_dtype=%d K=%d x_stride=%lld",
-                       dtype, sb_dtype, K, (long long)x_stride);
+                       "qlinear: tcgen05 kernel does not take x_dtype=%d dtype=%d sb_dtype=%d K=%d x_stride=%lld "
+                       "(it reads fp16 x -- b200_cast_bf16_to_f16 -- and writes bf16)",
+                       x_dtype, dtype, sb_dtype, K, (long long)x_stride);
   }
   B200_CHECK_ARG(x_stride >= K && x_stride % 8 == 0 && ((uintptr_t)x % 16) == 0,
                  "qlinear: x rows must be 16-byte aligned (stride %lld)", (long long)x_stride);
@@ -500,7 +503,7 @@ extern "C" int b200_qlinear_prepack(const uint32_t* w, uint32_t* out, int N, int
 
 extern "C" int b200_qlinear_prepacked(const void* x, const uint32_t* wp, const void* scales,
                                       const void* biases, const void* bias, void* y, int M, int N, int K,
-                                      int group_size, int bits, int dtype, int sb_dtype, int64_t x_stride,
+                                      int group_size, int bits, int x_dtype, int dtype, int sb_dtype, int64_t x_stride,
                                       int64_t y_stride, void* stream) {
   using namespace b200;
   int rc = check_quant_args("qlinear_prepacked", N, K, group_size, bits, sb_dtype);
@@ -509,11 +512,11 @@ extern "C" int b200_qlinear_prepacked(const void* x, const uint32_t* wp, const v
   if (M == 0) return B200_OK;
   B200_CHECK_ARG(x && wp && scales && biases && y, "qlinear_prepacked: null pointer argument");
   B200_CHECK_ARG(y_stride >= N, "qlinear_prepacked: y_stride (%lld) < N (%d)", (long long)y_stride, N);
-  if (!qgemm_tc_supported(x, wp, M, N, K, group_size, bits, dtype, sb_dtype, x_stride))
+  if (!qgemm_tc_supported(x, wp, M, N, K, group_size, bits, x_dtype, dtype, sb_dtype, x_stride))
     return set_error(B200_ERR_UNSUPPORTED,
                      "qlinear_prepacked: the streaming layout is only read by the tcgen05 kernel, which does not "
-                     "take dtype=%d sb_dtype=%d K=%d x_stride=%lld",
-                     dtype, sb_dtype, K, (long long)x_stride);
+                     "take x_dtype=%d (fp16 needed) dtype=%d sb_dtype=%d K=%d x_stride=%lld",
+                     x_dtype, dtype, sb_dtype, K, (long long)x_stride);
   return qgemm_tc_launch(x, wp, scales, biases, bias, y, M, N, K, group_size, bits, dtype, x_stride, y_stride,
                          true, (cudaStream_t)stream);
 }

@@ -162,7 +162,7 @@ def load_library() -> ctypes.CDLL:
     vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
     lib.b200_reshape_and_cache.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i32, vp]
     lib.b200_copy_blocks.argtypes = [vp, vp, vp, vp, i32, i64, i64, vp]
-    lib.b200_qlinear.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i64, i64, vp]
+    lib.b200_qlinear.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, vp]
     lib.b200_qlinear_prepacked.argtypes = lib.b200_qlinear.argtypes
     lib.b200_qlinear_prepack.argtypes = [vp, vp, i32, i32, i32, i32, vp]
     lib.b200_dequantize_rows.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
@@ -222,6 +222,7 @@ class _Ops:
         self._workspaces: dict[int, list[torch.Tensor]] = {}
         self._qstream_ws: dict[int, torch.Tensor] = {}
         self.launches = 0  # kernels launched through this object (bench.py's gpu_launches)
+        self._qlinear_kernel = 0
 
     # -- error plumbing -----------------------------------------------------
     def _check(self, rc: int) -> None:
@@ -444,18 +445,27 @@ class _Ops:
         if x2.stride(1) != 1:
             x2 = x2.contiguous()
         m = x2.shape[0]
+        # result dtype: x's, except an fp16 x into bf16 scales (the tensor-core kernels' operand type) gives bf16
+        odt = torch.bfloat16 if (x.dtype == torch.float16 and scales.dtype == torch.bfloat16) else x.dtype
         if out is None:
-            out = torch.empty((m, n_out), dtype=x.dtype, device=x.device)
+            out = torch.empty((m, n_out), dtype=odt, device=x.device)
         y2 = out.reshape(m, n_out)
         if bias is not None:
-            bias = bias.to(dtype=x.dtype).contiguous()
+            bias = bias.to(dtype=odt).contiguous()
+        n_launch = 1
+        if (x2.dtype == torch.bfloat16 and scales.dtype == torch.bfloat16 and k % 64 == 0
+                and x2.data_ptr() % 16 == 0 and x2.stride(0) % 8 == 0 and self._qlinear_kernel != 1):
+            x2 = self.cast_f16(x2)  # the tcgen05 kernel multiplies fp16 x fp16 (see b200_qlinear)
+            self.launches -= 1
+            n_launch = 2
         fn = self._lib.b200_qlinear_prepacked if prepacked else self._lib.b200_qlinear
         rc = fn(
             x2.data_ptr(), w.contiguous().data_ptr(), scales.contiguous().data_ptr(),
             biases.contiguous().data_ptr(), _ptr(bias), y2.data_ptr(), m, n_out, k, group_size, bits,
-            _dtype_code("x", x), _dtype_code("scales", scales), x2.stride(0), y2.stride(0), _stream())
+            _dtype_code("x", x2), _dtype_code("out", out), _dtype_code("scales", scales), x2.stride(0), y2.stride(0),
+            _stream())
         self._check(rc)
-        self.launches += 1
+        self.launches += n_launch
         return out.reshape(*lead, n_out)
 
     def qlinear_prepack(self, w, bits: int = 4, inverse: bool = False, out=None):
@@ -583,6 +593,7 @@ class _Ops:
     def set_qlinear_kernel(self, kernel: int) -> None:
         """0 = auto, 1 = mma.sync kernel, 2 = tcgen05 kernel (raises if the shape does not qualify)."""
         self._check(self._lib.b200_set_qlinear_kernel(int(kernel)))
+        self._qlinear_kernel = int(kernel)
 
     def set_qlinear_tuning(self, ksplit: int = 0, dequant_warps: int = 0) -> None:
         """Sweep knob of the tcgen05 kernel's M <= 64 regime (0 = heuristic)."""
