@@ -41,15 +41,34 @@ CTX = 4096
 BLOCK = 16
 METRIC = "decode tok/s (Llama-3.1-8B int4, bs=64)"
 WORKLOAD = "Llama-3.1-8B affine int4 g64 random-init, paged decode bs=64 ctx 4096 block_size 16 (configs[1])"
+MODEL_DESC = "Llama-3.1-8B (random-init, affine int4 g64 incl. lm_head)"
+
+# --config: the other BASELINE.json configs as bench lines (the default, b, is the headline the driver runs).
+# name: (preset, batch, ctx, metric, workload, model description, min gpus)
+CONFIGS = {
+    "b": (MODEL, BATCH, CTX, METRIC, WORKLOAD, MODEL_DESC, 1),
+    "d": ("gpt-oss-20b-attn", 32, 4096, "decode tok/s (gpt-oss-20b attention blocks int4, bs=32)",
+          "gpt-oss-20b attention blocks (sinks, 128-token window on even layers), int4 g64 q/k/v/o, paged decode "
+          "bs=32 ctx 4096 block_size 16 (configs[3]; MoE MLP out of scope)",
+          "gpt-oss-20b attention blocks (random-init, affine int4 g64 incl. lm_head)", 1),
+    "e": ("llama-3.1-70b", 16, 32768, "decode tok/s (Llama-3.1-70B int4, bs=16, ctx 32k)",
+          "Llama-3.1-70B affine int4 g64 random-init, split-KV paged decode bs=16 ctx 32768 block_size 16 at TP=8 "
+          "(configs[4])", "Llama-3.1-70B (random-init, affine int4 g64 incl. lm_head)", 8),
+}
+
+
+def select_config(name: str) -> None:
+    global MODEL, BATCH, CTX, METRIC, WORKLOAD, MODEL_DESC
+    MODEL, BATCH, CTX, METRIC, WORKLOAD, MODEL_DESC, _ = CONFIGS[name]
 
 
 def base_config(gpus: int) -> dict:
     """The workload description both arms print (key-identical dicts)."""
-    return {"workload": WORKLOAD, "model": "Llama-3.1-8B (random-init, affine int4 g64 incl. lm_head)",
+    return {"workload": WORKLOAD, "model": MODEL_DESC,
             "global_batch": BATCH, "ctx": CTX, "block_size": BLOCK, "kv_cache": "bf16",
             "parallelism": f"tp{gpus}", "decode_steps_timed": "steps",
-            "l2_policy": "inputs larger than L2: every step streams the whole KV pool (32 GiB over all ranks) "
-                         "and all weights (4.2 GB)"}
+            "l2_policy": "inputs larger than L2: every step streams the whole KV pool and all weights "
+                         "(sizes in per_rank_resident)"}
 
 
 def _ncu_traffic(summary: str) -> float | None:
@@ -311,7 +330,8 @@ def run_b200(args) -> None:
     max_len = CTX + 2 * total + 8
     blocks_per_seq = (max_len + BLOCK - 1) // BLOCK
     nb = 1 + BATCH * blocks_per_seq
-    cache = B200PagedKVCache(a.num_layers, a.n_kv_heads // world, a.head_dim, nb, BLOCK, torch.bfloat16, dev)
+    cache = B200PagedKVCache(a.num_layers, a.n_kv_heads // world, a.head_dim, nb, BLOCK, torch.bfloat16, dev,
+                             sliding_window_per_layer=a.sliding_window_per_layer())
     g = torch.Generator(device=dev).manual_seed(3 + rank)
     for t in (cache._k_all, cache._v_all):
         for i in range(a.num_layers):
@@ -399,23 +419,27 @@ def run_b200(args) -> None:
     peak, peak_src = _peaks()
     achieved = alg_bytes / (attn_ms * 1e-3) / 1e9
 
-    # ---------------- secondary: int4 GEMV (gate_up) ----------------------------------------
+    # ---------------- secondary: int4 GEMV (gate_up + fused SwiGLU, stream-K kernel) --------
+    # every layer's own blob in turn (32 x 57 MB >> L2), x in fp16 as the decoder's norm hands it over
+    gemv_ms, gemv_bytes, gemv_gbs = 0.0, 0.0, 0.0
     mlp = model.layers[0].mlp
-    x = torch.randn((BATCH, a.hidden), device=dev, generator=g).bfloat16()
-    for _ in range(3):
-        for layer in model.layers:
-            layer.mlp.gate_up_proj(x)
-    barrier()
-    e0.record()
-    for _ in range(reps):
-        for layer in model.layers:
-            layer.mlp.gate_up_proj(x)
-    e1.record()
-    barrier()
-    gemv_ms = e0.elapsed_time(e1) / (reps * a.num_layers)
-    n_gu, k_gu = mlp.gate_up_proj.out_features, mlp.gate_up_proj.in_features
-    gemv_bytes = n_gu * k_gu * (a.bits / 8 + 4 / a.group_size) + BATCH * (k_gu + n_gu) * 2
-    gemv_gbs = gemv_bytes / (gemv_ms * 1e-3) / 1e9
+    if mlp is not None:
+        x = torch.randn((BATCH, a.hidden), device=dev, generator=g).half()
+        for _ in range(3):
+            for layer in model.layers:
+                layer.mlp.gate_up_proj(x, out_f16=True)
+        barrier()
+        e0.record()
+        for _ in range(reps):
+            for layer in model.layers:
+                layer.mlp.gate_up_proj(x, out_f16=True)
+        e1.record()
+        barrier()
+        gemv_ms = e0.elapsed_time(e1) / (reps * a.num_layers)
+        n_gu, k_gu = mlp.gate_up_proj.out_features, mlp.gate_up_proj.in_features
+        n_out = n_gu // 2 if mlp.gate_up_proj.swiglu else n_gu
+        gemv_bytes = n_gu * k_gu * (a.bits / 8 + 4 / a.group_size) + BATCH * (k_gu + n_out) * 2
+        gemv_gbs = gemv_bytes / (gemv_ms * 1e-3) / 1e9
 
     # max over ranks
     times = torch.tensor([dev_ms, e2e_ms, attn_ms, gemv_ms], device=dev, dtype=torch.float64)
@@ -424,7 +448,7 @@ def run_b200(args) -> None:
     dev_ms, e2e_ms, attn_ms, gemv_ms = times.tolist()
 
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.config == "b":
         layers = 6
         cs = CpuSample()
         cs.layer()
@@ -453,12 +477,16 @@ def run_b200(args) -> None:
             "roofline": {"bound": "hbm", "kernel": "paged_decode_mma_kernel (+ split_reduce_kernel)",
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0,
-                         "traffic": _ncu_traffic("r01_attn_full_summary.txt") if world == 1 else None,
-                         "traffic_source": "profiles/r01_attn_full_summary.txt (ncu --set full, same shape)",
+                         "traffic": _ncu_traffic("r01_attn_full_summary.txt") if world == 1 and args.config == "b" else None,
+                         "traffic_source": "profiles/r01_attn_full_summary.txt (ncu --set full, same shape; the "
+                                           "attention kernel is unchanged since)",
                          "bytes_per_launch": alg_bytes, "us_per_launch": attn_ms * 1e3},
-            "roofline_qgemv": {"bound": "hbm", "kernel": "qgemm_tc_kernel, A tile in TMEM (gate_up 28672x4096 int4 g64, M=64)",
-                               "achieved": gemv_gbs, "peak": peak, "unit": "GB/s", "frac": gemv_gbs / peak,
-                               "bytes_per_launch": gemv_bytes, "us_per_launch": gemv_ms * 1e3},
+            "roofline_qgemv": None if mlp is None else {
+                "bound": "hbm",
+                "kernel": f"qgemm_stream_kernel, persistent stream-K, fp16 A in TMEM, SwiGLU epilogue "
+                          f"(gate_up {n_gu}x{k_gu} int{a.bits} g{a.group_size}, M={BATCH})",
+                "achieved": gemv_gbs, "peak": peak, "unit": "GB/s", "frac": gemv_gbs / peak,
+                "bytes_per_launch": gemv_bytes, "us_per_launch": gemv_ms * 1e3},
             "cpu_baseline": cpu,
         }
         _emit(json.dumps(line))
@@ -494,11 +522,16 @@ def main() -> None:
     _capture_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--steps", type=int, default=128)  # >= 1 s timed at the headline config
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", default="b", choices=sorted(CONFIGS), help="BASELINE.json config (default b = headline)")
     args = ap.parse_args()
+    select_config(args.config)
+    if args.gpus < CONFIGS[args.config][6] and args.impl == "b200":
+        _emit(json.dumps({"config": args.config, "unavailable": f"config {args.config} needs --gpus >= {CONFIGS[args.config][6]}"}))
+        return
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":

@@ -33,6 +33,30 @@ def test_register_entry_points_resolve():
         B200Platform.get_attn_backend_cls(None, types.SimpleNamespace(use_sparse=True))
 
 
+def test_pyproject_declares_the_reference_entry_point_groups(monkeypatch):
+    """vLLM finds the plugin through the two groups the reference declares (pyproject.toml:104-112); each
+    target must resolve to a callable, and register() stays inert without the operator's opt-in."""
+    import importlib
+    import os
+    import tomllib
+
+    import vllm_metal_b200 as pkg
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with open(os.path.join(root, "pyproject.toml"), "rb") as f:
+        eps = tomllib.load(f)["project"]["entry-points"]
+    assert set(eps) == {"vllm.platform_plugins", "vllm.general_plugins"}
+    for group in eps.values():
+        for target in group.values():
+            mod, _, fn = target.partition(":")
+            assert callable(getattr(importlib.import_module(mod), fn))
+    monkeypatch.delenv("VLLM_B200_PLUGIN", raising=False)
+    assert pkg.register() is None
+    monkeypatch.setenv("VLLM_B200_PLUGIN", "1")
+    monkeypatch.setattr(pkg, "_cuda_sm100_available", lambda: True)
+    assert pkg.register() == pkg.PLATFORM_CLS
+
+
 def test_synthetic_backend_advertises_multiple_of_16_and_refuses_dispatch():
     from vllm.v1.attention.backend import MultipleOf
 

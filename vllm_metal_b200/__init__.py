@@ -28,7 +28,14 @@ def _cuda_sm100_available() -> bool:
 
 
 def register() -> str | None:
-    """``vllm.platform_plugins`` entry point (reference ``_register``, __init__.py:117-145)."""
+    """``vllm.platform_plugins`` entry point (reference ``_register``, __init__.py:117-145).
+
+    Claims the platform only on an sm_100 device AND when ``VLLM_B200_PLUGIN=1`` is set: vLLM's in-tree
+    CUDA platform also runs on a B200, so taking the device over must be the operator's explicit choice."""
+    import os
+
+    if os.environ.get("VLLM_B200_PLUGIN", "0") in ("", "0"):
+        return None
     return PLATFORM_CLS if _cuda_sm100_available() else None
 
 
