@@ -15,6 +15,7 @@ struct SplitWorkspace {
   float* exp_sum;
   int num_partitions;  // P
   int partition_size;  // tokens
+  int skip_qlen;       // > 0: rows of sequences with q_len >= skip_qlen belong to the tile kernel (left untouched here)
 };
 
 inline size_t split_workspace_bytes(int64_t T, int64_t Hq, int64_t P, int64_t D) {
@@ -29,6 +30,7 @@ inline SplitWorkspace carve_workspace(void* ws, int64_t T, int64_t Hq, int64_t P
   w.exp_sum = w.max_l2 + T * Hq * P;
   w.num_partitions = (int)P;
   w.partition_size = partition_size;
+  w.skip_qlen = 0;
   return w;
 }
 
@@ -54,12 +56,13 @@ struct RowInfo {
 };
 __device__ __forceinline__ RowInfo row_info(const int32_t* __restrict__ cu,
                                             const int32_t* __restrict__ seq_lens, int num_seqs,
-                                            int t, int sliding_window) {
+                                            int t, int sliding_window, int skip_qlen = 0) {
   RowInfo r;
   r.seq = find_seq_idx(cu, num_seqs, t);
   const int q_start = cu[r.seq];
   const int q_len = cu[r.seq + 1] - q_start;
   r.eff = seq_lens[r.seq] - q_len + (t - q_start) + 1;
+  if (skip_qlen > 0 && q_len >= skip_qlen) r.eff = 0;  // mixed batch: the tile kernel owns this sequence
   r.beg = 0;
   r.base = 0;
   if (sliding_window >= 0) {
@@ -71,9 +74,12 @@ __device__ __forceinline__ RowInfo row_info(const int32_t* __restrict__ cu,
 
 // Launchers implemented in paged_attention_generic.cu / paged_attention_decode.cu.
 // `ws == nullptr` => single pass.
-int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st);
+int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st, int skip_qlen = 0);
 bool decode_mma_supported(const b200_paged_attn_args& a);
-int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st);
+int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st, int skip_qlen = 0);
 int launch_split_reduce(const b200_paged_attn_args& a, const SplitWorkspace& ws, cudaStream_t st);
+// Tile kernel (paged_attention_prefill.cu): sequences with q_len >= min_qlen, one CTA per (128-row Q tile, q head).
+bool prefill_tc_supported(const b200_paged_attn_args& a);
+int launch_prefill_tc(const b200_paged_attn_args& a, int min_qlen, cudaStream_t st);
 
 }  // namespace b200

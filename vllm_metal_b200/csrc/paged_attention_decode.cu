@@ -122,7 +122,7 @@ paged_decode_mma_kernel(const DecodeParams p) {
   const int g = lane >> 2, tq = lane & 3;
   const int G = p.group;
 
-  const RowInfo ri = row_info(p.cu_seqlens_q, p.seq_lens, p.num_seqs, t, p.sliding_window);
+  const RowInfo ri = row_info(p.cu_seqlens_q, p.seq_lens, p.num_seqs, t, p.sliding_window, p.ws.skip_qlen);
   const int s = ri.seq, eff = ri.eff;  // pagedattention.metal:913
   if (eff <= 0) return;                // :917-920
   int beg = ri.beg, end = eff;         // window: :1129-1133
@@ -380,7 +380,7 @@ static int launch_one(const DecodeParams& p, dim3 grid, cudaStream_t st) {
   return check_launch("paged_decode_mma_kernel");
 }
 
-int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st) {
+int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st, int skip_qlen) {
   DecodeParams p{};
   p.out = a.out;
   p.query = a.query;
@@ -406,7 +406,9 @@ int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, c
   p.scale = a.scale;
   p.softcap = a.softcap;
   p.partitioned = ws != nullptr;
+  p.ws = SplitWorkspace{};
   if (ws) p.ws = *ws;
+  p.ws.skip_qlen = skip_qlen;
   dim3 grid(a.num_kv_heads, a.num_q_tokens, ws ? ws->num_partitions : 1);
   if (a.dtype == B200_BF16) {
     if (a.head_dim == 128) return launch_one<__nv_bfloat16, 128, 3>(p, grid, st);

@@ -35,7 +35,7 @@ paged_attention_generic_kernel(T* __restrict__ out, const T* __restrict__ query,
   const int part = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  const RowInfo ri = row_info(cu_seqlens_q, seq_lens, num_seqs, t, sliding_window);
+  const RowInfo ri = row_info(cu_seqlens_q, seq_lens, num_seqs, t, sliding_window, ws.skip_qlen);
   const int s = ri.seq, eff = ri.eff;  // eff: pagedattention.metal:913
   if (eff <= 0) return;                // :917-920 (row left untouched)
 
@@ -162,7 +162,7 @@ split_reduce_kernel(T* __restrict__ out, const int32_t* __restrict__ seq_lens,
   pdl_trigger();
   pdl_wait();
   const int h = blockIdx.x, t = blockIdx.y;
-  const RowInfo ri = row_info(cu_seqlens_q, seq_lens, num_seqs, t, sliding_window);
+  const RowInfo ri = row_info(cu_seqlens_q, seq_lens, num_seqs, t, sliding_window, ws.skip_qlen);
   const int eff = ri.eff;
   if (eff <= 0) return;
   int np = (eff - ri.base + ws.partition_size - 1) / ws.partition_size;  // :1946
@@ -201,11 +201,12 @@ static int log2_exact(int v) {
   return (1 << s) == v ? s : -1;
 }
 
-int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st) {
+int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st, int skip_qlen) {
   const int shift = log2_exact(a.block_size);
   const size_t smem = (2 * kGenericWarps + (size_t)kGenericWarps * a.head_dim) * sizeof(float);
   SplitWorkspace w{};
   if (ws) w = *ws;
+  w.skip_qlen = skip_qlen;
   dim3 grid(a.num_q_heads, a.num_q_tokens, ws ? ws->num_partitions : 1);
   return B200_DISPATCH_DTYPE(a.dtype, T, [&]() -> int {
     launch_pdl(paged_attention_generic_kernel<T>, dim3(grid), dim3(kGenericWarps * 32), smem, st, 
@@ -316,6 +317,22 @@ extern "C" int b200_paged_attention(const b200_paged_attn_args* a, void* stream)
   if (rc != B200_OK) return rc;
   if (a->num_q_tokens == 0 || a->num_seqs == 0) return B200_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  // Varlen prefill / mixed batches (reference paged_ops.cpp:463-497 sends them to the tiled kernel): sequences
+  // with at least kTileMinQlen query rows run on the tcgen05 tile kernel, the remaining (decode) rows of a mixed
+  // batch on the per-row kernels below, which leave the tile kernel's sequences untouched.
+  constexpr int kTileMinQlen = 16;
+  int skip_qlen = 0;
+  const bool tile_ok = prefill_tc_supported(*a);
+  if (a->kernel == 3 && !tile_ok)
+    return set_error(B200_ERR_UNSUPPORTED,
+                     "paged_attention: the tcgen05 tile kernel needs bf16/fp16, head_dim 64/128, block_size | 128 and "
+                     "a contiguous [blocks, block_size, kv_heads, head_dim] cache");
+  if (a->kernel == 3 || (a->kernel == 0 && tile_ok && a->num_q_tokens - a->num_seqs + 1 >= kTileMinQlen)) {
+    // kernel == 3 pins every sequence to the tile kernel (parity tests); auto keeps short ones on the row kernels
+    skip_qlen = a->kernel == 3 ? 1 : kTileMinQlen;
+    rc = launch_prefill_tc(*a, skip_qlen, st);
+    if (rc != B200_OK || a->kernel == 3) return rc;
+  }
   const bool mma = pick_mma(*a);
   if (a->kernel == 2 && !mma)
     return set_error(B200_ERR_UNSUPPORTED,
@@ -339,7 +356,8 @@ extern "C" int b200_paged_attention(const b200_paged_attn_args* a, void* stream)
     }
   }
   const SplitWorkspace* wsp = parts > 1 ? &ws : nullptr;
-  rc = mma ? launch_decode_mma(*a, wsp, st) : launch_generic(*a, wsp, st);
+  if (wsp) ws.skip_qlen = skip_qlen;
+  rc = mma ? launch_decode_mma(*a, wsp, st, skip_qlen) : launch_generic(*a, wsp, st, skip_qlen);
   if (rc != B200_OK) return rc;
   if (wsp) rc = launch_split_reduce(*a, ws, st);
   return rc;
