@@ -90,7 +90,15 @@ struct Smem {
   static constexpr int TOTAL = Q_BYTES + 2 * STAGES * KV_BYTES + 1024 /*barriers*/ + 1024 /*align*/;
 };
 
-template <int D>
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// SOFTCAP is a template flag so that the (rare) tanh path never sits in the hot loop's instruction stream: with it
+// inline the unrolled softmax body was ~150 KB of SASS and the four softmax warps ran out of the instruction cache.
+template <int D, bool SOFTCAP>
 __global__ void __launch_bounds__(THREADS, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
                   const __grid_constant__ CUtensorMap v_map, const Params p) {
@@ -99,7 +107,9 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
   pdl_trigger();
   pdl_wait();  // the metadata (seq_lens advance on the device), q, the caches come from earlier kernels of the step
   // ---- which (sequence, local Q tile) is this CTA: largest i with cu[i]/BQ + i <= tile (reference :162-171)
-  const int tile = blockIdx.x, h = blockIdx.y;
+  // CTAs are dispatched in blockIdx order: hand out the LAST tiles first -- under a causal mask they walk the most
+  // KV blocks, so the long ones start early and the short ones fill the tail of the last wave
+  const int tile = gridDim.x - 1 - blockIdx.x, h = blockIdx.y;
   int lo_i = 0, hi_i = p.num_seqs;
   while (hi_i - lo_i > 1) {
     const int mid = (lo_i + hi_i) >> 1;
@@ -279,6 +289,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
     const int row_hi = r < nrows ? min(seq_len, qabs + 1) : 0;
     const int row_lo = p.sliding_window >= 0 ? max(0, qabs + 1 - p.sliding_window) : 0;
     const float sc = p.scale * kLog2e;
+    const float cap_in = SOFTCAP ? p.scale / p.softcap : 0.f, cap_out = SOFTCAP ? p.softcap * kLog2e : 0.f;  // tanh(s*scale/c)*c
+    (void)cap_in; (void)cap_out;
     float m_used = -INFINITY, m_true = -INFINITY, l = 0.f;
     for (int it = 0; it < nblk; ++it) {
       const int b = it & 1;
@@ -297,14 +309,25 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
       if (lane == 0) mbar_arrive(bar_s_free + 8 * b);
       const int kv0 = (j0 + it) * BK;
       float m_blk = -INFINITY;
+      // blocks wholly inside every row's [row_lo, row_hi) of this warp need no mask (the common case away from
+      // the causal diagonal and the window edge)
+      const bool need_mask = __any_sync(0xffffffffu, kv0 < row_lo || kv0 + BK > row_hi);
+      if (need_mask) {
 #pragma unroll
-      for (int c = 0; c < BK; ++c) {
-        float x = s[c] * sc;
-        if (p.softcap > 0.f) x = tanhf(s[c] * p.scale / p.softcap) * p.softcap * kLog2e;
-        const int kv = kv0 + c;
-        x = (kv >= row_lo && kv < row_hi) ? x : -INFINITY;
-        s[c] = x;
-        m_blk = fmaxf(m_blk, x);
+        for (int c = 0; c < BK; ++c) {
+          float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out : s[c] * sc;
+          const int kv = kv0 + c;
+          x = (kv >= row_lo && kv < row_hi) ? x : -INFINITY;
+          s[c] = x;
+          m_blk = fmaxf(m_blk, x);
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < BK; ++c) {
+          const float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out : s[c] * sc;
+          s[c] = x;
+          m_blk = fmaxf(m_blk, x);
+        }
       }
       m_true = fmaxf(m_true, m_blk);
       const float m_new = (m_blk > m_used + kRescaleThreshold) ? m_blk : m_used;
@@ -387,10 +410,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
   }
 }
 
-template <int D>
+template <int D, bool SOFTCAP>
 static int launch(const b200_paged_attn_args& a, int min_qlen, cudaStream_t st) {
   using SM = Smem<D>;
-  auto kern = prefill_tc_kernel<D>;
+  auto kern = prefill_tc_kernel<D, SOFTCAP>;
   static int configured_dev[16] = {0};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
@@ -462,7 +485,8 @@ bool prefill_tc_supported(const b200_paged_attn_args& a) {
 }
 
 int launch_prefill_tc(const b200_paged_attn_args& a, int min_qlen, cudaStream_t st) {
-  return a.head_dim == 128 ? pf::launch<128>(a, min_qlen, st) : pf::launch<64>(a, min_qlen, st);
+  if (a.softcap > 0.f) return a.head_dim == 128 ? pf::launch<128, true>(a, min_qlen, st) : pf::launch<64, true>(a, min_qlen, st);
+  return a.head_dim == 128 ? pf::launch<128, false>(a, min_qlen, st) : pf::launch<64, false>(a, min_qlen, st);
 }
 
 }  // namespace b200
