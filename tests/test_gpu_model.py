@@ -155,3 +155,85 @@ def test_cfg_a_qwen3_0p6b_128_free_running_greedy_steps():
         cur, seq_len = nxt, seq_len + 1
     assert len(tokens) == steps
     print(f"cfg a: {steps} free-running greedy steps, {len(ties)} bf16-ulp ties at steps {ties}")
+
+
+def test_worker_with_vllm_scheduler_outputs_matches_oracle():
+    """B2 end to end on the device: ``B200Worker.execute_model(SchedulerOutput)`` / ``sample_tokens`` driven the way
+    vLLM's engine core does (new request -> chunked prefill in two chunks -> 16 free-running decode steps, a second
+    request joining mid-way), real runner + kernels underneath, every sampled token checked against the oracle
+    stepped along the same trajectory (<= 1 bf16 ulp tie rule of the cfg-a test)."""
+    pytest.importorskip("vllm")
+    from vllm.v1.core.sched.output import CachedRequestData, NewRequestData, SchedulerOutput
+
+    from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
+    from vllm_metal_b200.lm.decoder import PRESETS, Model
+    from vllm_metal_b200.v1.model_runner import PagedModelRunner
+    from vllm_metal_b200.v1.worker import B200Worker
+
+    args, bs = PRESETS["tiny"], 16
+    model = Model(args, torch.bfloat16, "cuda", seed=3)
+    nb = 24
+    cache = B200PagedKVCache(args.num_layers, args.n_kv_heads, args.head_dim, nb, bs, torch.bfloat16, "cuda")
+    w = object.__new__(B200Worker)
+    w._requests, w._pending = {}, None
+    w.model, w.kv_cache = model, cache
+    w.model_runner = PagedModelRunner(model, cache, max_batch=4, max_model_len=8 * bs, use_cuda_graph=True)
+    oracle = oracle_from_model(model, nb, bs)
+    rng = np.random.default_rng(11)
+    prompts = {"A": rng.integers(0, args.vocab, 40).tolist(), "B": rng.integers(0, args.vocab, 21).tolist()}
+    blocks = {"A": [5, 9, 2, 17, 11], "B": [3, 20, 7]}
+    known = {k: list(v) for k, v in prompts.items()}  # what the engine knows: prompt + sampled tokens
+    computed = {"A": 0, "B": 0}
+    live: list[str] = []
+
+    def sched(new, num):
+        new_reqs = [NewRequestData(req_id=r, prompt_token_ids=prompts[r], mm_features=[], sampling_params=None,
+                                   pooling_params=None, block_ids=(blocks[r][:(computed[r] + num[r] + bs - 1) // bs],),
+                                   num_computed_tokens=0, lora_request=None) for r in new]
+        old = [r for r in live if r not in new and r in num]
+        nbk = []
+        for r in old:  # blocks the scheduler hands out as the sequence grows
+            have = (computed[r] + bs - 1) // bs
+            need = (computed[r] + num[r] + bs - 1) // bs
+            nbk.append((blocks[r][have:need],) if need > have else None)
+        cached = CachedRequestData(req_ids=old, resumed_req_ids=set(), new_token_ids=[[] for _ in old], all_token_ids={},
+                                   new_block_ids=nbk, num_computed_tokens=[computed[r] for r in old],
+                                   num_output_tokens=[len(known[r]) - len(prompts[r]) for r in old])
+        return SchedulerOutput(scheduled_new_reqs=new_reqs, scheduled_cached_reqs=cached, num_scheduled_tokens=num,
+                               total_num_scheduled_tokens=sum(num.values()), scheduled_spec_decode_tokens={},
+                               scheduled_encoder_inputs={}, num_common_prefix_blocks=[0], finished_req_ids=set(),
+                               free_encoder_mm_hashes=[])
+
+    def step(new, num):
+        for r in new:
+            live.append(r)
+        assert w.execute_model(sched(new, num)) is None
+        out = w.sample_tokens(None)
+        # the oracle runs the same rows in the worker's packing order (decode rows first)
+        dec = [r for r in out.req_ids if num[r] == 1 and computed[r] > 0]
+        pre = [r for r in out.req_ids if r not in dec]
+        assert out.req_ids == dec + pre
+        ids = [known[r][computed[r]] for r in dec] + [t for r in pre for t in known[r][computed[r]:computed[r] + num[r]]]
+        ologits = oracle.forward(ids, [(blocks[r], computed[r]) for r in dec],
+                                 [(blocks[r], num[r], computed[r]) for r in pre])
+        want = oracle.greedy(ologits).tolist()
+        for i, r in enumerate(out.req_ids):
+            toks = out.sampled_token_ids[i]
+            if computed[r] + num[r] < len(known[r]):
+                assert toks == []  # partial prefill chunk samples nothing
+            else:
+                assert len(toks) == 1
+                if toks[0] != want[i]:
+                    gap = float(ologits[i, want[i]] - ologits[i, toks[0]])
+                    assert gap <= 2.0 ** (int(np.floor(np.log2(abs(float(ologits[i, want[i]])) + 1e-30))) - 7), (r, toks, want[i], gap)
+                known[r].append(toks[0])
+            computed[r] += num[r]
+
+    step(["A"], {"A": 24})            # chunk 1 of A's 40-token prompt
+    step([], {"A": 16})               # chunk 2 finishes the prompt -> first token
+    for i in range(16):
+        if i == 4:
+            step(["B"], {"A": 1, "B": 21})  # B joins: A's decode row is packed before B's prefill
+        else:
+            step([], {r: 1 for r in live})
+    assert len(known["A"]) == 40 + 17 and len(known["B"]) == 21 + 12

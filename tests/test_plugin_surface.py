@@ -146,11 +146,91 @@ def test_worker_kv_cache_spec_names_and_window_types():
     assert w.get_cache_block_size_bytes() == 2 * 4 * 16 * 2 * 64 * 2
 
 
-def test_worker_packs_decodes_before_prefills():
+class _SpyRunner:
+    """Stands where PagedModelRunner does: records what the worker packs, returns one token per sequence."""
+
+    use_cuda_graph = False
+
+    def __init__(self):
+        self.calls = []
+        self.next_tok = 1000
+
+    def execute(self, tokens, decodes, prefills):
+        self.calls.append((list(tokens), [(list(b), n) for b, n in decodes], [(list(b), q, o) for b, q, o in prefills]))
+        out = list(range(self.next_tok, self.next_tok + len(decodes) + len(prefills)))
+        self.next_tok += len(out)
+        return out
+
+
+def _sched(new=(), cached=None, num=None, finished=()):
+    from vllm.v1.core.sched.output import CachedRequestData, SchedulerOutput
+
+    cached = cached or CachedRequestData(req_ids=[], resumed_req_ids=set(), new_token_ids=[], all_token_ids={},
+                                         new_block_ids=[], num_computed_tokens=[], num_output_tokens=[])
+    num = num or {}
+    return SchedulerOutput(scheduled_new_reqs=list(new), scheduled_cached_reqs=cached, num_scheduled_tokens=num,
+                           total_num_scheduled_tokens=sum(num.values()), scheduled_spec_decode_tokens={},
+                           scheduled_encoder_inputs={}, num_common_prefix_blocks=[0], finished_req_ids=set(finished),
+                           free_encoder_mm_hashes=[])
+
+
+def test_worker_drives_real_scheduler_outputs_through_chunked_prefill_decode_finish():
+    """B2 with vLLM's own types (reference MetalWorker.execute_model(SchedulerOutput) -> sample_tokens ->
+    ModelRunnerOutput, v1/worker.py:267-285): new request -> chunked prefill (no token for the partial chunk)
+    -> mixed step with a second request's decode row packed FIRST -> finish frees the state."""
+    from vllm.v1.core.sched.output import CachedRequestData, NewRequestData
+    from vllm.v1.outputs import ModelRunnerOutput
+
     from vllm_metal_b200.v1.worker import B200Worker
 
     w = object.__new__(B200Worker)
-    so = types.SimpleNamespace(decodes=[(11, [3, 4], 20), (12, [5], 7)], prefills=[([1, 2, 3], [6], 0)])
-    tokens, dec, pre = w._pack(so)
-    assert tokens == [11, 12, 1, 2, 3]
-    assert dec == [([3, 4], 20), ([5], 7)] and pre == [([6], 3, 0)]
+    w._requests, w._pending = {}, None
+    spy = w.model_runner = _SpyRunner()
+
+    def new_req(rid, prompt, blocks):
+        return NewRequestData(req_id=rid, prompt_token_ids=prompt, mm_features=[], sampling_params=None,
+                              pooling_params=None, block_ids=(blocks,), num_computed_tokens=0, lora_request=None)
+
+    # step 1: request A arrives, 5-token prompt, only 3 scheduled (chunked prefill); B arrives whole (2 tokens)
+    so = _sched(new=[new_req("A", [10, 11, 12, 13, 14], [7]), new_req("B", [20, 21], [9])], num={"A": 3, "B": 2})
+    assert w.execute_model(so) is None  # deferred-sampling contract
+    out = w.sample_tokens(None)
+    assert isinstance(out, ModelRunnerOutput)
+    assert spy.calls[-1] == ([10, 11, 12, 20, 21], [], [([7], 3, 0), ([9], 2, 0)])
+    assert out.req_ids == ["A", "B"] and out.sampled_token_ids == [[], [1001]]  # A's chunk is partial: no token
+    assert out.req_id_to_index == {"A": 0, "B": 1}
+
+    # step 2: A finishes its prompt (2 more tokens, a new block), B decodes: decode rows are packed first
+    cached = CachedRequestData(req_ids=["A", "B"], resumed_req_ids=set(), new_token_ids=[[], []], all_token_ids={},
+                               new_block_ids=[([8],), None], num_computed_tokens=[3, 2], num_output_tokens=[0, 1])
+    w.execute_model(_sched(cached=cached, num={"A": 2, "B": 1}))
+    out = w.sample_tokens(None)
+    assert spy.calls[-1] == ([1001, 13, 14], [([9], 2)], [([7, 8], 2, 3)])
+    assert out.req_ids == ["B", "A"] and out.sampled_token_ids == [[1002], [1003]]
+
+    # step 3: both decode; B finished last step -> its state is dropped, A continues alone
+    cached = CachedRequestData(req_ids=["A"], resumed_req_ids=set(), new_token_ids=[[]], all_token_ids={},
+                               new_block_ids=[None], num_computed_tokens=[5], num_output_tokens=[1])
+    w.execute_model(_sched(cached=cached, num={"A": 1}, finished=["B"]))
+    out = w.sample_tokens(None)
+    assert "B" not in w._requests
+    assert spy.calls[-1] == ([1003], [([7, 8], 5)], [])
+    assert out.sampled_token_ids == [[1004]] and w._requests["A"].tokens[-3:] == [14, 1003, 1004]
+    assert w.sample_tokens(None) is None  # nothing pending
+
+
+def test_worker_rejects_what_it_does_not_implement():
+    from vllm_metal_b200.v1.worker import B200Worker
+
+    w = object.__new__(B200Worker)
+    w._requests, w._pending, w.model_runner = {}, None, _SpyRunner()
+    with pytest.raises(NotImplementedError, match="SchedulerOutput"):
+        w.execute_model(types.SimpleNamespace(decodes=[], prefills=[]))  # the old private duck type
+    so = _sched()
+    so.scheduled_spec_decode_tokens = {"A": [1]}
+    with pytest.raises(NotImplementedError, match="speculative"):
+        w.execute_model(so)
+    w.execute_model(_sched())
+    with pytest.raises(NotImplementedError, match="structured"):
+        w.sample_tokens(object())
+    assert w.get_supported_tasks() == ("generate",) and w.take_draft_token_ids() is None

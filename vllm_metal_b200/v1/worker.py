@@ -53,6 +53,16 @@ def model_args_from_hf_config(hf_config: Any, quant: dict | None = None) -> Mode
     return dataclasses.replace(PRESETS["tiny"], **{k: v for k, v in fields.items() if k in known})
 
 
+class _RequestState:
+    """What the runner keeps per live request (reference RequestState, model_runner.py:1150-1200): every known
+    token id (prompt + generated), the block ids of KV group 0 and how many tokens are already in the cache."""
+
+    __slots__ = ("tokens", "block_ids", "num_computed")
+
+    def __init__(self, tokens: list[int], block_ids: list[int], num_computed: int) -> None:
+        self.tokens, self.block_ids, self.num_computed = tokens, block_ids, num_computed
+
+
 class B200Worker(WorkerBase):
     """One process per GPU; ``rank`` is the tensor-parallel rank."""
 
@@ -65,7 +75,8 @@ class B200Worker(WorkerBase):
         self.kv_cache: B200PagedKVCache | None = None
         self.model_runner: PagedModelRunner | None = None
         self._allreduce = None
-        self._pending: list[int] | None = None
+        self._pending = None
+        self._requests: dict[str, _RequestState] = {}
 
     # ---- device / distributed (worker.py:117-193) -----------------------------
     def init_device(self) -> None:
@@ -85,6 +96,13 @@ class B200Worker(WorkerBase):
             self._allreduce = NVLinkAllReduce(device=self.device, max_bytes=min(max_tokens, 256) * hidden * 2)
 
     def load_model(self) -> None:
+        """Builds the decoder for the HF config with RANDOM-INITIALISED affine-quantized weights (``seed``):
+        the BASELINE configs are all random-init and no checkpoint reader is wired (the AWQ repack path is
+        ``quant/awq_loader.py``; safetensors loading is out of scope).  ``load_format`` other than
+        "dummy"/"auto" therefore raises instead of silently ignoring a checkpoint."""
+        lf = str(getattr(getattr(self.vllm_config, "load_config", None), "load_format", "dummy"))
+        if lf not in ("dummy", "auto", "LoadFormat.DUMMY", "LoadFormat.AUTO"):
+            raise NotImplementedError(f"load_format={lf}: only random-init ('dummy') weights are wired on this path")
         args = model_args_from_hf_config(self.model_config.hf_config)
         world = self.parallel_config.tensor_parallel_size
         self.model = Model(args, torch.bfloat16, self.device, seed=int(self.model_config.seed or 0),
@@ -100,8 +118,14 @@ class B200Worker(WorkerBase):
         return 2 * a.num_layers * self.cache_config.block_size * (a.n_kv_heads // world) * a.head_dim * 2
 
     def determine_available_memory(self) -> int:
+        """Bytes the KV cache may take: the utilisation budget minus everything resident NOW -- called after
+        ``load_model`` (vLLM's order), so the weights are inside ``total - free``; the stream-K workspace and
+        graph pools allocated later are covered by a fixed 1 GiB reserve."""
+        if self.model is None:
+            raise RuntimeError("determine_available_memory must follow load_model (weights are not resident yet)")
+        torch.cuda.synchronize(self.device)
         free, total = torch.cuda.mem_get_info(self.device)
-        budget = int(total * self.cache_config.gpu_memory_utilization) - (total - free)
+        budget = int(total * self.cache_config.gpu_memory_utilization) - (total - free) - (1 << 30)
         return max(budget, 0)
 
     def get_kv_cache_spec(self) -> dict[str, KVCacheSpec]:
@@ -134,35 +158,115 @@ class B200Worker(WorkerBase):
                                              use_cuda_graph=not self.model_config.enforce_eager)
 
     def compile_or_warm_up_model(self) -> float:
+        """Capture the decode CUDA graphs the first real steps would otherwise pay for (reference
+        ``compile_or_warm_up_model`` returns CompilationTimes, worker.py:252-257; vLLM 0.22 takes the
+        elapsed seconds): one dummy decode step per batch bucket on the padding block."""
         start = time.perf_counter()
+        r = self.model_runner
+        if r is not None and r.use_cuda_graph:
+            for b in sorted({1, min(8, r.max_batch), r.max_batch}):
+                r.decode_step([0] * b, [[0]] * b, [1] * b)  # block 0 is the reserved padding block
         torch.cuda.synchronize(self.device)
         return time.perf_counter() - start
 
-    # ---- step (worker.py:267-285; model_runner.py:1138-1410) -------------------
+    # ---- step (worker.py:267-285; model_runner.py:1138-1410, 2733-2783) ----------
     def execute_model(self, scheduler_output: Any) -> None:
-        """Pack the scheduled requests (decode rows first, then prefill chunks -- the reference's
-        order, model_runner.py batch packing) and run the step; tokens are handed out by
-        ``sample_tokens`` (deferred sampling contract)."""
-        tokens, decodes, prefills = self._pack(scheduler_output)
-        self._pending = self.model_runner.execute(tokens, decodes, prefills) if tokens else []
-
-    def sample_tokens(self, grammar_output: Any = None) -> list[int]:
-        out, self._pending = self._pending or [], None
-        return out
-
-    def _pack(self, so: Any):
-        """``scheduler_output`` duck type used here: ``.decodes`` = [(token, block_ids, seq_len)],
-        ``.prefills`` = [(tokens, block_ids, start_pos)] -- the per-step facts the reference's
-        runner extracts from vLLM's SchedulerOutput before ``prepare_grouped``."""
+        """Consume vLLM's ``SchedulerOutput``: update the per-request state (reference
+        ``_start_paged_forward``, model_runner.py:1138-1240), pack decode rows first, then prefill
+        chunks (the reference's packing order, attention/context.py:198-283), and run the step.
+        Returns ``None``: tokens are handed out by ``sample_tokens`` (the deferred-sampling contract of
+        the reference, model_runner.py:2588-2596)."""
+        so = scheduler_output
+        for field in ("scheduled_new_reqs", "scheduled_cached_reqs", "num_scheduled_tokens", "finished_req_ids"):
+            if not hasattr(so, field):
+                raise NotImplementedError(
+                    f"execute_model expects vllm.v1.core.sched.output.SchedulerOutput; {type(so).__name__} has no "
+                    f"'{field}'")
+        if so.scheduled_spec_decode_tokens:
+            raise NotImplementedError("speculative decoding is outside the B200 decode hot path")
+        for rid in list(so.finished_req_ids) + list(so.preempted_req_ids or ()):
+            self._requests.pop(rid, None)
+        for nr in so.scheduled_new_reqs:
+            if nr.prompt_token_ids is None:
+                raise NotImplementedError("prompt embeddings are outside the B200 decode hot path")
+            if len(nr.block_ids) != 1:
+                raise NotImplementedError("one KV-cache group is supported (mixed full/sliding groups: DESIGN.md)")
+            self._requests[nr.req_id] = _RequestState(list(nr.prompt_token_ids), list(nr.block_ids[0]),
+                                                      int(nr.num_computed_tokens))
+        cached = so.scheduled_cached_reqs
+        for i, rid in enumerate(cached.req_ids):
+            st = self._requests[rid]
+            st.num_computed = int(cached.num_computed_tokens[i])
+            new_blocks = cached.new_block_ids[i]
+            if rid in cached.resumed_req_ids:
+                st.block_ids = list(new_blocks[0]) if new_blocks is not None else []
+                if rid in cached.all_token_ids:
+                    st.tokens = list(cached.all_token_ids[rid])
+            elif new_blocks is not None:
+                st.block_ids.extend(new_blocks[0])
+            if cached.new_token_ids and cached.new_token_ids[i]:  # pipeline-parallel peers only; we sample here
+                st.tokens = st.tokens[:st.num_computed] + list(cached.new_token_ids[i])
+        decodes, prefills = [], []  # (req_id, state, n)
+        for rid, n in so.num_scheduled_tokens.items():
+            st = self._requests[rid]
+            if st.num_computed + n > len(st.tokens):
+                raise RuntimeError(f"request {rid}: scheduled {n} tokens from {st.num_computed} but only "
+                                   f"{len(st.tokens)} are known")
+            (decodes if n == 1 and st.num_computed > 0 else prefills).append((rid, st, int(n)))
         tokens: list[int] = []
-        decodes, prefills = [], []
-        for tok, blocks, seq_len in getattr(so, "decodes", []):
-            tokens.append(int(tok))
-            decodes.append((list(blocks), int(seq_len)))
-        for toks, blocks, start in getattr(so, "prefills", []):
-            tokens.extend(int(t) for t in toks)
-            prefills.append((list(blocks), len(toks), int(start)))
-        return tokens, decodes, prefills
+        dec_rows, pre_rows = [], []
+        for _, st, _n in decodes:
+            tokens.append(st.tokens[st.num_computed])
+            dec_rows.append((st.block_ids, st.num_computed))
+        for _, st, n in prefills:
+            tokens.extend(st.tokens[st.num_computed:st.num_computed + n])
+            pre_rows.append((st.block_ids, n, st.num_computed))
+        order = decodes + prefills
+        sampled = self.model_runner.execute(tokens, dec_rows, pre_rows) if tokens else []
+        self._pending = (order, sampled)
+
+    def sample_tokens(self, grammar_output: Any = None):
+        """Greedy tokens of the step as a ``ModelRunnerOutput`` (reference ``_build_output``,
+        model_runner.py:2450-2457).  A prefill chunk that does not reach the end of the known tokens
+        samples nothing (``[]``), exactly as vLLM expects for partial prefills."""
+        from vllm.v1.outputs import ModelRunnerOutput
+
+        if grammar_output is not None:
+            raise NotImplementedError("structured output (grammar bitmask) is outside the B200 decode hot path")
+        if self._pending is None:
+            return None
+        (order, sampled), self._pending = self._pending, None
+        req_ids, out = [], []
+        for (rid, st, n), tok in zip(order, sampled, strict=True):
+            req_ids.append(rid)
+            if st.num_computed + n >= len(st.tokens):  # reached the last known token: this step samples
+                st.tokens.append(int(tok))
+                out.append([int(tok)])
+            else:
+                out.append([])
+            st.num_computed += n
+        return ModelRunnerOutput(req_ids=req_ids, req_id_to_index={r: i for i, r in enumerate(req_ids)},
+                                 sampled_token_ids=out, logprobs=None, prompt_logprobs_dict={}, pooler_output=[])
+
+    def take_draft_token_ids(self):
+        return None  # no speculative drafts on this path (reference worker.py:287-289 forwards the runner's)
+
+    def get_supported_tasks(self) -> tuple[str, ...]:
+        return ("generate",)
+
+    def profile(self, is_start: bool = True, profile_prefix: str | None = None) -> None:
+        """``cudaProfilerStart/Stop`` + an NVTX range, the CUDA analogue of the reference's Metal capture
+        hook (worker.py:358-390): `ncu/nsys --capture-range=cudaProfilerApi` then record exactly the
+        steps between the two calls."""
+        if is_start:
+            torch.cuda.profiler.start()
+            torch.cuda.nvtx.range_push(profile_prefix or "b200_worker")
+            self._profiling = True
+        elif getattr(self, "_profiling", False):
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.synchronize(self.device)
+            torch.cuda.profiler.stop()
+            self._profiling = False
 
     # ---- gates the reference worker also has (worker.py:259-356) ---------------
     def reset_mm_cache(self) -> None:
