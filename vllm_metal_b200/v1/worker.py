@@ -222,7 +222,14 @@ class B200Worker(WorkerBase):
             tokens.extend(st.tokens[st.num_computed:st.num_computed + n])
             pre_rows.append((st.block_ids, n, st.num_computed))
         order = decodes + prefills
-        sampled = self.model_runner.execute(tokens, dec_rows, pre_rows) if tokens else []
+        r = self.model_runner
+        if not tokens:
+            sampled = []
+        elif not pre_rows and r.use_cuda_graph and len(dec_rows) <= r.max_batch:
+            # pure decode: the CUDA-graph path (pinned staging -> one H2D -> graph replay -> D2H token ids)
+            sampled = r.decode_step(tokens, [b for b, _ in dec_rows], [n for _, n in dec_rows])
+        else:
+            sampled = r.execute(tokens, dec_rows, pre_rows)
         self._pending = (order, sampled)
 
     def sample_tokens(self, grammar_output: Any = None):
