@@ -51,6 +51,10 @@ CONFIGS = {
           "gpt-oss-20b attention blocks (sinks, 128-token window on even layers), int4 g64 q/k/v/o, paged decode "
           "bs=32 ctx 4096 block_size 16 (configs[3]; MoE MLP out of scope)",
           "gpt-oss-20b attention blocks (random-init, affine int4 g64 incl. lm_head)", 1),
+    "c": ("qwen3-32b", 32, 8192, "mixed prefill+decode tok/s (Qwen3-32B int8, 2048-token chunk + 32 decode rows)",
+          "Qwen3-32B affine int8 g64 random-init, mixed varlen batch: one 2048-token prefill chunk continuing at "
+          "offset 6144 + 32 decode rows at ctx U[512, 8192], block_size 16, TP=2/4 (configs[2])",
+          "Qwen3-32B (random-init, affine int8 g64 incl. lm_head)", 1),
     "e": ("llama-3.1-70b", 16, 32768, "decode tok/s (Llama-3.1-70B int4, bs=16, ctx 32k)",
           "Llama-3.1-70B affine int4 g64 random-init, split-KV paged decode bs=16 ctx 32768 block_size 16 at TP=8 "
           "(configs[4])", "Llama-3.1-70B (random-init, affine int4 g64 incl. lm_head)", 8),
@@ -291,6 +295,162 @@ def run_reference(args) -> None:
 
 
 # ------------------------------------------------------------------------ GPU arm ---
+
+def run_mixed(args) -> None:
+    """Config c: a mixed prefill+decode step (eager launches through ``PagedModelRunner.execute``: host lists in,
+    token ids out every step, so ``value`` already IS the end-to-end number and ``e2e`` repeats the same run's
+    bytes).  M > 64 linears run the tensor-core GEMM (csrc/qgemm_tc.cu), the chunk's attention the tcgen05 tile
+    kernel, the decode rows the per-row kernels."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
+    from vllm_metal_b200.lm.decoder import PRESETS, Model
+    from vllm_metal_b200.metal import get_ops
+    from vllm_metal_b200.v1.model_runner import PagedModelRunner
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    ops = get_ops()
+    a = PRESETS[MODEL]
+    chunk, offset, ndec = 2048, int(os.environ.get("B200_CHUNK_OFFSET", "6144")), BATCH
+    T = chunk + ndec
+    nvl = None
+    if world > 1:
+        from vllm_metal_b200.distributed.nvlink_allreduce import NVLinkAllReduce
+
+        nvl = NVLinkAllReduce(device=dev, max_bytes=T * a.hidden * 2)
+
+    def allreduce(x):
+        nvl(x)
+
+    model = Model(a, torch.bfloat16, dev, seed=0, rank=rank, world=world, allreduce=allreduce, prefill_layout=True)
+    rng = np.random.default_rng(4)
+    dec_ctx = rng.integers(512, CTX, ndec).tolist()
+    lens = [n + 1 for n in dec_ctx] + [offset + chunk]
+    per = [(n + BLOCK - 1) // BLOCK for n in lens]
+    nb = 1 + sum(per)
+    cache = B200PagedKVCache(a.num_layers, a.n_kv_heads // world, a.head_dim, nb, BLOCK, torch.bfloat16, dev)
+    g = torch.Generator(device=dev).manual_seed(3 + rank)
+    for t in (cache._k_all, cache._v_all):
+        for i in range(a.num_layers):
+            t[i].normal_(0.0, 1.0, generator=g)
+    runner = PagedModelRunner(model, cache, max_batch=ndec + 1, max_model_len=max(lens) + BLOCK, use_cuda_graph=False)
+    perm = (rng.permutation(nb - 1) + 1).tolist()
+    tables, o = [], 0
+    for n in per:
+        tables.append(perm[o:o + n])
+        o += n
+    dec = [(tables[i], dec_ctx[i]) for i in range(ndec)]
+    pre = [(tables[ndec], chunk, offset)]
+    ids = rng.integers(0, a.vocab, T).tolist()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    for _ in range(args.warmup):
+        runner.execute(ids, dec, pre)
+    l0 = ops.launches
+    h2d0, d2h0 = runner.h2d_bytes, runner.d2h_bytes
+    barrier()
+    sampler.mark()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        runner.execute(ids, dec, pre)
+    e1.record()
+    barrier()
+    sampler.window()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    launches = ops.launches - l0
+    h2d, d2h = (runner.h2d_bytes - h2d0) // args.steps, (runner.d2h_bytes - d2h0) // args.steps
+
+    # dominant kernels, timed alone: the gate_up GEMM at M = T (tensor bound) and the chunk's attention
+    gu = model.layers[0].mlp.gate_up_proj
+    x = torch.randn((T, a.hidden), device=dev, generator=g).bfloat16()
+    for _ in range(2):
+        for layer in model.layers[:8]:
+            layer.mlp.gate_up_proj(x)
+    barrier()
+    e0.record()
+    for layer in model.layers[:16]:
+        layer.mlp.gate_up_proj(x)
+    e1.record()
+    barrier()
+    gemm_ms = e0.elapsed_time(e1) / 16
+    gemm_flops = 2.0 * T * gu.out_features * gu.in_features
+    hq, hkv, d = a.n_heads // world, a.n_kv_heads // world, a.head_dim
+    q = torch.randn((chunk, hq, d), device=dev, generator=g).bfloat16()
+    out = torch.empty_like(q)
+    bt = torch.tensor([tables[ndec]], dtype=torch.int32, device=dev)
+    cu = torch.tensor([0, chunk], dtype=torch.int32, device=dev)
+    sl = torch.tensor([offset + chunk], dtype=torch.int32, device=dev)
+    for _ in range(3):
+        ops.paged_attention_primitive(q, cache.key_caches[0], cache.value_caches[0], hkv, d ** -0.5, 0.0, bt, sl, cu, BLOCK,
+                                      offset + chunk, -1, out)
+    barrier()
+    e0.record()
+    for i in range(16):
+        ops.paged_attention_primitive(q, cache.key_caches[i], cache.value_caches[i], hkv, d ** -0.5, 0.0, bt, sl, cu,
+                                      BLOCK, offset + chunk, -1, out)
+    e1.record()
+    barrier()
+    attn_ms = e0.elapsed_time(e1) / 16
+    attn_flops = 4.0 * d * hq * chunk * (offset + (chunk + 1) / 2)
+    times = torch.tensor([ms, gemm_ms, attn_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms, gemm_ms, attn_ms = times.tolist()
+    if rank == 0:
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                pk = json.load(f)
+            peak_tf, peak_src = float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"])), "measured (sustained)"
+        except Exception:  # noqa: BLE001
+            peak_tf, peak_src = 1400.0, "fallback"
+        tok_s = T * args.steps / (ms * 1e-3)
+        cfg = base_config(world)
+        cfg.update({"global_batch": f"{ndec} decode rows + 1 chunk of {chunk}", "chunk_offset": offset,
+                    "tokens_per_step": T, "ctx": f"decode U[512,{CTX}] (seed 4), chunk ctx {offset + chunk}"})
+        _emit(json.dumps({
+            "metric": METRIC, "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": cfg,
+            "allreduce": "none" if world == 1 else f"nvlink kernel, {nvl.calls} calls, {nvl.nccl_calls} routed to NCCL",
+            "per_rank_resident": f"KV pool {cache.nbytes / 2**30:.1f} GiB + weights {model.weight_bytes() / 2**30:.2f} GiB "
+                                 f"(stream-K blobs + tensor-core GEMM layout)",
+            "e2e": {"value": tok_s, "unit": "tok/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "note": "the timed loop is the public runner API with host lists in and token ids out"},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": f"qgemm_tc_kernel gate_up {gu.out_features}x{gu.in_features} int{a.bits} "
+                                                      f"g{a.group_size}, M={T} (+ cast + silu_mul)",
+                         "achieved": gemm_flops / (gemm_ms * 1e-3) / 1e12, "peak": peak_tf, "peak_source": peak_src,
+                         "unit": "TFLOP/s", "frac": gemm_flops / (gemm_ms * 1e-3) / 1e12 / peak_tf, "traffic": None,
+                         "flops_per_launch": gemm_flops, "us_per_launch": gemm_ms * 1e3},
+            "roofline_attention": {"bound": "tensor", "kernel": "prefill_tc_kernel (2048-token chunk, causal)",
+                                   "achieved": attn_flops / (attn_ms * 1e-3) / 1e12, "peak": peak_tf, "unit": "TFLOP/s",
+                                   "frac": attn_flops / (attn_ms * 1e-3) / 1e12 / peak_tf, "flops_per_launch": attn_flops,
+                                   "us_per_launch": attn_ms * 1e3},
+            "cpu_baseline": None,
+        }))
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
+
 
 def run_b200(args) -> None:
     import numpy as np
@@ -536,6 +696,10 @@ def main() -> None:
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)
+    elif args.config == "c":
+        if args.steps == 128:
+            args.steps = 8  # a mixed step is ~2080 tokens; 8 steps already time >= 1 s of work per GPU
+        run_mixed(args)
     else:
         run_b200(args)
 

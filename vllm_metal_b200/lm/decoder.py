@@ -159,7 +159,8 @@ class Model(nn.Module):
     """``forward(input_ids [T], ctx|meta, kv_cache) -> logits`` for the packed batch."""
 
     def __init__(self, args: ModelArgs, dtype=torch.bfloat16, device="cuda", seed: int = 0,
-                 rank: int = 0, world: int = 1, allreduce=None, prepack: bool = True) -> None:
+                 rank: int = 0, world: int = 1, allreduce=None, prepack: bool = True,
+                 prefill_layout: bool = False) -> None:
         super().__init__()
         self.args = args
         self.rank, self.world = rank, world
@@ -176,6 +177,7 @@ class Model(nn.Module):
         else:
             self.lm_head = _rand_qlinear(args.hidden, args.vocab, args, gen, dtype, device)
         self._f16_acts = False
+        self._prefill_layout = prefill_layout
         if prepack:
             self.prepack()
 
@@ -184,10 +186,10 @@ class Model(nn.Module):
         ``weight`` is dropped (rebuilt on demand by ``mlx_weight()``) so the footprint is unchanged."""
         for m in self.modules():
             if isinstance(m, MLP):
-                m.gate_up_proj.prepack(keep_mlx_layout=False, swiglu=True)
+                m.gate_up_proj.prepack(keep_mlx_layout=False, swiglu=True, prefill_layout=self._prefill_layout)
         for m in self.modules():
             if isinstance(m, QuantizedLinear) and getattr(m, "weight_blob", None) is None:
-                m.prepack(keep_mlx_layout=False)
+                m.prepack(keep_mlx_layout=False, prefill_layout=self._prefill_layout and m is not self.lm_head)
         if self.lm_head is None:
             self.embed_tokens.prepack()
         # norms feed the stream-K linears fp16 directly (their operand type) when every consumer is one

@@ -90,14 +90,23 @@ class QuantizedLinear(nn.Module):
             m.bias.copy_(self.bias)
         return m
 
-    def prepack(self, keep_mlx_layout: bool = True, swiglu: bool = False) -> QuantizedLinear:
+    #: rows of x above which the tensor-core GEMM layout (``weight_tc``) is used when it is resident
+    PREFILL_M = 64
+
+    def prepack(self, keep_mlx_layout: bool = True, swiglu: bool = False, prefill_layout: bool = False) -> QuantizedLinear:
         """Load-time transform into the streaming blob of the persistent stream-K kernel
         (``b200_qstream_prepack``).  ``swiglu=True``: rows are ``[gate; up]`` and the call returns
         ``silu(gate) * up`` (``[.., out_features / 2]``), the fusion of the reference's compiled_mlp.py.
         ``weight`` keeps the MLX layout for loaders / LoRA introspection unless
-        ``keep_mlx_layout=False`` (then ``mlx_weight()`` rebuilds it bit-exactly from the blob)."""
+        ``keep_mlx_layout=False`` (then ``mlx_weight()`` rebuilds it bit-exactly from the blob).
+        ``prefill_layout=True`` also keeps the copy the M > 64 tensor-core GEMM (csrc/qgemm_tc.cu) reads
+        (``weight_tc``: nibble-permuted words for int4, the MLX words for int8): the stream-K kernel re-streams
+        and re-dequantises the weights once per 64 rows of x, which a 2048-token prefill chunk cannot afford."""
         if self.scales.dtype not in (torch.bfloat16, torch.float16):
             return self
+        if prefill_layout and self.scales.dtype == torch.bfloat16 and self.in_features % 64 == 0 and self.weight.shape[0]:
+            tc = get_ops().qlinear_prepack(self.weight, self.bits) if self.bits == 4 else self.weight.clone()
+            self.register_buffer("weight_tc", tc, persistent=False)
         try:
             blob = get_ops().qstream_prepack(self.weight, self.scales, self.biases, self.group_size, self.bits, swiglu)
         except ValueError:
@@ -125,6 +134,13 @@ class QuantizedLinear(nn.Module):
         by one extra launch, so producers that can emit fp16 do).  ``out_f16``: a bf16 module stores its
         (bf16-rounded) result as fp16 for a following QuantizedLinear."""
         blob = getattr(self, "weight_blob", None)
+        tc = getattr(self, "weight_tc", None)
+        if tc is not None and x.dtype in (torch.bfloat16, torch.float16) and x.numel() // x.shape[-1] > self.PREFILL_M:
+            y = get_ops().quantized_matmul(x, tc, self.scales, self.biases, transpose=True, group_size=self.group_size,
+                                           bits=self.bits, bias=self.bias, prepacked=True)
+            if self.swiglu:  # the blob's fused epilogue, unfused here
+                y = get_ops().silu_mul(y)
+            return y
         if blob is not None and x.dtype in (torch.bfloat16, torch.float16):
             dt = self.scales.dtype
             return get_ops().qstream_linear(x, blob, self.out_features, self.in_features, self.group_size, self.bits,

@@ -106,7 +106,15 @@ class PagedModelRunner:
                 self.device, non_blocking=True)
             logits = self.model(ids, ctx, self.kv_cache, logits_rows=last_rows)
             toks = get_ops().argmax(logits)
-            return toks.cpu().tolist()
+            out = toks.cpu().tolist()
+            # bytes that crossed PCIe for this step: ids + logit rows + the kernel metadata sdpa uploads once
+            # (slot_mapping int64 [T], seq_lens / cu_seqlens int32, block tables int32), token ids back
+            nseq = len(ctx.cu_seqlens) - 1
+            maxb = max((len(t) for t in ctx.block_tables), default=0)
+            self.h2d_bytes += ids.numel() * 4 + last_rows.numel() * 8 + len(ctx.slot_mapping) * 8 + \
+                (2 * nseq + 1) * 4 + nseq * maxb * 4 + len(ctx.slot_mapping) * 4
+            self.d2h_bytes += len(out) * 4
+            return out
         finally:
             clear_context()
 
