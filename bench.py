@@ -565,16 +565,26 @@ def run_b200(args) -> None:
                                           meta.block_tables, meta.seq_lens, meta.cu_seqlens_q, BLOCK,
                                           meta.max_seq_len, -1, out)
 
-    for _ in range(3):
-        attn_all_layers()
-    barrier()
-    e0.record()
+    def timed_graph(fn, reps):
+        """fn() captured once in a CUDA graph and replayed: the host's launch cost (~20 us per call through
+        ctypes) must not pace kernels that take less than that (it did at TP >= 2 in round 1)."""
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            fn()
+        gr.replay()
+        barrier()
+        e0.record()
+        for _ in range(reps):
+            gr.replay()
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1) / reps
+
     reps = max(3, min(args.steps, 10))
-    for _ in range(reps):
-        attn_all_layers()
-    e1.record()
-    barrier()
-    attn_ms = e0.elapsed_time(e1) / (reps * a.num_layers)
+    attn_ms = timed_graph(attn_all_layers, reps) / a.num_layers
     alg_bytes = BATCH * (2 * cur_len * hkv * d * 2 + 2 * hq * d * 2 + ((cur_len + BLOCK - 1) // BLOCK) * 4)
     peak, peak_src = _peaks()
     achieved = alg_bytes / (attn_ms * 1e-3) / 1e9
@@ -585,17 +595,11 @@ def run_b200(args) -> None:
     mlp = model.layers[0].mlp
     if mlp is not None:
         x = torch.randn((BATCH, a.hidden), device=dev, generator=g).half()
-        for _ in range(3):
+        def gate_up_all_layers():
             for layer in model.layers:
                 layer.mlp.gate_up_proj(x, out_f16=True)
-        barrier()
-        e0.record()
-        for _ in range(reps):
-            for layer in model.layers:
-                layer.mlp.gate_up_proj(x, out_f16=True)
-        e1.record()
-        barrier()
-        gemv_ms = e0.elapsed_time(e1) / (reps * a.num_layers)
+
+        gemv_ms = timed_graph(gate_up_all_layers, reps) / a.num_layers
         n_gu, k_gu = mlp.gate_up_proj.out_features, mlp.gate_up_proj.in_features
         n_out = n_gu // 2 if mlp.gate_up_proj.swiglu else n_gu
         gemv_bytes = n_gu * k_gu * (a.bits / 8 + 4 / a.group_size) + BATCH * (k_gu + n_out) * 2

@@ -38,6 +38,8 @@ MODELS = {  # name: (bits, {shape: (N, K, swiglu)})
                          "down": (4096, 1792, 0), "lm_head_vp": (16032, 4096, 0)}),
     "llama-8b-tp2": (4, {"qkv": (3072, 4096, 0), "o_proj": (4096, 2048, 0), "gate_up": (14336, 4096, 1),
                          "down": (4096, 7168, 0)}),
+    "llama-8b-tp4": (4, {"qkv": (1536, 4096, 0), "o_proj": (4096, 1024, 0), "gate_up": (7168, 4096, 1),
+                         "down": (4096, 3584, 0)}),
     "qwen3-32b": (8, {"qkv": (10240, 5120, 0), "o_proj": (5120, 8192, 0), "gate_up": (51200, 5120, 1),
                       "down": (5120, 25600, 0)}),
     "llama-70b-tp8": (4, {"qkv": (1280, 8192, 0), "o_proj": (8192, 1024, 0), "gate_up": (7168, 8192, 1),
@@ -118,7 +120,7 @@ def main():
         ops.set_qstream_grid(0)
         if args.legacy:
             yl = torch.empty((m, n), device="cuda", dtype=torch.bfloat16)
-            us = time_us(lambda i: ops.quantized_matmul(x, *mlx[i], group_size=g, bits=bits, out=yl), copies)
+            us = time_us(lambda i: ops.quantized_matmul(x, *mlx[i], group_size=g, bits=bits, out=yl), copies)  # x fp16 with --x16: no cast launch
             row["legacy_us"] = us
             line += f" round-1 kernel: {us:7.2f} us ({(n * k * (bits / 8 + 4 / g) + m * (k + n) * 2) / us / 1e3 / PEAK:4.2f})"
         if args.trace:

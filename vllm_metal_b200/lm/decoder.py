@@ -141,7 +141,8 @@ class MLP(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.gate_up_proj.swiglu:  # SiLU * up fused into the gate_up epilogue (streaming layout)
-            f16 = getattr(self.down_proj, "weight_blob", None) is not None
+            f16 = getattr(self.down_proj, "weight_blob", None) is not None or \
+                getattr(self.down_proj, "weight_tc", None) is not None
             return self.down_proj(self.gate_up_proj(x, out_f16=f16))
         return self.down_proj(get_ops().silu_mul(self.gate_up_proj(x)))
 
@@ -188,13 +189,14 @@ class Model(nn.Module):
             if isinstance(m, MLP):
                 m.gate_up_proj.prepack(keep_mlx_layout=False, swiglu=True, prefill_layout=self._prefill_layout)
         for m in self.modules():
-            if isinstance(m, QuantizedLinear) and getattr(m, "weight_blob", None) is None:
+            if isinstance(m, QuantizedLinear) and getattr(m, "weight_blob", None) is None \
+                    and getattr(m, "weight_tc", None) is None:
                 m.prepack(keep_mlx_layout=False, prefill_layout=self._prefill_layout and m is not self.lm_head)
         if self.lm_head is None:
             self.embed_tokens.prepack()
         # norms feed the stream-K linears fp16 directly (their operand type) when every consumer is one
-        self._f16_acts = all(getattr(m, "weight_blob", None) is not None for m in self.modules()
-                             if isinstance(m, QuantizedLinear)) and (
+        self._f16_acts = all(getattr(m, "weight_blob", None) is not None or getattr(m, "weight_tc", None) is not None
+                             for m in self.modules() if isinstance(m, QuantizedLinear)) and (
             self.lm_head is not None or getattr(self.embed_tokens, "weight_blob", None) is not None)
 
     def _reduce(self, x: torch.Tensor) -> torch.Tensor:

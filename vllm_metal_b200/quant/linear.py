@@ -90,38 +90,58 @@ class QuantizedLinear(nn.Module):
             m.bias.copy_(self.bias)
         return m
 
-    #: rows of x above which the tensor-core GEMM layout (``weight_tc``) is used when it is resident
+    #: rows of x above which the tensor-core GEMM layout (``weight_tc``) is used when both layouts are resident
     PREFILL_M = 64
+    #: packed-weight bytes up to which a (non-SwiGLU) linear is served by the cluster split-K kernel alone.
+    #: Measured at M = 64 (profiles/r02_qstream_vs_cluster_tp_shapes.txt): below ~16 MB a launch is all fixed
+    #: cost, and the cluster kernel's DSMEM reduction (5-11 us) beats the stream-K kernel's exchange through
+    #: global memory (8-13 us); from ~18 MB up the persistent stream wins (and it fuses SwiGLU).
+    SMALL_BYTES = 16 << 20
 
     def prepack(self, keep_mlx_layout: bool = True, swiglu: bool = False, prefill_layout: bool = False) -> QuantizedLinear:
-        """Load-time transform into the streaming blob of the persistent stream-K kernel
-        (``b200_qstream_prepack``).  ``swiglu=True``: rows are ``[gate; up]`` and the call returns
-        ``silu(gate) * up`` (``[.., out_features / 2]``), the fusion of the reference's compiled_mlp.py.
-        ``weight`` keeps the MLX layout for loaders / LoRA introspection unless
-        ``keep_mlx_layout=False`` (then ``mlx_weight()`` rebuilds it bit-exactly from the blob).
-        ``prefill_layout=True`` also keeps the copy the M > 64 tensor-core GEMM (csrc/qgemm_tc.cu) reads
-        (``weight_tc``: nibble-permuted words for int4, the MLX words for int8): the stream-K kernel re-streams
-        and re-dequantises the weights once per 64 rows of x, which a 2048-token prefill chunk cannot afford."""
-        if self.scales.dtype not in (torch.bfloat16, torch.float16):
+        """Load-time transform into the kernels' layouts; picks per shape:
+
+        * ``weight_blob`` -- streaming blob of the persistent stream-K kernel (``b200_qstream_prepack``).
+          ``swiglu=True``: rows are ``[gate; up]`` and the call returns ``silu(gate) * up``
+          (``[.., out_features / 2]``), the fusion of the reference's compiled_mlp.py.
+        * ``weight_tc`` -- the words the tcgen05 cluster split-K / M > 64 GEMM kernel (csrc/qgemm_tc.cu) reads
+          (nibble-permuted for int4, the MLX words for int8).  Kept INSTEAD of the blob for small matrices
+          (``SMALL_BYTES``), and BESIDE it with ``prefill_layout=True``: the stream-K kernel re-streams and
+          re-dequantises the weights once per 64 rows of x, which a 2048-token prefill chunk cannot afford.
+
+        ``weight`` keeps the MLX layout for loaders / LoRA introspection unless ``keep_mlx_layout=False``
+        (then ``mlx_weight()`` rebuilds it bit-exactly from whichever layout is resident)."""
+        if self.scales.dtype not in (torch.bfloat16, torch.float16) or not self.weight.shape[0]:
             return self
-        if prefill_layout and self.scales.dtype == torch.bfloat16 and self.in_features % 64 == 0 and self.weight.shape[0]:
-            tc = get_ops().qlinear_prepack(self.weight, self.bits) if self.bits == 4 else self.weight.clone()
+        ops = get_ops()
+        tc_ok = self.scales.dtype == torch.bfloat16 and self.in_features % 64 == 0
+        small = tc_ok and not swiglu and self.weight.numel() * 4 <= self.SMALL_BYTES
+        blob = None
+        if not small:
+            try:
+                blob = ops.qstream_prepack(self.weight, self.scales, self.biases, self.group_size, self.bits, swiglu)
+            except ValueError:
+                blob = None  # a scale/bias outside fp16: stay on the MLX-layout kernels
+        if tc_ok and (small or prefill_layout or blob is None):
+            tc = ops.qlinear_prepack(self.weight, self.bits) if self.bits == 4 else self.weight.clone()
             self.register_buffer("weight_tc", tc, persistent=False)
-        try:
-            blob = get_ops().qstream_prepack(self.weight, self.scales, self.biases, self.group_size, self.bits, swiglu)
-        except ValueError:
-            return self  # a scale/bias outside fp16: stay on the MLX-layout kernels
-        self.register_buffer("weight_blob", blob, persistent=False)
-        self.swiglu = bool(swiglu)
-        if not keep_mlx_layout:
-            self.weight = torch.empty((0, self.weight.shape[1]), dtype=torch.int32, device=blob.device)
+        if blob is not None:
+            self.register_buffer("weight_blob", blob, persistent=False)
+            self.swiglu = bool(swiglu)
+        if not keep_mlx_layout and (blob is not None or getattr(self, "weight_tc", None) is not None):
+            self.weight = torch.empty((0, self.weight.shape[1]), dtype=torch.int32, device=self.scales.device)
         return self
 
     def mlx_weight(self) -> torch.Tensor:
-        if self.weight.shape[0] or getattr(self, "weight_blob", None) is None:
+        if self.weight.shape[0]:
             return self.weight
-        return get_ops().qstream_unpack(self.weight_blob, self.out_features, self.in_features, self.group_size,
-                                        self.bits, self.swiglu)
+        if getattr(self, "weight_blob", None) is not None:
+            return get_ops().qstream_unpack(self.weight_blob, self.out_features, self.in_features, self.group_size,
+                                            self.bits, self.swiglu)
+        tc = getattr(self, "weight_tc", None)
+        if tc is not None:
+            return get_ops().qlinear_prepack(tc, self.bits, inverse=True) if self.bits == 4 else tc
+        return self.weight
 
     def _save_to_state_dict(self, destination, prefix, keep_vars):
         # checkpoints always carry the MLX layout, whatever the resident layout is
@@ -135,7 +155,8 @@ class QuantizedLinear(nn.Module):
         (bf16-rounded) result as fp16 for a following QuantizedLinear."""
         blob = getattr(self, "weight_blob", None)
         tc = getattr(self, "weight_tc", None)
-        if tc is not None and x.dtype in (torch.bfloat16, torch.float16) and x.numel() // x.shape[-1] > self.PREFILL_M:
+        if tc is not None and x.dtype in (torch.bfloat16, torch.float16) and (
+                blob is None or x.numel() // x.shape[-1] > self.PREFILL_M):
             y = get_ops().quantized_matmul(x, tc, self.scales, self.biases, transpose=True, group_size=self.group_size,
                                            bits=self.bits, bias=self.bias, prepacked=True)
             if self.swiglu:  # the blob's fused epilogue, unfused here
