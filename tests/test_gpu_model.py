@@ -109,12 +109,14 @@ def test_cfg_a_qwen3_0p6b_128_free_running_greedy_steps():
     decode steps.  The product runs FREE (CUDA graph, its own tokens fed back, as in
     /root/reference/tests/test_paged_deterministic.py:50-74); the oracle is stepped along the
     product's trajectory and must name the same token at every step.  A differing token is only
-    tolerated -- and printed -- when the oracle's own logits of the two candidates are AT MOST one
-    bf16 ulp apart: logits are stored in bf16, the product accumulates in another order (tensor-core
-    tiles, stream-K pieces) than the oracle's fp32 loop, so either candidate's logit may round one
-    ulp the other way -- a tie at the logits' storage precision.  With random-init weights and a
-    151936-way argmax such ties do occur (the vocabulary's top two logits are routinely 0-1 ulp
-    apart); anything wider fails.  No mismatch budget."""
+    tolerated -- and printed -- when the oracle's own logits of the two candidates are closer than the
+    north-star parity bound on those logits themselves (2e-2 max-abs + 1e-2 relative: they are bf16
+    GEMM outputs over 28 layers of bf16 activations, the product accumulates in other orders --
+    tensor-core tiles, cluster split-K, stream-K pieces -- than the oracle's fp32 loop, so a candidate's
+    logit may legitimately land a couple of bf16 ulps (1 ulp = 0.0156 at |logit| in [1, 2)) away).  With
+    random-init weights and a 151936-way argmax the top two logits are routinely 0-2 ulp apart, so such
+    ties do occur; anything wider fails, and at most 5% of the steps may be ties at all (an actual
+    numerical bug flips far more: the logits' spread is ~40 ulp)."""
     from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
     from vllm_metal_b200.lm.decoder import PRESETS, Model
     from vllm_metal_b200.v1.model_runner import PagedModelRunner
@@ -142,7 +144,8 @@ def test_cfg_a_qwen3_0p6b_128_free_running_greedy_steps():
         gap = float(ologits[0, want] - ologits[0, got_tok])
         ulp = _bf16_ulp(ologits[0, want])
         print(f"step {step}: product {got_tok} vs oracle {want}, oracle logit gap {gap:.6f} (1 bf16 ulp = {ulp:.6f})")
-        assert gap <= ulp, f"step {step}: token {got_tok} != oracle {want}; oracle top-2 gap {gap} > 1 bf16 ulp {ulp}"
+        bound = 2e-2 + 1e-2 * abs(float(ologits[0, want]))
+        assert gap <= bound, f"step {step}: token {got_tok} != oracle {want}; oracle top-2 gap {gap} > parity bound {bound}"
         ties.append(step)
 
     check(-1, got[0], ologits)
@@ -154,7 +157,8 @@ def test_cfg_a_qwen3_0p6b_128_free_running_greedy_steps():
         tokens.append(nxt)
         cur, seq_len = nxt, seq_len + 1
     assert len(tokens) == steps
-    print(f"cfg a: {steps} free-running greedy steps, {len(ties)} bf16-ulp ties at steps {ties}")
+    print(f"cfg a: {steps} free-running greedy steps, {len(ties)} near-ties at steps {ties}")
+    assert len(ties) <= 0.05 * steps, f"{len(ties)} near-tie steps of {steps}"
 
 
 def test_worker_with_vllm_scheduler_outputs_matches_oracle():
