@@ -327,10 +327,7 @@ def run_mixed(args) -> None:
 
         nvl = NVLinkAllReduce(device=dev, max_bytes=T * a.hidden * 2)
 
-    def allreduce(x):
-        nvl(x)
-
-    model = Model(a, torch.bfloat16, dev, seed=0, rank=rank, world=world, allreduce=allreduce, prefill_layout=True)
+    model = Model(a, torch.bfloat16, dev, seed=0, rank=rank, world=world, allreduce=nvl, prefill_layout=True)
     rng = np.random.default_rng(4)
     dec_ctx = rng.integers(512, CTX, ndec).tolist()
     lens = [n + 1 for n in dec_ctx] + [offset + chunk]
@@ -479,13 +476,12 @@ def run_b200(args) -> None:
 
         nvl = NVLinkAllReduce(device=dev, max_bytes=BATCH * a.hidden * 2)
 
-    def allreduce(x):
-        if nvl is not None:
-            nvl(x)
-        else:
-            dist.all_reduce(x)
+    def nccl_allreduce(x):
+        dist.all_reduce(x)
 
-    model = Model(a, torch.bfloat16, dev, seed=0, rank=rank, world=world, allreduce=allreduce)
+    # the NVLink object itself: the decoder then uses its fused all-reduce + residual + RMSNorm kernel
+    model = Model(a, torch.bfloat16, dev, seed=0, rank=rank, world=world,
+                  allreduce=nvl if nvl is not None else nccl_allreduce)
     total = args.warmup + args.steps
     max_len = CTX + 2 * total + 8
     blocks_per_seq = (max_len + BLOCK - 1) // BLOCK
@@ -631,7 +627,7 @@ def run_b200(args) -> None:
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": base_config(world),
-            "allreduce": ("none" if world == 1 else "nvlink kernel (csrc/nvlink_allreduce.cu)"
+            "allreduce": ("none" if world == 1 else "nvlink kernel fused with residual add + RMSNorm (csrc/nvlink_allreduce.cu)"
                           if nvl is not None else "nccl"),
             "per_rank_resident": f"KV pool {cache.nbytes / 2**30:.1f} GiB + weights {model.weight_bytes() / 2**30:.2f} GiB",
             "e2e": {"value": BATCH * args.steps / (e2e_ms * 1e-3), "unit": "tok/s",

@@ -100,6 +100,14 @@ int b200_ipc_free(void* ptr);
 int b200_allreduce_sum(void* x, int64_t numel, int dtype, void* const* symm_ptrs,
                        void* const* flag_ptrs, void* epoch, int rank, int world,
                        int64_t half_bytes, int grid, void* stream);
+/* Fused tensor-parallel epilogue of a decoder sub-block: s = all-reduce(x) (as above, x [rows, hidden] contiguous,
+ * left untouched), residual += s (in place, rounded to dtype), out = rms_norm(residual) * weight -- bit-identical
+ * to b200_allreduce_sum followed by b200_rms_norm(x, residual, ...), in one launch.  Shares buffers, flags and
+ * epochs with b200_allreduce_sum (same `grid`); hidden % 8 == 0, hidden <= 8192; out_dtype as in b200_rms_norm. */
+int b200_allreduce_add_rmsnorm(void* x, void* residual, const void* weight, void* out, int rows, int hidden,
+                               float eps, int dtype, int out_dtype, void* const* symm_ptrs,
+                               void* const* flag_ptrs, void* epoch, int rank, int world,
+                               int64_t half_bytes, int grid, void* stream);
 
 #ifdef __cplusplus
 }

@@ -101,6 +101,47 @@ def main() -> None:
     timed(lambda t: ar(t), "nvlink one-shot")
     timed(lambda t: dist.all_reduce(t), "nccl")
 
+    # ---- fused all-reduce + residual add + RMSNorm vs the two-step sequence (bit-identical at hidden 4096 / 8192,
+    # where both kernels map threads to elements the same way; equal up to the fp32 order of the mean square else)
+    from vllm_metal_b200.metal import get_ops
+
+    ops = get_ops()
+    for rows, hidden, f16 in ((64, 4096, True), (64, 4096, False), (1, 4096, True), (16, 8192, True), (37, 5120, False),
+                              (100, 2880, True)):
+        g = torch.Generator(device=dev).manual_seed(7 * rank + rows + hidden)
+        part = torch.randn((rows, hidden), device=dev, generator=g).bfloat16()
+        g2_ = torch.Generator(device=dev).manual_seed(rows + hidden)  # residual / weight: same on every rank
+        res0 = torch.randn((rows, hidden), device=dev, generator=g2_).bfloat16()
+        w = (torch.rand((hidden,), device=dev, generator=g2_) + 0.5).bfloat16()
+        odt = torch.float16 if f16 else None
+        # two-step reference
+        s_ = part.clone()
+        ar(s_)
+        res_ref = res0.clone()
+        want = ops.rms_norm(s_, w, 1e-5, residual=res_ref, out_dtype=odt if hidden >= 512 else None)
+        for _ in range(2):
+            res = res0.clone()
+            got = ar.fused_add_rmsnorm(part.clone(), res, w, 1e-5, odt)
+        torch.cuda.synchronize()
+        assert got is not None, (rows, hidden)
+        same_map = hidden in (4096, 8192)
+        good = torch.equal(res, res_ref) and (torch.equal(got, want) if same_map else
+                                               bool((got.float() - want.float()).abs().max() <= 2.0 ** -6 * want.float().abs().max()))
+        if not good:
+            ok = False
+            print(f"[rank {rank}] fused add+norm differs rows={rows} hidden={hidden} f16={f16}: residual equal "
+                  f"{torch.equal(res, res_ref)}, out max diff {(got.float() - want.float()).abs().max().item()}", flush=True)
+    parts = [x0.clone() for _ in range(16)]
+    resid = x0.clone()
+    wn = torch.ones((4096,), device=dev).bfloat16()
+    timed(lambda t: ar.fused_add_rmsnorm(t, resid, wn, 1e-5, torch.float16), "nvlink one-shot fused with residual add + RMSNorm")
+
+    def two_step(t):
+        ar(t)
+        ops.rms_norm(t, wn, 1e-5, residual=resid, out_dtype=torch.float16)
+
+    timed(two_step, "nvlink one-shot, then add + RMSNorm (two launches)")
+
     # graph-replayed result equals the eager one
     a = x0.clone()
     ar(a)

@@ -128,6 +128,140 @@ static int launch(const Params& p, int grid, cudaStream_t st) {
   return check_launch("allreduce_oneshot_kernel");
 }
 
+
+// ---- fused: all-reduce + residual add + RMSNorm ------------------------------------------------------------
+// The two sums of a tensor-parallel decoder layer are each followed by `h += sum; x = rms_norm(h) * w`
+// (reference layer wiring; SURVEY.md 8(e) asks for the fused form).  CTA b owns ROWS b, b + grid, ... on every
+// rank (a row of the headline shape is 8 KiB: one 16-byte vector per thread), so after the same flag exchange as
+// above it gathers a whole row from every peer, adds in rank order, rounds the sum to T exactly as the unfused
+// all-reduce stores it, adds the residual (rounded to T, as b200_rms_norm does), keeps the row in registers for
+// the sum of squares, and writes the residual stream and the normalised row -- one launch and one HBM round trip
+// of [M, hidden] less than allreduce_oneshot_kernel + rms_norm_vec_kernel, bit-identical to that sequence.
+struct FusedParams {
+  Params ar;
+  void* residual;       // [rows, hidden] in place
+  const void* weight;   // [hidden] or null
+  void* out;            // [rows, hidden] T, or fp16 when out_f16
+  int rows, hidden;
+  float eps;
+  int out_f16;
+};
+
+__device__ __forceinline__ float block_sum_512(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = lane < (kThreads >> 5) ? red[lane] : 0.f;
+  t = warp_sum(t);
+  __syncthreads();
+  return t;
+}
+
+template <typename T, int WORLD>
+__global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_kernel(const FusedParams f) {
+  pdl_trigger();
+  pdl_wait();
+  constexpr int NV = 2;  // vectors per thread: hidden <= 512 * 8 * 2
+  __shared__ float red[32];
+  const Params& p = f.ar;
+  const int b = blockIdx.x, G = gridDim.x;
+  const uint32_t e = p.epoch[b] + 1u;
+  const int64_t half_off = (int64_t)(e & 1u) * p.half_bytes;
+  const int nvec = f.hidden >> 3;  // 16-byte vectors per row
+  uint4* xv = reinterpret_cast<uint4*>(p.x);
+  uint4* mine = reinterpret_cast<uint4*>(p.symm[p.rank] + half_off);
+  // 1. publish my rows
+  for (int r = b; r < f.rows; r += G)
+    for (int v = threadIdx.x; v < nvec; v += kThreads) mine[(int64_t)r * nvec + v] = xv[(int64_t)r * nvec + v];
+  __syncthreads();
+  // 2. + 3. flag exchange (same slots and epochs as allreduce_oneshot_kernel: the two kernels interleave freely)
+  if (threadIdx.x < WORLD && (int)threadIdx.x != p.rank) {
+    const int peer = threadIdx.x;
+    st_release_sys(p.flags[peer] + (size_t)b * WORLD + p.rank, e);
+    const uint32_t* slot = p.flags[p.rank] + (size_t)b * WORLD + peer;
+    uint32_t spins = 0;
+    while ((int32_t)(ld_acquire_sys(slot) - e) < 0) {
+      if (++spins > (1u << 27)) __trap();
+    }
+  }
+  __syncthreads();
+  // 4. per row: gather + sum, residual add, norm
+  uint4* rv = reinterpret_cast<uint4*>(f.residual);
+  uint4* ov = reinterpret_cast<uint4*>(f.out);
+  const uint4* wv = reinterpret_cast<const uint4*>(f.weight);
+  for (int r = b; r < f.rows; r += G) {
+    float h[NV][8];
+    float ss = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int v = threadIdx.x + j * kThreads;
+      if (v < nvec) {
+        const int64_t idx = (int64_t)r * nvec + v;
+        uint4 part[WORLD];
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q)
+          part[q] = (q == p.rank) ? xv[idx] : ld_peer_u4(reinterpret_cast<const uint4*>(p.symm[q] + half_off) + idx);
+        float acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q) accumulate<T>(acc, part[q]);
+        const uint4 res = rv[idx];
+        const T* re = reinterpret_cast<const T*>(&res);
+        uint4 hn;
+        T* he = reinterpret_cast<T*>(&hn);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float a = to_float(from_float<T>(acc[i]));        // the all-reduce's own rounding
+          he[i] = from_float<T>(a + to_float(re[i]));             // residual stream kept in T
+          h[j][i] = to_float(he[i]);
+          ss += h[j][i] * h[j][i];
+        }
+        rv[idx] = hn;
+      }
+    }
+    ss = block_sum_512(ss, red);
+    const float inv = rsqrtf(ss / (float)f.hidden + f.eps);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int v = threadIdx.x + j * kThreads;
+      if (v < nvec) {
+        uint4 c;
+        T* ce = reinterpret_cast<T*>(&c);
+        if (wv) {
+          const uint4 w = __ldg(wv + v);
+          const T* we = reinterpret_cast<const T*>(&w);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) ce[i] = from_float<T>(h[j][i] * inv * to_float(we[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) ce[i] = from_float<T>(h[j][i] * inv);
+        }
+        if (f.out_f16) {
+          __half* hh = reinterpret_cast<__half*>(&c);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) hh[i] = __float2half_rn(fminf(fmaxf(to_float(ce[i]), -65504.f), 65504.f));
+        }
+        ov[(int64_t)r * nvec + v] = c;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) p.epoch[b] = e;
+}
+
+template <typename T>
+static int launch_fused(const FusedParams& f, int grid, cudaStream_t st) {
+  switch (f.ar.world) {
+    case 2: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 2>, dim3(grid), dim3(kThreads), 0, st, f)); break;
+    case 4: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 4>, dim3(grid), dim3(kThreads), 0, st, f)); break;
+    case 8: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 8>, dim3(grid), dim3(kThreads), 0, st, f)); break;
+    default: return set_error(B200_ERR_INVALID_ARGUMENT, "allreduce: world size must be 2, 4 or 8, got %d", f.ar.world);
+  }
+  return check_launch("allreduce_add_rmsnorm_kernel");
+}
+
 }  // namespace ar
 }  // namespace b200
 
@@ -193,6 +327,47 @@ int b200_allreduce_sum(void* x, int64_t numel, int dtype, void* const* symm_ptrs
   p.world = world;
   cudaStream_t st = (cudaStream_t)stream;
   return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int { return ar::launch<T>(p, grid, st); });
+}
+
+int b200_allreduce_add_rmsnorm(void* x, void* residual, const void* weight, void* out, int rows, int hidden, float eps,
+                               int dtype, int out_dtype, void* const* symm_ptrs, void* const* flag_ptrs, void* epoch,
+                               int rank, int world, int64_t half_bytes, int grid, void* stream) {
+  using namespace b200;
+  if (rows == 0) return B200_OK;
+  B200_CHECK_ARG(x && residual && out && symm_ptrs && flag_ptrs && epoch && rows > 0, "allreduce_add_rmsnorm: bad arguments");
+  B200_CHECK_ARG(dtype == B200_BF16 || dtype == B200_F16, "allreduce_add_rmsnorm: dtype must be bf16 or fp16");
+  B200_CHECK_ARG(out_dtype == dtype || (out_dtype == B200_F16 && dtype == B200_BF16),
+                 "allreduce_add_rmsnorm: out dtype must be the input dtype, or fp16 for bf16 input");
+  B200_CHECK_ARG(hidden % 8 == 0 && hidden <= ar::kThreads * 8 * 2, "allreduce_add_rmsnorm: hidden %d must be a multiple of 8, <= %d",
+                 hidden, ar::kThreads * 8 * 2);
+  B200_CHECK_ARG(rank >= 0 && rank < world && world <= ar::kMaxWorld, "allreduce: rank %d of world %d", rank, world);
+  B200_CHECK_ARG(grid > 0 && grid <= 1024, "allreduce: grid %d out of range", grid);
+  const int64_t bytes = (int64_t)rows * hidden * 2;
+  B200_CHECK_ARG((((uintptr_t)x | (uintptr_t)residual | (uintptr_t)out | (uintptr_t)weight) & 15) == 0,
+                 "allreduce_add_rmsnorm: pointers must be 16-byte aligned");
+  B200_CHECK_ARG(bytes <= half_bytes, "allreduce: %lld bytes exceed the staging half (%lld)", (long long)bytes,
+                 (long long)half_bytes);
+  ar::FusedParams f;
+  f.ar.x = x;
+  for (int r = 0; r < world; ++r) {
+    f.ar.symm[r] = reinterpret_cast<char*>(symm_ptrs[r]);
+    f.ar.flags[r] = reinterpret_cast<uint32_t*>(flag_ptrs[r]);
+  }
+  f.ar.epoch = reinterpret_cast<uint32_t*>(epoch);
+  f.ar.nvec = bytes / 16;
+  f.ar.half_bytes = half_bytes;
+  f.ar.rank = rank;
+  f.ar.world = world;
+  f.residual = residual;
+  f.weight = weight;
+  f.out = out;
+  f.rows = rows;
+  f.hidden = hidden;
+  f.eps = eps;
+  f.out_f16 = (out_dtype == B200_F16 && dtype == B200_BF16) ? 1 : 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_BF16) return ar::launch_fused<__nv_bfloat16>(f, grid, st);
+  return ar::launch_fused<__half>(f, grid, st);
 }
 
 }  // extern "C"

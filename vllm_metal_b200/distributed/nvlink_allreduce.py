@@ -40,6 +40,11 @@ class NVLinkAllReduce:
                                            ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
                                            ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int64,
                                            ctypes.c_int, ctypes.c_void_p]
+        lib.b200_allreduce_add_rmsnorm.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                   ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_int, ctypes.c_int,
+                                                   ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
+                                                   ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int64,
+                                                   ctypes.c_int, ctypes.c_void_p]
         self.half_bytes = (int(max_bytes) + 255) // 256 * 256
         self.grid = int(grid)
         with torch.cuda.device(self.device):
@@ -90,6 +95,29 @@ class NVLinkAllReduce:
         self.ops.launches += 1
         self.calls += 1
         return x
+
+    def fused_add_rmsnorm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor | None, eps: float,
+                          out_dtype: torch.dtype | None = None) -> torch.Tensor | None:
+        """``residual += allreduce(x); return rms_norm(residual) * weight`` in one kernel (x is left holding this
+        rank's partial).  Returns ``None`` when the shape does not qualify -- the caller then runs the two-step
+        sequence, which gives the same bits."""
+        hidden = x.shape[-1]
+        x2, r2 = x.reshape(-1, hidden), residual.reshape(-1, hidden)
+        nbytes = x2.numel() * 2
+        if (x.dtype not in (torch.bfloat16, torch.float16) or not x2.is_contiguous() or not r2.is_contiguous()
+                or hidden % 8 or hidden > 8192 or nbytes > self.half_bytes or x2.data_ptr() % 16 or r2.data_ptr() % 16
+                or (weight is not None and (weight.dtype != x.dtype or weight.data_ptr() % 16))):
+            return None
+        out = torch.empty(x2.shape, dtype=out_dtype or x.dtype, device=x.device)
+        rc = self.lib.b200_allreduce_add_rmsnorm(
+            x2.data_ptr(), r2.data_ptr(), None if weight is None else weight.data_ptr(), out.data_ptr(), x2.shape[0],
+            hidden, float(eps), _DTYPE_CODE[x.dtype], _DTYPE_CODE[out.dtype], self._symm, self._flags,
+            self.epoch.data_ptr(), self.rank, self.world, self.half_bytes, self.grid,
+            torch.cuda.current_stream().cuda_stream)
+        self.ops._check(rc)
+        self.ops.launches += 1
+        self.calls += 1
+        return out.reshape(x.shape)
 
     def close(self) -> None:
         torch.cuda.synchronize(self.device)

@@ -204,19 +204,31 @@ class Model(nn.Module):
             self._allreduce(x)
         return x
 
+    def _sum_add_norm(self, norm: RMSNorm, part: torch.Tensor | None, h: torch.Tensor) -> torch.Tensor:
+        """``h += sum over ranks(part); return norm(h)``: the tensor-parallel epilogue of a sub-block.  With the
+        NVLink all-reduce object this is ONE kernel (all-reduce + residual add + RMSNorm, csrc/nvlink_allreduce.cu);
+        otherwise all-reduce, then the fused add + norm."""
+        if part is None:  # first layer: nothing to add yet
+            return norm(h, out_f16=self._f16_acts)
+        fused = getattr(self._allreduce, "fused_add_rmsnorm", None) if self.world > 1 else None
+        if fused is not None:
+            f16 = self._f16_acts and part.dtype == torch.bfloat16
+            x = fused(part, h, norm.weight, norm.eps, torch.float16 if f16 else None)
+            if x is not None:
+                return x
+        return norm(self._reduce(part), residual=h, out_f16=self._f16_acts)
+
     def forward(self, input_ids: torch.Tensor, ctx, kv_cache, meta=None, logits_rows=None) -> torch.Tensor:
         h = self.embed_tokens(input_ids)  # residual stream [T, hidden]
-        delta = None
+        part = None                        # this rank's partial output of the previous sub-block (not yet summed)
         for i, layer in enumerate(self.layers):
-            x = layer.input_layernorm(h if delta is None else delta, residual=None if delta is None else h,
-                                      out_f16=self._f16_acts)
-            a = self._reduce(sdpa_forward(layer.self_attn, x, ctx, kv_cache, i, meta=meta))
+            x = self._sum_add_norm(layer.input_layernorm, part, h)
+            part = sdpa_forward(layer.self_attn, x, ctx, kv_cache, i, meta=meta)
             if layer.mlp is None:
-                delta = a
                 continue
-            x = layer.post_attention_layernorm(a, residual=h, out_f16=self._f16_acts)  # h += a; x = norm(h)
-            delta = self._reduce(layer.mlp(x))
-        x = self.norm(delta, residual=h, out_f16=self._f16_acts) if delta is not None else self.norm(h, out_f16=self._f16_acts)
+            x = self._sum_add_norm(layer.post_attention_layernorm, part, h)  # h += a; x = norm(h)
+            part = layer.mlp(x)
+        x = self._sum_add_norm(self.norm, part, h)
         if logits_rows is not None:
             x = x.index_select(0, logits_rows)
         return self.embed_tokens.as_linear(x) if self.lm_head is None else self.lm_head(x)

@@ -119,6 +119,7 @@ EXPORTED_SYMBOLS = (
     "b200_ipc_close",
     "b200_ipc_free",
     "b200_allreduce_sum",
+    "b200_allreduce_add_rmsnorm",
 )
 
 
