@@ -104,6 +104,8 @@ class NVLinkAllReduce:
         hidden = x.shape[-1]
         x2, r2 = x.reshape(-1, hidden), residual.reshape(-1, hidden)
         nbytes = x2.numel() * 2
+        if x2.shape[0] > 4 * self.grid:  # prefill-sized: the norm wants one CTA per row, not grid CTAs looping over rows
+            return None
         if (x.dtype not in (torch.bfloat16, torch.float16) or not x2.is_contiguous() or not r2.is_contiguous()
                 or hidden % 8 or hidden > 8192 or nbytes > self.half_bytes or x2.data_ptr() % 16 or r2.data_ptr() % 16
                 or (weight is not None and (weight.dtype != x.dtype or weight.data_ptr() % 16))):
