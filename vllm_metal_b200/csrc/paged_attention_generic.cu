@@ -274,11 +274,36 @@ static int plan_partitions(const b200_paged_attn_args& a, bool mma, int* parts) 
     return unit;
   }
   if (mma) {
-    // Bandwidth kernel: one CTA per (kv head, row, partition).  Split until the
-    // grid is a few waves of the 2 resident CTAs per SM, with partitions as long
-    // as that allows (fewer pipeline fills, smaller reduce).
+    // Bandwidth kernel: one CTA per (kv head, row, partition), 2 resident CTAs per SM.
     const int64_t items = (int64_t)a.num_kv_heads * a.num_q_tokens;
     const int sms = sm_count() > 0 ? sm_count() : 148;
+    if (items <= 2LL * sms) {
+      // Thin grid (tensor-parallel shards, small batches at long context): the whole launch is a handful of
+      // waves, so pick the partition count that minimises waves x (partition length + pipeline fill/drain)
+      // rather than a fixed CTA target -- e.g. 64 items at ctx 4160: 4 partitions of 1040 tokens are ONE wave
+      // of 256 CTAs, where 9 partitions of 512 were 1.95 waves of 576.  Partitions are multiples of 64 tokens.
+      const int64_t slots = 2LL * sms;
+      const int fill = 192;  // tokens' worth of prologue / drain / merge per CTA
+      int64_t best_cost = -1;
+      int best_p = 1, best_size = ((span + 63) / 64) * 64;
+      const int pmax = max_parts;  // what b200_paged_attention_workspace_bytes() sizes the scratch for
+      for (int p = 1; p <= pmax; ++p) {
+        const int psz = (((span + p - 1) / p + 63) / 64) * 64;
+        const int np = (span + psz - 1) / psz;
+        const int64_t waves = (items * np + slots - 1) / slots;
+        const int64_t cost = waves * (psz + fill);
+        if (np > pmax) continue;
+        if (best_cost < 0 || cost < best_cost) {
+          best_cost = cost;
+          best_p = np;
+          best_size = psz;
+        }
+      }
+      *parts = best_p;
+      return best_size;
+    }
+    // Wide grid: split until the grid is a few waves, with partitions as long as that allows (fewer pipeline
+    // fills, smaller reduce).
     const int64_t want = 8LL * sms;  // CTAs
     int64_t p = (want + items - 1) / items;
     if (p < 1) p = 1;
