@@ -277,13 +277,15 @@ static int plan_partitions(const b200_paged_attn_args& a, bool mma, int* parts) 
     // Bandwidth kernel: one CTA per (kv head, row, partition), 2 resident CTAs per SM.
     const int64_t items = (int64_t)a.num_kv_heads * a.num_q_tokens;
     const int sms = sm_count() > 0 ? sm_count() : 148;
-    if (items <= 2LL * sms) {
-      // Thin grid (tensor-parallel shards, small batches at long context): the whole launch is a handful of
-      // waves, so pick the partition count that minimises waves x (partition length + pipeline fill/drain)
-      // rather than a fixed CTA target -- e.g. 64 items at ctx 4160: 4 partitions of 1040 tokens are ONE wave
-      // of 256 CTAs, where 9 partitions of 512 were 1.95 waves of 576.  Partitions are multiples of 64 tokens.
-      const int64_t slots = 2LL * sms;
-      const int fill = 192;  // tokens' worth of prologue / drain / merge per CTA
+    {
+      // The whole launch is a handful of waves of (2 x SMs) resident CTAs, so pick the partition count that
+      // minimises waves x (partition length + pipeline fill/drain) rather than a fixed CTA target.  Measured
+      // (profiles/r02_decode_attn_plan.txt): 512 items at ctx 4096 (the headline shape) run 12% faster single pass
+      // (2 waves, no reduce kernel) than as 3 partitions; 64 items (TP=8) want 4 partitions of 1040 tokens = ONE
+      // wave of 256 CTAs, where 9 partitions of 512 were 1.95 waves of 576.  Partitions are multiples of 64 tokens.
+      const int64_t slots = (a.head_dim >= 128 ? 2LL : 3LL) * sms;  // paged_decode_mma_kernel's launch bounds
+      const int fill = 192;     // tokens' worth of prologue / drain / merge per CTA
+      const int reduce = 448;   // the separate LSE-merge launch (~8 us), in the same token units
       int64_t best_cost = -1;
       int best_p = 1, best_size = ((span + 63) / 64) * 64;
       const int pmax = max_parts;  // what b200_paged_attention_workspace_bytes() sizes the scratch for
@@ -291,7 +293,7 @@ static int plan_partitions(const b200_paged_attn_args& a, bool mma, int* parts) 
         const int psz = (((span + p - 1) / p + 63) / 64) * 64;
         const int np = (span + psz - 1) / psz;
         const int64_t waves = (items * np + slots - 1) / slots;
-        const int64_t cost = waves * (psz + fill);
+        const int64_t cost = waves * (psz + fill) + (np > 1 ? reduce : 0);
         if (np > pmax) continue;
         if (best_cost < 0 || cost < best_cost) {
           best_cost = cost;
@@ -302,15 +304,6 @@ static int plan_partitions(const b200_paged_attn_args& a, bool mma, int* parts) 
       *parts = best_p;
       return best_size;
     }
-    // Wide grid: split until the grid is a few waves, with partitions as long as that allows (fewer pipeline
-    // fills, smaller reduce).
-    const int64_t want = 8LL * sms;  // CTAs
-    int64_t p = (want + items - 1) / items;
-    if (p < 1) p = 1;
-    if (p > max_parts) p = max_parts;
-    int psize = (int)(((span + p - 1) / p + unit - 1) / unit) * unit;
-    *parts = (span + psize - 1) / psize;
-    return psize;
   }
   // Reference gate (paged_ops.cpp:539-541): pure decode && grid below occupancy bound.
   const bool pure_decode = a.num_q_tokens == a.num_seqs;
