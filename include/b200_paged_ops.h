@@ -120,12 +120,13 @@ int b200_copy_blocks(void* key_cache, void* value_cache, const int32_t* src,
  * untouched (:917-920).
  *
  * `workspace` is scratch for split-KV partials; size it with
- * b200_paged_attention_workspace_bytes() for the same args (0 is legal: the
- * call then runs single pass).  `force_partitions`: 0 = heuristic gate,
+ * b200_paged_attention_workspace_bytes() for the same args: it returns exactly what the call's own plan needs
+ * (0 when that plan is single pass).  Passing less is legal: the call then runs single pass.  `force_partitions`: 0 = heuristic gate,
  * 1 = never split, >1 = split into partitions of b200_partition_size() tokens
  * whenever max_seq_len allows (used by the parity tests to pin both routes).
- * `kernel`: 0 = auto, 1 = generic scalar kernel, 2 = tensor-core decode kernel
- * (fails with B200_ERR_UNSUPPORTED if the shape is not instantiated).
+ * `kernel`: 0 = auto, 1 = generic scalar kernel, 2 = tensor-core decode kernel, 3 = tcgen05 tile kernel for
+ * every sequence (2 and 3 fail with B200_ERR_UNSUPPORTED if the shape is not instantiated).  Auto sends
+ * sequences with >= 16 query rows to the tile kernel and the rest to the per-row kernels.
  * --------------------------------------------------------------------------- */
 typedef struct b200_paged_attn_args {
   void* out;
@@ -161,6 +162,9 @@ typedef struct b200_paged_attn_args {
 } b200_paged_attn_args;
 
 size_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args* args);
+/* Kernels one b200_paged_attention call launches for these args (tile kernel + per-row kernel + split-KV merge,
+ * from the same plan the call itself uses; `workspace` / `workspace_bytes` as they will be passed). */
+int b200_paged_attention_num_launches(const b200_paged_attn_args* args);
 int b200_paged_attention(const b200_paged_attn_args* args, void* stream);
 
 /* ---------------------------------------------------------------------------

@@ -98,6 +98,25 @@ def test_copy_blocks(ops):
     assert torch.equal(kc, k0) and torch.equal(vc, v0)
 
 
+def test_cache_copy_blocks_gathers_before_it_scatters():
+    """``array[dst] = array[src]`` (reference kv_cache.py:353) reads every source before any write: a chain
+    1 -> 2, 2 -> 3 must put the OLD block 2 into block 3."""
+    from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
+
+    c = B200PagedKVCache(2, 2, 64, 8, 16, torch.bfloat16, "cuda")
+    for t in (*c.key_caches, *c.value_caches):
+        t.copy_(torch.randn(t.shape, device="cuda").bfloat16())
+    k0 = [k.clone() for k in c.key_caches]
+    v0 = [v.clone() for v in c.value_caches]
+    c.copy_blocks([(1, 2), (2, 3), (5, 6)])
+    for k, v, kk, vv in zip(c.key_caches, c.value_caches, k0, v0, strict=True):
+        kk[[2, 3, 6]] = kk[[1, 2, 5]]  # advanced indexing gathers first, like mx
+        vv[[2, 3, 6]] = vv[[1, 2, 5]]
+        assert torch.equal(k, kk) and torch.equal(v, vv)
+    with pytest.raises(RuntimeError, match="twice"):
+        c.copy_blocks([(1, 4), (2, 4)])
+
+
 # ------------------------------------------------------------ golden fixtures
 
 @pytest.mark.parametrize("name", ["decode_gqa", "decode_window", "mixed", "mixed_window", "softcap", "half"])

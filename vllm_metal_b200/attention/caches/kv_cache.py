@@ -89,9 +89,33 @@ class B200PagedKVCache:
         src_ids, dst_ids = zip(*block_copies, strict=True)
         if any(b < 0 or b >= self.num_blocks for b in (*src_ids, *dst_ids)):
             raise RuntimeError("paged KV block copy contains an out-of-range block id")
+        if len(set(dst_ids)) != len(dst_ids):
+            raise RuntimeError("paged KV block copy writes one destination block twice")
+        # The reference's ``array[dst] = array[src]`` gathers every source before it scatters; the kernel copies
+        # all pairs in parallel, so a pair whose source is another pair's destination must still read the OLD
+        # contents: those sources are staged first.
+        dst_set = set(dst_ids)
+        ops = get_ops()
+        clash = [(s_, d_) for s_, d_ in block_copies if s_ in dst_set and s_ != d_]
+        if clash:
+            # gather-then-scatter through a scratch copy of the clashing sources
+            cs = sorted({s_ for s_, _ in clash})
+            idx = torch.tensor(cs, dtype=torch.int64, device=self.device)
+            pos = {b: i for i, b in enumerate(cs)}
+            for k, v in zip(self.key_caches, self.value_caches, strict=True):
+                ks, vs = k.index_select(0, idx), v.index_select(0, idx)
+                plain = [(s_, d_) for s_, d_ in block_copies if s_ not in dst_set and s_ != d_]
+                if plain:
+                    ps = torch.tensor([s_ for s_, _ in plain], dtype=torch.int32, device=self.device)
+                    pd = torch.tensor([d_ for _, d_ in plain], dtype=torch.int32, device=self.device)
+                    ops.copy_blocks(k, v, ps, pd)
+                di = torch.tensor([d_ for _, d_ in clash], dtype=torch.int64, device=self.device)
+                si = torch.tensor([pos[s_] for s_, _ in clash], dtype=torch.int64, device=self.device)
+                k.index_copy_(0, di, ks.index_select(0, si))
+                v.index_copy_(0, di, vs.index_select(0, si))
+            return
         src = torch.tensor(src_ids, dtype=torch.int32, device=self.device)
         dst = torch.tensor(dst_ids, dtype=torch.int32, device=self.device)
-        ops = get_ops()
         for k, v in zip(self.key_caches, self.value_caches, strict=True):
             ops.copy_blocks(k, v, src, dst)
 

@@ -370,7 +370,10 @@ bool decode_mma_supported(const b200_paged_attn_args& a) {
 template <typename T, int D, int STAGES>
 static int launch_one(const DecodeParams& p, dim3 grid, cudaStream_t st) {
   constexpr int smem = kDecodeWarps * STAGES * 2 * kTileTokens * D * 2;
-  static bool configured = false;
+  static bool configured_dev[16] = {false};  // cudaFuncSetAttribute is per device
+  int dev_ = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev_));
+  bool& configured = configured_dev[dev_ & 15];
   if (!configured) {
     B200_CUDA_OK(cudaFuncSetAttribute(paged_decode_mma_kernel<T, D, STAGES>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -320,13 +320,50 @@ static bool pick_mma(const b200_paged_attn_args& a) {
 
 }  // namespace b200
 
+namespace b200 {
+// What one b200_paged_attention call does for these arguments; shared by the scratch-size query, the launch count
+// query and the launcher so they cannot disagree.
+struct AttnPlan {
+  bool tile;       // tcgen05 tile kernel over the sequences with q_len >= skip_qlen
+  bool rows;       // per-row kernels (everything when !tile, the short sequences of a mixed batch otherwise)
+  bool mma;        // per-row kernel = tensor-core decode kernel (else the generic scalar kernel)
+  int skip_qlen;
+  int parts, psize;  // split-KV plan of the per-row kernels
+};
+constexpr int kTileMinQlen = 16;
+
+static AttnPlan make_plan(const b200_paged_attn_args& a) {
+  AttnPlan pl{};
+  // Varlen prefill / mixed batches (reference paged_ops.cpp:463-497 sends them to the tiled kernel): sequences
+  // with at least kTileMinQlen query rows run on the tcgen05 tile kernel, the remaining (decode) rows of a mixed
+  // batch on the per-row kernels, which leave the tile kernel's sequences untouched.
+  const bool tile_ok = prefill_tc_supported(a);
+  pl.tile = a.kernel == 3 || (a.kernel == 0 && tile_ok && a.num_q_tokens - a.num_seqs + 1 >= kTileMinQlen);
+  // kernel == 3 pins every sequence to the tile kernel (parity tests); auto keeps short ones on the row kernels
+  pl.skip_qlen = pl.tile ? (a.kernel == 3 ? 1 : kTileMinQlen) : 0;
+  pl.rows = a.kernel != 3;
+  pl.mma = pick_mma(a);
+  pl.parts = 1;
+  pl.psize = plan_partitions(a, pl.mma, &pl.parts);
+  return pl;
+}
+}  // namespace b200
+
 extern "C" size_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args* a) {
   using namespace b200;
-  if (!a || a->num_q_tokens <= 0) return 0;
-  const int psize = b200_partition_size();
-  const int64_t P = (a->max_seq_len + psize - 1) / psize;
-  if (P < 2) return 0;
-  return split_workspace_bytes(a->num_q_tokens, a->num_q_heads, P, a->head_dim);
+  if (!a || a->num_q_tokens <= 0 || a->num_seqs <= 0) return 0;
+  const AttnPlan pl = make_plan(*a);
+  if (!pl.rows || pl.parts < 2) return 0;  // single pass: no scratch
+  return split_workspace_bytes(a->num_q_tokens, a->num_q_heads, pl.parts, a->head_dim);
+}
+
+extern "C" int b200_paged_attention_num_launches(const b200_paged_attn_args* a) {
+  using namespace b200;
+  if (!a || a->num_q_tokens <= 0 || a->num_seqs <= 0) return 0;
+  const AttnPlan pl = make_plan(*a);
+  const bool split = pl.rows && pl.parts > 1 && a->workspace != nullptr &&
+                     a->workspace_bytes >= split_workspace_bytes(a->num_q_tokens, a->num_q_heads, pl.parts, a->head_dim);
+  return (pl.tile ? 1 : 0) + (pl.rows ? 1 : 0) + (split ? 1 : 0);
 }
 
 extern "C" int b200_paged_attention(const b200_paged_attn_args* a, void* stream) {
@@ -335,30 +372,24 @@ extern "C" int b200_paged_attention(const b200_paged_attn_args* a, void* stream)
   if (rc != B200_OK) return rc;
   if (a->num_q_tokens == 0 || a->num_seqs == 0) return B200_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  // Varlen prefill / mixed batches (reference paged_ops.cpp:463-497 sends them to the tiled kernel): sequences
-  // with at least kTileMinQlen query rows run on the tcgen05 tile kernel, the remaining (decode) rows of a mixed
-  // batch on the per-row kernels below, which leave the tile kernel's sequences untouched.
-  constexpr int kTileMinQlen = 16;
-  int skip_qlen = 0;
-  const bool tile_ok = prefill_tc_supported(*a);
-  if (a->kernel == 3 && !tile_ok)
+  if (a->kernel == 3 && !prefill_tc_supported(*a))
     return set_error(B200_ERR_UNSUPPORTED,
                      "paged_attention: the tcgen05 tile kernel needs bf16/fp16, head_dim 64/128, block_size | 128 and "
                      "a contiguous [blocks, block_size, kv_heads, head_dim] cache");
-  if (a->kernel == 3 || (a->kernel == 0 && tile_ok && a->num_q_tokens - a->num_seqs + 1 >= kTileMinQlen)) {
-    // kernel == 3 pins every sequence to the tile kernel (parity tests); auto keeps short ones on the row kernels
-    skip_qlen = a->kernel == 3 ? 1 : kTileMinQlen;
+  const AttnPlan pl = make_plan(*a);
+  const int skip_qlen = pl.skip_qlen;
+  if (pl.tile) {
     rc = launch_prefill_tc(*a, skip_qlen, st);
-    if (rc != B200_OK || a->kernel == 3) return rc;
+    if (rc != B200_OK || !pl.rows) return rc;
   }
-  const bool mma = pick_mma(*a);
+  const bool mma = pl.mma;
   if (a->kernel == 2 && !mma)
     return set_error(B200_ERR_UNSUPPORTED,
                      "paged_attention: tensor-core decode kernel does not instantiate "
                      "dtype=%d head_dim=%d block_size=%d group=%d",
                      a->dtype, a->head_dim, a->block_size, a->num_q_heads / a->num_kv_heads);
-  int parts = 1;
-  const int psize = plan_partitions(*a, mma, &parts);
+  int parts = pl.parts;
+  const int psize = pl.psize;
   SplitWorkspace ws{};
   if (parts > 1) {
     const size_t need = split_workspace_bytes(a->num_q_tokens, a->num_q_heads, parts, a->head_dim);

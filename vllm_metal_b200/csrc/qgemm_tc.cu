@@ -724,7 +724,10 @@ static int launch_cfg(const HostArgs& a, int ksplit, cudaStream_t st) {
   constexpr int smem = smem_bytes<NB, PS, NS, SBT, TA>();
   auto kern = qgemm_tc_kernel<T, BITS, G, NB, PS, NS, DQW, SBT, PRE, TA>;
   constexpr int KB_PER_P = (1024 / BITS) / KB;
-  static bool configured = false;
+  static bool configured_dev[16] = {false};  // cudaFuncSetAttribute is per device
+  int dev_ = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev_));
+  bool& configured = configured_dev[dev_ & 15];
   if (!configured) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;

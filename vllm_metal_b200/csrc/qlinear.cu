@@ -289,7 +289,10 @@ static int launch(const Params& p, cudaStream_t st) {
   constexpr int NT = 64 * RB;
   constexpr int stage_bytes = NT * (KT * BITS / 128) * 16 + MT * PITCH * 2;
   constexpr int smem = STAGES * stage_bytes + NT * PITCH * 2;
-  static bool configured = false;
+  static bool configured_dev[16] = {false};  // cudaFuncSetAttribute is per device
+  int dev_ = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev_));
+  bool& configured = configured_dev[dev_ & 15];
   if (!configured) {
     B200_CUDA_OK(cudaFuncSetAttribute(qgemm_mma_kernel<T, BITS, MT, RB>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

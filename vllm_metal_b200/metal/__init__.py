@@ -90,6 +90,7 @@ EXPORTED_SYMBOLS = (
     "b200_reshape_and_cache",
     "b200_copy_blocks",
     "b200_paged_attention_workspace_bytes",
+    "b200_paged_attention_num_launches",
     "b200_paged_attention",
     "b200_qlinear",
     "b200_qlinear_prepack",
@@ -159,6 +160,7 @@ def load_library() -> ctypes.CDLL:
     lib.b200_last_error.restype = ctypes.c_char_p
     lib.b200_paged_attention_workspace_bytes.restype = ctypes.c_size_t
     lib.b200_paged_attention_workspace_bytes.argtypes = [ctypes.POINTER(PagedAttnArgs)]
+    lib.b200_paged_attention_num_launches.argtypes = [ctypes.POINTER(PagedAttnArgs)]
     lib.b200_paged_attention.argtypes = [ctypes.POINTER(PagedAttnArgs), ctypes.c_void_p]
     vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
     lib.b200_reshape_and_cache.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i32, vp]
@@ -419,7 +421,7 @@ class _Ops:
         a.workspace = _ptr(ws)
         a.workspace_bytes = 0 if ws is None else ws.numel()
         self._check(self._lib.b200_paged_attention(ctypes.byref(a), _stream()))
-        self.launches += 2 if need else 1
+        self.launches += self._lib.b200_paged_attention_num_launches(ctypes.byref(a))  # from the call's own plan
 
     # -- MLX-affine quantized linears (mlx_native.py:212-239) -------------------
     def quantized_matmul(self, x, w, scales, biases, transpose: bool = True, group_size: int = 64,
