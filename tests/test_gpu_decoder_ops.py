@@ -218,3 +218,43 @@ def test_programmatic_dependent_launch_does_not_change_results(ops):
     torch.cuda.synchronize()
     assert torch.equal(x_off, x_on)
     assert torch.equal(ids0, ids1)
+
+
+def test_patched_model_wrapper_matches_direct_sdpa_forward():
+    """``MHAPagedAttentionRuntime.patch_model`` wraps every ``self_attn``; calling the wrapper under a step context
+    gives the same bits (and the same cache contents) as the direct ``sdpa_forward`` the runner uses."""
+    import dataclasses
+
+    from vllm_metal_b200.attention import context as ctx_mod
+    from vllm_metal_b200.attention.impls.sdpa import sdpa_forward
+    from vllm_metal_b200.attention.impls.sdpa_wrapper import SDPAPagedAttentionWrapper
+    from vllm_metal_b200.attention.runtime.mha import MHAPagedAttentionRuntime
+    from vllm_metal_b200.lm.decoder import PRESETS, Model
+
+    args = dataclasses.replace(PRESETS["tiny"], sinks=True, sliding_window=16,
+                               layer_types=["sliding_attention", "full_attention"])
+    model = Model(args, torch.bfloat16, "cuda", seed=5)
+    inner = [layer.self_attn for layer in model.layers]
+    rt = MHAPagedAttentionRuntime(num_layers=args.num_layers, num_kv_heads=args.n_kv_heads, head_dim=args.head_dim,
+                                  block_size=16, dtype=torch.bfloat16, device="cuda",
+                                  sliding_window_per_layer=args.sliding_window_per_layer())
+    rt.initialize(12)
+    rt.warm_up()
+    assert rt.patch_model(model) == args.num_layers
+    assert all(isinstance(layer.self_attn, SDPAPagedAttentionWrapper) for layer in model.layers)
+    ref = MHAPagedAttentionRuntime(num_layers=args.num_layers, num_kv_heads=args.n_kv_heads, head_dim=args.head_dim,
+                                   block_size=16, dtype=torch.bfloat16, device="cuda",
+                                   sliding_window_per_layer=args.sliding_window_per_layer())
+    ref.initialize(12)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randn((40, args.hidden), device="cuda", generator=g).bfloat16()
+    ctx_mod.prepare_unified([([3, 7], 20), ([5], 4)], [([9, 2, 11], 38, 0)], 16)
+    try:
+        ctx = ctx_mod.get_context()
+        for i, layer in enumerate(model.layers):
+            got = layer.self_attn(x)
+            want = sdpa_forward(inner[i], x, ctx, ref.kv_cache, i)
+            assert torch.equal(got, want)
+            assert torch.equal(rt.kv_cache.key_caches[i], ref.kv_cache.key_caches[i])
+    finally:
+        ctx_mod.clear_context()

@@ -33,6 +33,7 @@ class B200PagedKVCache:
         kv_heads_per_layer: list[int] | None = None,
         head_dim_per_layer: list[int] | None = None,
         sliding_window_per_layer: list[int] | None = None,
+        block_size_per_layer: list[int] | None = None,
     ) -> None:
         if dtype not in (torch.float16, torch.bfloat16, torch.float32):
             raise ValueError(f"unsupported KV cache dtype {dtype}")
@@ -46,17 +47,21 @@ class B200PagedKVCache:
         self.kv_heads_per_layer = kv_heads_per_layer or [num_kv_heads] * num_layers
         self.head_dim_per_layer = head_dim_per_layer or [head_dim] * num_layers
         self.sliding_window_per_layer = sliding_window_per_layer or [-1] * num_layers
+        self.block_size_per_layer = block_size_per_layer or [block_size] * num_layers
+        self._group_index_per_layer = [0] * num_layers
         for name, lst in (
             ("kv_heads_per_layer", self.kv_heads_per_layer),
             ("head_dim_per_layer", self.head_dim_per_layer),
             ("sliding_window_per_layer", self.sliding_window_per_layer),
+            ("block_size_per_layer", self.block_size_per_layer),
         ):
             if len(lst) != num_layers:
                 raise ValueError(f"{name} length {len(lst)} != num_layers {num_layers}")
 
         self.key_caches: list[torch.Tensor] = []
         self.value_caches: list[torch.Tensor] = []
-        uniform = len(set(self.kv_heads_per_layer)) == 1 and len(set(self.head_dim_per_layer)) == 1
+        uniform = len(set(self.kv_heads_per_layer)) == 1 and len(set(self.head_dim_per_layer)) == 1 and \
+            len(set(self.block_size_per_layer)) == 1
         if uniform:
             shape = (num_layers, num_blocks, block_size, self.kv_heads_per_layer[0], self.head_dim_per_layer[0])
             self._k_all = torch.zeros(shape, dtype=dtype, device=self.device)
@@ -65,16 +70,29 @@ class B200PagedKVCache:
             self.value_caches = [self._v_all[i] for i in range(num_layers)]
         else:
             for i in range(num_layers):
-                shape = (num_blocks, block_size, self.kv_heads_per_layer[i], self.head_dim_per_layer[i])
+                shape = (num_blocks, self.block_size_per_layer[i], self.kv_heads_per_layer[i], self.head_dim_per_layer[i])
                 self.key_caches.append(torch.zeros(shape, dtype=dtype, device=self.device))
                 self.value_caches.append(torch.zeros(shape, dtype=dtype, device=self.device))
 
+    @classmethod
+    def from_layout(cls, layout, dtype: torch.dtype = torch.bfloat16, device: torch.device | str = "cuda"):
+        """Cache shaped by vLLM's grouped layout (reference ``MetalPagedKVCache.from_layout``,
+        kv_cache.py:128-170): per-layer page size / heads / window and the scheduler KV group each layer reads
+        its slot mapping and block tables from (mixed full + sliding-window models)."""
+        ls = layout.layers
+        self = cls(len(ls), ls[0].num_kv_heads, ls[0].head_dim, layout.num_blocks, ls[0].block_size, dtype, device,
+                   kv_heads_per_layer=[l.num_kv_heads for l in ls], head_dim_per_layer=[l.head_dim for l in ls],
+                   sliding_window_per_layer=[l.sliding_window for l in ls],
+                   block_size_per_layer=[l.block_size for l in ls])
+        self._group_index_per_layer = [l.group_index for l in ls]
+        return self
+
     # -- reference API ----------------------------------------------------------
     def block_size_for_layer(self, layer_idx: int) -> int:
-        return self.block_size
+        return self.block_size_per_layer[layer_idx]
 
     def group_index_for_layer(self, layer_idx: int) -> int:
-        return 0
+        return self._group_index_per_layer[layer_idx]
 
     def replace_layer_cache(self, layer_idx: int, key_cache: torch.Tensor, value_cache: torch.Tensor) -> None:
         """Rebind the handles ``reshape_and_cache`` returns (kv_cache.py:310-325).
@@ -122,8 +140,8 @@ class B200PagedKVCache:
     def bytes_per_block(self) -> int:
         esize = torch.empty((), dtype=self.dtype).element_size()
         return sum(
-            2 * self.block_size * h * d * esize
-            for h, d in zip(self.kv_heads_per_layer, self.head_dim_per_layer, strict=True)
+            2 * b * h * d * esize
+            for b, h, d in zip(self.block_size_per_layer, self.kv_heads_per_layer, self.head_dim_per_layer, strict=True)
         )
 
     @property

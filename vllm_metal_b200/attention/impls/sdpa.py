@@ -162,14 +162,24 @@ def sdpa_forward(
     else:
         q, k, v = inner.q_proj(x2), inner.k_proj(x2), inner.v_proj(x2)
         hd = q.shape[-1] // n_heads
+    gate = None
+    if getattr(inner, "attn_output_gate", False):
+        # Qwen3-Next style: q_proj emits (query, gate) per head; out *= sigmoid(gate) (sdpa.py:735-736)
+        hd = q.shape[-1] // (2 * n_heads)
+        q, gate = q.reshape(t, n_heads, 2 * hd).split([hd, hd], dim=-1)
+        q, gate = q.reshape(t, n_heads * hd), gate.reshape(t, n_heads * hd)
     q = q.reshape(t, n_heads, hd)
     k = k.reshape(t, n_kv_heads, hd)
     v = v.reshape(t, n_kv_heads, hd)
     rope = getattr(inner, "rope", None)
     q_norm, k_norm = getattr(inner, "q_norm", None), getattr(inner, "k_norm", None)
     k_cache, v_cache = kv_cache.key_caches[layer_idx], kv_cache.value_caches[layer_idx]
+    cache_hd = kv_cache.head_dim_per_layer[layer_idx]
+    if hd > cache_hd:
+        raise ValueError(f"layer head_dim {hd} exceeds the cache head_dim {cache_hd}")
     fused = (
         _FUSE_NORM_ROPE_CACHE
+        and hd == cache_hd
         and q.dtype == kv_cache.dtype
         and all(x.stride(2) == 1 and x.stride(1) == hd for x in (q, k, v))
         and (q_norm is None) == (k_norm is None)
@@ -196,7 +206,12 @@ def sdpa_forward(
             ops.rope(q, k, meta.positions, rope.dims, rope.base, rope.traditional)
         if q.dtype != kv_cache.dtype:
             q, k, v = q.to(kv_cache.dtype), k.to(kv_cache.dtype), v.to(kv_cache.dtype)
-        k_cache, v_cache = ops.reshape_and_cache(k, v, k_cache, v_cache, meta.slot_mapping)
+        if hd < cache_hd:
+            # variable-head_dim models allocate the cache at the widest layer: zero-pad q/k/v up to it; zeros change
+            # neither q.k nor the first hd columns of P.V (sdpa.py:377-420, :536-539)
+            pad = (0, cache_hd - hd)
+            q, k, v = (torch.nn.functional.pad(z, pad) for z in (q, k, v))
+        k_cache, v_cache = ops.reshape_and_cache(k.contiguous(), v.contiguous(), k_cache, v_cache, meta.slot_mapping)
     kv_cache.replace_layer_cache(layer_idx, k_cache, v_cache)
 
     if meta.block_size != cache_block_size:  # zero-copy view at the kernel page size
@@ -204,11 +219,20 @@ def sdpa_forward(
         k_cache = k_cache.reshape(-1, meta.block_size, kvh, d)
         v_cache = v_cache.reshape(-1, meta.block_size, kvh, d)
 
-    out = torch.empty((t, n_heads, hd), dtype=q.dtype, device=q.device)
+    out = torch.empty((t, n_heads, cache_hd), dtype=q.dtype, device=q.device)
     ops.paged_attention_primitive(
         q, k_cache, v_cache, kv_cache.kv_heads_per_layer[layer_idx], float(scale), 0.0,
         meta.block_tables, meta.seq_lens, meta.cu_seqlens_q, meta.block_size, meta.max_seq_len,
         kv_cache.sliding_window_per_layer[layer_idx], out,
         window_seqlen_q=1, sinks=sinks)
-    y = inner.o_proj(out.reshape(t, n_heads * hd))
+    if hd < cache_hd:
+        out = out[..., :hd]  # strip the pad before o_proj (truncate_padded_output)
+    out = out.reshape(t, n_heads * hd)
+    if gate is not None:
+        out = out * torch.sigmoid(gate.to(out.dtype))
+    if getattr(inner, "gating", False) and hasattr(inner, "g_proj"):
+        # Laguna-style per-head gate: softplus(g_proj(x)) in fp32, one scalar per head (sdpa.py:742-773)
+        g = torch.nn.functional.softplus(inner.g_proj(x2).float()).to(out.dtype)
+        out = (out.reshape(t, n_heads, hd) * g.unsqueeze(-1)).reshape(t, n_heads * hd)
+    y = inner.o_proj(out.contiguous())
     return y.reshape(*lead_shape, y.shape[-1])

@@ -1,0 +1,1 @@
+"""Paged-attention runtimes (reference: vllm_metal/attention/runtime/)."""
