@@ -19,7 +19,7 @@ from collections.abc import Sequence
 import numpy as np
 import torch
 
-from ..attention.context import clear_context, get_context, prepare_unified
+from ..attention.context import clear_context, get_context, prepare_grouped, prepare_unified
 from ..attention.impls.sdpa import _KernelMetadata, _kernel_metadata
 from ..metal import get_ops
 from ..metal.constants import PARTITION_SIZE
@@ -84,6 +84,7 @@ class PagedModelRunner:
         self.max_batch = max_batch
         self.max_blocks = (max_model_len + self.block_size - 1) // self.block_size
         self.use_cuda_graph = use_cuda_graph
+        self.group_block_sizes: tuple[int, ...] | None = None  # set by the worker for multi-group KV layouts
         self.buf = StepBuffers(max_batch, self.max_blocks, self.device)
         self._graphs: dict[tuple[int, int, bool], torch.cuda.CUDAGraph] = {}
         # kernels of ours inside each captured graph (bench.py's gpu_launches)
@@ -98,7 +99,11 @@ class PagedModelRunner:
         ``decode_requests``: ``(block_ids, seq_len)``; ``prefill_requests``:
         ``(block_ids, num_tokens, start_pos)`` -- the ``prepare_unified`` contract.
         """
-        prepare_unified(decode_requests, prefill_requests, self.block_size)
+        if self.group_block_sizes is not None:
+            # mixed full / sliding-window KV groups: every request carries one block-id list per scheduler group
+            prepare_grouped(decode_requests, prefill_requests, self.group_block_sizes)
+        else:
+            prepare_unified(decode_requests, prefill_requests, self.block_size)
         ctx = get_context()
         try:
             ids = torch.tensor(list(input_ids), dtype=torch.int32).pin_memory().to(self.device, non_blocking=True)
@@ -110,7 +115,7 @@ class PagedModelRunner:
             # bytes that crossed PCIe for this step: ids + logit rows + the kernel metadata sdpa uploads once
             # (slot_mapping int64 [T], seq_lens / cu_seqlens int32, block tables int32), token ids back
             nseq = len(ctx.cu_seqlens) - 1
-            maxb = max((len(t) for t in ctx.block_tables), default=0)
+            maxb = max((len(t) for t in (ctx.block_tables or [])), default=0)
             self.h2d_bytes += ids.numel() * 4 + last_rows.numel() * 8 + len(ctx.slot_mapping) * 8 + \
                 (2 * nseq + 1) * 4 + nseq * maxb * 4 + len(ctx.slot_mapping) * 4
             self.d2h_bytes += len(out) * 4

@@ -55,7 +55,7 @@ def model_args_from_hf_config(hf_config: Any, quant: dict | None = None) -> Mode
 
 class _RequestState:
     """What the runner keeps per live request (reference RequestState, model_runner.py:1150-1200): every known
-    token id (prompt + generated), the block ids of KV group 0 and how many tokens are already in the cache."""
+    token id (prompt + generated), one block-id list per KV-cache group and how many tokens are already cached."""
 
     __slots__ = ("tokens", "block_ids", "num_computed")
 
@@ -148,14 +148,28 @@ class B200Worker(WorkerBase):
     def initialize_from_config(self, kv_cache_config: KVCacheConfig) -> None:
         a = self.model.args
         world = self.parallel_config.tensor_parallel_size
-        self.kv_cache = B200PagedKVCache(a.num_layers, a.n_kv_heads // world, a.head_dim,
-                                         int(kv_cache_config.num_blocks), self.cache_config.block_size,
-                                         torch.bfloat16, self.device,
-                                         sliding_window_per_layer=a.sliding_window_per_layer())
+        groups = getattr(kv_cache_config, "kv_cache_groups", None) or []
+        self._num_kv_groups = max(1, len(groups))
+        group_sizes = None
+        if len(groups) > 1:
+            # vLLM grouped the layers (full + sliding-window specs): adopt its layout as is -- per-layer page size,
+            # window and the scheduler group whose block ids the layer reads (reference adopt_layout, runtime/mha.py:74)
+            from ..attention.caches.mha_layout import MHAKVCacheLayout
+
+            names = tuple(f"layers.{i}.self_attn" for i in range(a.num_layers))
+            layout = MHAKVCacheLayout.from_config(kv_cache_config, names)
+            self.kv_cache = B200PagedKVCache.from_layout(layout, torch.bfloat16, self.device)
+            group_sizes = layout.group_block_sizes
+        else:
+            self.kv_cache = B200PagedKVCache(a.num_layers, a.n_kv_heads // world, a.head_dim,
+                                             int(kv_cache_config.num_blocks), self.cache_config.block_size,
+                                             torch.bfloat16, self.device,
+                                             sliding_window_per_layer=a.sliding_window_per_layer())
         self.model_runner = PagedModelRunner(self.model, self.kv_cache,
                                              max_batch=int(self.scheduler_config.max_num_seqs),
                                              max_model_len=int(self.model_config.max_model_len),
-                                             use_cuda_graph=not self.model_config.enforce_eager)
+                                             use_cuda_graph=not self.model_config.enforce_eager and group_sizes is None)
+        self.model_runner.group_block_sizes = group_sizes
 
     def compile_or_warm_up_model(self) -> float:
         """Capture the decode CUDA graphs the first real steps would otherwise pay for (reference
@@ -189,9 +203,10 @@ class B200Worker(WorkerBase):
         for nr in so.scheduled_new_reqs:
             if nr.prompt_token_ids is None:
                 raise NotImplementedError("prompt embeddings are outside the B200 decode hot path")
-            if len(nr.block_ids) != 1:
-                raise NotImplementedError("one KV-cache group is supported (mixed full/sliding groups: DESIGN.md)")
-            self._requests[nr.req_id] = _RequestState(list(nr.prompt_token_ids), list(nr.block_ids[0]),
+            if len(nr.block_ids) != getattr(self, "_num_kv_groups", 1):
+                raise RuntimeError(f"request {nr.req_id}: {len(nr.block_ids)} block-id lists for "
+                                   f"{getattr(self, '_num_kv_groups', 1)} KV-cache groups")
+            self._requests[nr.req_id] = _RequestState(list(nr.prompt_token_ids), [list(b) for b in nr.block_ids],
                                                       int(nr.num_computed_tokens))
         cached = so.scheduled_cached_reqs
         for i, rid in enumerate(cached.req_ids):
@@ -199,11 +214,12 @@ class B200Worker(WorkerBase):
             st.num_computed = int(cached.num_computed_tokens[i])
             new_blocks = cached.new_block_ids[i]
             if rid in cached.resumed_req_ids:
-                st.block_ids = list(new_blocks[0]) if new_blocks is not None else []
+                st.block_ids = [list(b) for b in new_blocks] if new_blocks is not None else [[] for _ in st.block_ids]
                 if rid in cached.all_token_ids:
                     st.tokens = list(cached.all_token_ids[rid])
             elif new_blocks is not None:
-                st.block_ids.extend(new_blocks[0])
+                for have, more in zip(st.block_ids, new_blocks, strict=True):
+                    have.extend(more)
             if cached.new_token_ids and cached.new_token_ids[i]:  # pipeline-parallel peers only; we sample here
                 st.tokens = st.tokens[:st.num_computed] + list(cached.new_token_ids[i])
         decodes, prefills = [], []  # (req_id, state, n)
@@ -215,12 +231,13 @@ class B200Worker(WorkerBase):
             (decodes if n == 1 and st.num_computed > 0 else prefills).append((rid, st, int(n)))
         tokens: list[int] = []
         dec_rows, pre_rows = [], []
+        grouped = getattr(self.model_runner, "group_block_sizes", None) is not None
         for _, st, _n in decodes:
             tokens.append(st.tokens[st.num_computed])
-            dec_rows.append((st.block_ids, st.num_computed))
+            dec_rows.append((st.block_ids if grouped else st.block_ids[0], st.num_computed))
         for _, st, n in prefills:
             tokens.extend(st.tokens[st.num_computed:st.num_computed + n])
-            pre_rows.append((st.block_ids, n, st.num_computed))
+            pre_rows.append((st.block_ids if grouped else st.block_ids[0], n, st.num_computed))
         order = decodes + prefills
         r = self.model_runner
         if not tokens:
