@@ -272,17 +272,28 @@ def test_prepacked_rejects_unsupported(ops):
 
 
 def test_quantized_linear_module_prepack(ops):
+    """prepack() picks the resident layout by size: small matrices keep the cluster split-K kernel's words
+    (``weight_tc``), large ones the stream-K blob (``weight_blob``); either way ``mlx_weight()`` and checkpoints
+    give the MLX layout back bit-exactly."""
     from vllm_metal_b200.quant.linear import QuantizedLinear
 
-    w = torch.randn((256, 512), device="cuda").bfloat16() * 0.02
-    lin = QuantizedLinear.from_dense(w, None, 64, 4, torch.bfloat16)
-    x = torch.randn((8, 512), device="cuda").bfloat16()
-    y0 = lin(x)  # MLX-layout kernel (bf16 dequant)
-    lin.prepack()
-    assert lin.weight_blob.dtype == torch.uint8 and lin.weight.shape == (256, 64)
-    y1 = lin(x)  # streaming blob, fp16 dequant: same math, one rounding finer
-    assert (y1.float() - y0.float()).abs().max().item() <= 2e-2 + 1e-2 * y0.float().abs().max().item()
-    lin2 = QuantizedLinear.from_dense(w, None, 64, 4, torch.bfloat16).prepack(keep_mlx_layout=False)
-    assert lin2.weight.shape[0] == 0 and torch.equal(lin2.mlx_weight(), lin.weight)
-    assert torch.equal(lin2(x), y1)
-    assert torch.equal(lin2.state_dict()["weight"], lin.weight)  # checkpoints keep the MLX layout
+    for (n, k), attr in (((256, 512), "weight_tc"), ((8192 + 256, 4096), "weight_blob")):
+        w = torch.randn((n, k), device="cuda").bfloat16() * 0.02
+        lin = QuantizedLinear.from_dense(w, None, 64, 4, torch.bfloat16)
+        x = torch.randn((8, k), device="cuda").bfloat16()
+        y0 = lin(x)  # MLX-layout call
+        lin.prepack()
+        assert getattr(lin, attr, None) is not None and lin.weight.shape == (n, k // 8)
+        assert (attr == "weight_blob") == (getattr(lin, "weight_tc", None) is None)
+        y1 = lin(x)
+        assert (y1.float() - y0.float()).abs().max().item() <= 2e-2 + 1e-2 * y0.float().abs().max().item()
+        lin2 = QuantizedLinear.from_dense(w, None, 64, 4, torch.bfloat16).prepack(keep_mlx_layout=False)
+        assert lin2.weight.shape[0] == 0 and torch.equal(lin2.mlx_weight(), lin.weight)
+        assert torch.equal(lin2(x), y1)
+        assert torch.equal(lin2.state_dict()["weight"], lin.weight)  # checkpoints keep the MLX layout
+        # both layouts resident (prefill deployments): M > 64 takes the tensor-core GEMM, M <= 64 the blob
+        lin3 = QuantizedLinear.from_dense(w, None, 64, 4, torch.bfloat16).prepack(keep_mlx_layout=False, prefill_layout=True)
+        assert getattr(lin3, "weight_tc", None) is not None
+        xb = torch.randn((200, k), device="cuda").bfloat16()
+        yb = lin3(xb)
+        assert (yb[:8].float() - lin3(xb[:8]).float()).abs().max().item() <= 2e-2 + 1e-2 * yb.float().abs().max().item()
