@@ -634,18 +634,20 @@ def run_b200(args) -> None:
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(per_step_launches * args.steps),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "paged_decode_mma_kernel (+ split_reduce_kernel)",
+            "roofline": {"bound": "hbm", "kernel": "paged_decode_mma_kernel (+ split_reduce_kernel when the plan splits)",
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0,
-                         "traffic": _ncu_traffic("r01_attn_full_summary.txt") if world == 1 and args.config == "b" else None,
-                         "traffic_source": "profiles/r01_attn_full_summary.txt (ncu --set full, same shape; the "
-                                           "attention kernel is unchanged since)",
+                         "traffic": _ncu_traffic("r02_decode_attn_full_summary.txt") if world == 1 and args.config == "b" else None,
+                         "traffic_source": "profiles/r02_decode_attn_full_summary.txt (ncu --set full of the shipped "
+                                           "kernel at this shape, single-pass plan; dram read + write per launch)",
                          "bytes_per_launch": alg_bytes, "us_per_launch": attn_ms * 1e3},
             "roofline_qgemv": None if mlp is None else {
                 "bound": "hbm",
                 "kernel": f"qgemm_stream_kernel, persistent stream-K, fp16 A in TMEM, SwiGLU epilogue "
                           f"(gate_up {n_gu}x{k_gu} int{a.bits} g{a.group_size}, M={BATCH})",
                 "achieved": gemv_gbs, "peak": peak, "unit": "GB/s", "frac": gemv_gbs / peak,
+                "traffic": _ncu_traffic("r02_qstream_gate_up_full_summary.txt") if world == 1 and args.config == "b" else None,
+                "traffic_source": "profiles/r02_qstream_gate_up_full_summary.txt (ncu --set full, same shape)",
                 "bytes_per_launch": gemv_bytes, "us_per_launch": gemv_ms * 1e3},
             "cpu_baseline": cpu,
         }
