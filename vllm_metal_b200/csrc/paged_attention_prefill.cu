@@ -8,15 +8,16 @@
 // sequence lookup is the reference's `cu_seqlens_q[i]/BQ + i` bound (:162-171).  Like the NAX variant, P is
 // rounded to the operand type before the PV product (relaxed precision); everything else is fp32.
 //
-// One CTA = one 128-row Q tile of one (sequence, q head):
+// One CTA = two 128-row Q tiles (256 consecutive query rows) of one (sequence, q head), ping-ponged FlashAttention-4
+// style so that one tile's softmax overlaps the other tile's tensor-core work and K/V are fetched once for both:
 //   warp 0      TMA producer: Q tile once; per 128-token KV block the K and V pages of the block table
 //               (one box [64 d x block_size tokens] per page and 64-wide half of the head) into two 2-deep rings
-//   warp 1      MMA issuer: S_j = Q K_j^T (SS form, both K-major, 128B swizzle) into one of two TMEM S buffers,
-//               O += P_j V_j (TS form: P from TMEM, V MN-major straight from the token-major cache layout)
-//   warps 2..5  softmax: thread = query row; S row TMEM -> registers, mask, running max with lazy rescale
-//               (O and l are rescaled only when the max grows by more than 2^8, FlashAttention-4's rule), P -> TMEM,
-//               final sink fold, normalise, store
-// TMEM: S0 [0,128) | S1 [128,256) | P [256,320) | O [320,320+D).
+//   warp 1      MMA issuer: S_i(j) = Q_i K_j^T (SS form, both K-major, 128B swizzle), O_i += P_i(j) V_j (TS form: P
+//               from TMEM, V MN-major straight from the token-major cache layout), tiles i = 0, 1 interleaved
+//   warps 2..5 / 6..9  softmax of Q tile 0 / 1: thread = query row; S row TMEM -> registers, mask, running max with
+//               lazy rescale (O and l are rescaled only when the max grows by more than 2^8, FlashAttention-4's
+//               rule), P -> TMEM over S's own columns, final sink fold, normalise, store
+// TMEM: S0/P0 [0,128) | S1/P1 [128,256) | O0 [256,256+D) | O1 [256+D,256+2D).
 //
 // Flops per launch: 4 * D * sum_i q_i * (ctx_i + (q_i + 1) / 2) per q head (causal).
 #include "paged_attention.cuh"
@@ -26,9 +27,9 @@ namespace b200 {
 namespace pf {
 using namespace tc;
 
-constexpr int BQ = 128, BK = 128;
-constexpr int THREADS = 6 * 32;
-constexpr int TM_S = 0, TM_P = 256, TM_O = 320;
+constexpr int BQ = 128, BK = 128, BQ2 = 2 * BQ;
+constexpr int THREADS = 10 * 32;          // TMA, MMA, 2 x 4 softmax warps
+constexpr int TM_SP = 0, TM_O = 2 * BK;   // S_i / P_i at TM_SP + i * 128, O_i at TM_O + i * D
 constexpr float kRescaleThreshold = 8.f;  // log2 units
 
 struct Params {
@@ -87,7 +88,7 @@ struct Smem {
   static constexpr int KV_BYTES = BK * D * 2;   // one K (or V) tile: HALVES x [128 tokens x 128 B]
   static constexpr int HALF_BYTES = BK * 128;   // 16 KiB
   static constexpr int STAGES = 2;
-  static constexpr int TOTAL = Q_BYTES + 2 * STAGES * KV_BYTES + 1024 /*barriers*/ + 1024 /*align*/;
+  static constexpr int TOTAL = 2 * Q_BYTES + 2 * STAGES * KV_BYTES + 1024 /*barriers*/ + 1024 /*align*/;
 };
 
 __device__ __forceinline__ float tanh_approx(float x) {
@@ -106,25 +107,27 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
   constexpr int HALVES = SM::HALVES, STAGES = SM::STAGES;
   pdl_trigger();
   pdl_wait();  // the metadata (seq_lens advance on the device), q, the caches come from earlier kernels of the step
-  // ---- which (sequence, local Q tile) is this CTA: largest i with cu[i]/BQ + i <= tile (reference :162-171)
+  // ---- which (sequence, local 256-row Q super-tile) is this CTA: largest i with cu[i]/BQ2 + i <= tile (:162-171)
   // CTAs are dispatched in blockIdx order: hand out the LAST tiles first -- under a causal mask they walk the most
   // KV blocks, so the long ones start early and the short ones fill the tail of the last wave
   const int tile = gridDim.x - 1 - blockIdx.x, h = blockIdx.y;
   int lo_i = 0, hi_i = p.num_seqs;
   while (hi_i - lo_i > 1) {
     const int mid = (lo_i + hi_i) >> 1;
-    if (p.cu[mid] / BQ + mid <= tile) lo_i = mid; else hi_i = mid;
+    if (p.cu[mid] / BQ2 + mid <= tile) lo_i = mid; else hi_i = mid;
   }
   const int seq = lo_i;
   const int q_start = p.cu[seq], q_len = p.cu[seq + 1] - q_start;
-  const int local = tile - (q_start / BQ + seq);
-  if (local * BQ >= q_len || q_len < p.min_qlen) return;  // padding tile, or a sequence the row kernels own
-  const int row0 = local * BQ;                       // first query row of the tile inside the sequence
-  const int nrows = min(BQ, q_len - row0);
+  const int local = tile - (q_start / BQ2 + seq);
+  if (local * BQ2 >= q_len || q_len < p.min_qlen) return;  // padding tile, or a sequence the row kernels own
+  const int row0 = local * BQ2;                      // first query row of the super-tile inside the sequence
+  const int nrows_all = min(BQ2, q_len - row0);
+  const bool two = nrows_all > BQ;                    // the second 128-row Q tile exists
   const int seq_len = p.seq_lens[seq];
-  const int qabs0 = seq_len - q_len + row0;           // absolute position of tile row 0
-  // KV positions any row of the tile can see: [kv_lo, kv_hi)
-  const int kv_hi = min(seq_len, qabs0 + nrows);
+  const int qabs0 = seq_len - q_len + row0;           // absolute position of row 0
+  // KV positions any row of the super-tile can see: [kv_lo, kv_hi); both Q tiles walk this same block range (the
+  // tile that cannot see a block masks it: at most one block at either end)
+  const int kv_hi = min(seq_len, qabs0 + nrows_all);
   if (kv_hi <= 0) return;
   const int kv_lo = p.sliding_window >= 0 ? max(0, qabs0 + 1 - p.sliding_window) : 0;
   const int j0 = kv_lo / BK, j1 = (kv_hi - 1) / BK;   // KV blocks j0..j1
@@ -132,16 +135,17 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sm_q = base;
-  const uint32_t sm_k = sm_q + SM::Q_BYTES;
+  const uint32_t sm_q = base;                         // 2 Q tiles
+  const uint32_t sm_k = sm_q + 2 * SM::Q_BYTES;
   const uint32_t sm_v = sm_k + STAGES * SM::KV_BYTES;
   const uint32_t sm_bar = sm_v + STAGES * SM::KV_BYTES;
   const uint32_t bar_q = sm_bar;
   const uint32_t bar_k_full = bar_q + 8, bar_k_empty = bar_k_full + 8 * STAGES;
   const uint32_t bar_v_full = bar_k_empty + 8 * STAGES, bar_v_empty = bar_v_full + 8 * STAGES;
-  const uint32_t bar_s_full = bar_v_empty + 8 * STAGES, bar_s_free = bar_s_full + 16;
-  const uint32_t bar_p_full = bar_s_free + 16, bar_o_full = bar_p_full + 8;
-  const uint32_t tmem_ptr_addr = bar_o_full + 8;
+  const uint32_t bar_s_full = bar_v_empty + 8 * STAGES;   // [2 tiles]
+  const uint32_t bar_p_full = bar_s_full + 16;            // [2 tiles]
+  const uint32_t bar_o_full = bar_p_full + 16;            // [2 tiles]
+  const uint32_t tmem_ptr_addr = bar_o_full + 16;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(gen + (tmem_ptr_addr - base));
 
@@ -156,10 +160,9 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_s_full + 8 * i, 1);
-      mbar_init(bar_s_free + 8 * i, 4);
+      mbar_init(bar_p_full + 8 * i, 4);
+      mbar_init(bar_o_full + 8 * i, 1);
     }
-    mbar_init(bar_p_full, 4);
-    mbar_init(bar_o_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -176,10 +179,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
   if (warp == 0) {
     // ===== TMA producer =====
     if (elect_one()) {
-      mbar_expect_tx(bar_q, SM::Q_BYTES);
+      mbar_expect_tx(bar_q, (two ? 2 : 1) * SM::Q_BYTES);
+      for (int i = 0; i < (two ? 2 : 1); ++i)
 #pragma unroll
-      for (int hf = 0; hf < HALVES; ++hf)
-        tma_load_2d(sm_q + hf * SM::HALF_BYTES, &q_map, bar_q, h * D + hf * 64, q_start + row0);
+        for (int hf = 0; hf < HALVES; ++hf)
+          tma_load_2d(sm_q + i * SM::Q_BYTES + hf * SM::HALF_BYTES, &q_map, bar_q, h * D + hf * 64, q_start + row0 + i * BQ);
     }
     __syncwarp();
     const int32_t* table = p.block_tables + (int64_t)seq * p.max_blocks_per_seq;
@@ -223,180 +227,185 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
       if (++st == STAGES) { st = 0; ph ^= 1; }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
+    // ===== MMA issuer.  The two Q tiles ping-pong: while one tile's softmax warps work on S_i(j), the tensor pipe
+    // runs the other tile's S / PV.  S_i and P_i share tensor memory (P overwrites the first half of S's columns):
+    // tcgen05.mma executes in issue order, so S_i(j+1), issued after PV_i(j), cannot overtake it. =====
     const uint32_t fmt = p.is_fp16 ? 0u : 1u;
     const uint32_t idesc_s = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BK >> 3) << 17) | ((uint32_t)(BQ >> 4) << 24);
     // PV: B (V) is MN-major (bit 16)
     const uint32_t idesc_o = (1u << 4) | (fmt << 7) | (fmt << 10) | (1u << 16) | ((uint32_t)(D >> 3) << 17) |
                              ((uint32_t)(BQ >> 4) << 24);
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const int ntile = two ? 2 : 1;
     mbar_wait(bar_q, 0);
-    auto issue_s = [&](int it) {  // S_it = Q K_it^T into S buffer it & 1
-      const int st = it % STAGES, b = it & 1;
-      mbar_wait(bar_k_full + 8 * st, (it / STAGES) & 1);
-      mbar_wait(bar_s_free + 8 * b, ((it >> 1) & 1) ^ 1);
+    auto issue_s = [&](int it, int i, bool last_tile) {  // S_i(it) = Q_i K_it^T into SP_i
+      const int st = it % STAGES;
+      if (i == 0) mbar_wait(bar_k_full + 8 * st, (it / STAGES) & 1);
       tc_fence_after();
       if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
           const uint32_t off = (uint32_t)((k >> 2) * SM::HALF_BYTES + (k & 3) * 32);
-          tc_mma_f16(tb + TM_S + b * BK, make_smem_desc(sm_q + off), make_smem_desc(sm_k + st * SM::KV_BYTES + off), idesc_s,
-                     k == 0 ? 0u : 1u);
+          tc_mma_f16(tb + TM_SP + i * BK, make_smem_desc(sm_q + i * SM::Q_BYTES + off),
+                     make_smem_desc(sm_k + st * SM::KV_BYTES + off), idesc_s, k == 0 ? 0u : 1u);
         }
-        tc_commit(bar_k_empty + 8 * st);
-        tc_commit(bar_s_full + 8 * b);
+        if (last_tile) tc_commit(bar_k_empty + 8 * st);
+        tc_commit(bar_s_full + 8 * i);
       }
       __syncwarp();
     };
-    issue_s(0);
+    for (int i = 0; i < ntile; ++i) issue_s(0, i, i == ntile - 1);
     for (int it = 0; it < nblk; ++it) {
-      if (it + 1 < nblk) issue_s(it + 1);  // overlaps the softmax of block it
       const int st = it % STAGES;
-      mbar_wait(bar_p_full, it & 1);
-      mbar_wait(bar_v_full + 8 * st, (it / STAGES) & 1);
-      {
-        // V rows at positions >= seq_len are whatever the pool holds (another sequence's page, never-written
-        // memory): their P is 0, but 0 * NaN would poison O, so those rows are zeroed before the product
-        const int nvalid = seq_len - (j0 + it) * BK;
-        if (nvalid < BK) {
-          for (int idx = lane; idx < (BK - nvalid) * 8 * HALVES; idx += 32) {
-            const int row = nvalid + idx / (8 * HALVES), rem = idx % (8 * HALVES);
-            asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(sm_v + st * SM::KV_BYTES + (rem >> 3) * SM::HALF_BYTES +
-                                                                       row * 128 + (rem & 7) * 16), "r"(0u) : "memory");
+      for (int i = 0; i < ntile; ++i) {
+        mbar_wait(bar_p_full + 8 * i, it & 1);
+        if (i == 0) {
+          mbar_wait(bar_v_full + 8 * st, (it / STAGES) & 1);
+          // V rows at positions >= seq_len are whatever the pool holds (another sequence's page, never-written
+          // memory): their P is 0, but 0 * NaN would poison O, so those rows are zeroed before the product
+          const int nvalid = seq_len - (j0 + it) * BK;
+          if (nvalid < BK) {
+            for (int idx = lane; idx < (BK - nvalid) * 8 * HALVES; idx += 32) {
+              const int row = nvalid + idx / (8 * HALVES), rem = idx % (8 * HALVES);
+              asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(sm_v + st * SM::KV_BYTES + (rem >> 3) * SM::HALF_BYTES +
+                                                                         row * 128 + (rem & 7) * 16), "r"(0u) : "memory");
+            }
+            fence_proxy_async();
+            __syncwarp();
           }
-          fence_proxy_async();
-          __syncwarp();
         }
-      }
-      tc_fence_after();
-      if (elect_one()) {
+        tc_fence_after();
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint64_t dv = make_smem_desc_mn(sm_v + st * SM::KV_BYTES + k * 16 * 128, SM::HALF_BYTES, 1024);
-          tc_mma_f16_ts(tb + TM_O, tb + TM_P + 8 * k, dv, idesc_o, (it | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t dv = make_smem_desc_mn(sm_v + st * SM::KV_BYTES + k * 16 * 128, SM::HALF_BYTES, 1024);
+            tc_mma_f16_ts(tb + TM_O + i * D, tb + TM_SP + i * BK + 8 * k, dv, idesc_o, (it | k) != 0 ? 1u : 0u);
+          }
+          if (i == ntile - 1) tc_commit(bar_v_empty + 8 * st);
+          tc_commit(bar_o_full + 8 * i);
         }
-        tc_commit(bar_v_empty + 8 * st);
-        tc_commit(bar_o_full);
+        __syncwarp();
+        if (it + 1 < nblk) issue_s(it + 1, i, i == ntile - 1);  // overwrites P_i(it): ordered after PV_i(it) by issue order
       }
-      __syncwarp();
     }
   } else {
-    // ===== softmax / correction / epilogue: thread <-> query row =====
-    const int r = (warp & 3) * 32 + lane;
-    const uint32_t lane_addr = ((uint32_t)((warp & 3) * 32) << 16);
-    const int qabs = qabs0 + r;
-    // this row sees KV positions [row_lo, row_hi); rows past the tile's valid rows see nothing
-    const int row_hi = r < nrows ? min(seq_len, qabs + 1) : 0;
-    const int row_lo = p.sliding_window >= 0 ? max(0, qabs + 1 - p.sliding_window) : 0;
-    const float sc = p.scale * kLog2e;
-    const float cap_in = SOFTCAP ? p.scale / p.softcap : 0.f, cap_out = SOFTCAP ? p.softcap * kLog2e : 0.f;  // tanh(s*scale/c)*c
-    (void)cap_in; (void)cap_out;
-    float m_used = -INFINITY, m_true = -INFINITY, l = 0.f;
-    for (int it = 0; it < nblk; ++it) {
-      const int b = it & 1;
-      mbar_wait(bar_s_full + 8 * b, (it >> 1) & 1);
-      tc_fence_after();
-      float s[BK];
-#pragma unroll
-      for (int c0 = 0; c0 < BK; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld<32>(tmem_base + lane_addr + TM_S + b * BK + c0, v);
-#pragma unroll
-        for (int q = 0; q < 32; ++q) s[c0 + q] = __uint_as_float(v[q]);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_s_free + 8 * b);
-      const int kv0 = (j0 + it) * BK;
-      float m_blk = -INFINITY;
-      // blocks wholly inside every row's [row_lo, row_hi) of this warp need no mask (the common case away from
-      // the causal diagonal and the window edge)
-      const bool need_mask = __any_sync(0xffffffffu, kv0 < row_lo || kv0 + BK > row_hi);
-      if (need_mask) {
-#pragma unroll
-        for (int c = 0; c < BK; ++c) {
-          float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out : s[c] * sc;
-          const int kv = kv0 + c;
-          x = (kv >= row_lo && kv < row_hi) ? x : -INFINITY;
-          s[c] = x;
-          m_blk = fmaxf(m_blk, x);
-        }
-      } else {
-#pragma unroll
-        for (int c = 0; c < BK; ++c) {
-          const float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out : s[c] * sc;
-          s[c] = x;
-          m_blk = fmaxf(m_blk, x);
-        }
-      }
-      m_true = fmaxf(m_true, m_blk);
-      const float m_new = (m_blk > m_used + kRescaleThreshold) ? m_blk : m_used;
-      const float alpha = (m_used == -INFINITY) ? 0.f : ex2(m_used - m_new);
-      const float m_eff = (m_new == -INFINITY) ? 0.f : m_new;
-      float sum = 0.f;
-      uint32_t pk[BK / 2];
-#pragma unroll
-      for (int c = 0; c < BK; c += 2) {
-        const float p0 = ex2(s[c] - m_eff), p1 = ex2(s[c + 1] - m_eff);
-        sum += p0 + p1;
-        pk[c >> 1] = pack2(p0, p1, p.is_fp16);
-      }
-      l = l * alpha + sum;
-      // P and O belong to the PV product of the previous block until it has completed
-      if (it > 0) {
-        mbar_wait(bar_o_full, (it - 1) & 1);
+    // ===== softmax / correction / epilogue: warps 2..5 own Q tile 0, warps 6..9 Q tile 1; thread <-> query row =====
+    const int ti = (warp - 2) >> 2;
+    if (ti == 0 || two) {
+      const int r = (warp & 3) * 32 + lane;
+      const uint32_t lane_addr = ((uint32_t)((warp & 3) * 32) << 16);
+      const int nrows = min(BQ, nrows_all - ti * BQ);
+      const int qabs = qabs0 + ti * BQ + r;
+      // this row sees KV positions [row_lo, row_hi); rows past the tile's valid rows see nothing
+      const int row_hi = r < nrows ? min(seq_len, qabs + 1) : 0;
+      const int row_lo = p.sliding_window >= 0 ? max(0, qabs + 1 - p.sliding_window) : 0;
+      const float sc = p.scale * kLog2e;
+      const float cap_in = SOFTCAP ? p.scale / p.softcap : 0.f, cap_out = SOFTCAP ? p.softcap * kLog2e : 0.f;  // tanh(s*scale/c)*c
+      (void)cap_in; (void)cap_out;
+      const uint32_t t_sp = tmem_base + lane_addr + TM_SP + ti * BK, t_o = tmem_base + lane_addr + TM_O + ti * D;
+      float m_used = -INFINITY, m_true = -INFINITY, l = 0.f;
+      for (int it = 0; it < nblk; ++it) {
+        mbar_wait(bar_s_full + 8 * ti, it & 1);
         tc_fence_after();
-        if (__any_sync(0xffffffffu, m_new != m_used)) {
+        float s[BK];
 #pragma unroll
-          for (int c0 = 0; c0 < D; c0 += 32) {
-            uint32_t v[32];
-            tmem_ld<32>(tmem_base + lane_addr + TM_O + c0, v);
+        for (int c0 = 0; c0 < BK; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld<32>(t_sp + c0, v);
 #pragma unroll
-            for (int q = 0; q < 32; ++q) v[q] = __float_as_uint(__uint_as_float(v[q]) * alpha);
-            tmem_st32(tmem_base + lane_addr + TM_O + c0, v);
-          }
+          for (int q = 0; q < 32; ++q) s[c0 + q] = __uint_as_float(v[q]);
         }
-      }
-      m_used = m_new;
-      tmem_st32(tmem_base + lane_addr + TM_P, pk);
-      tmem_st32(tmem_base + lane_addr + TM_P + 32, pk + 32);
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_p_full);
-    }
-    // ---- epilogue: sink fold (pagedattention_tiled.metal sinks, pagedattention.metal:1318-1328), normalise, store
-    mbar_wait(bar_o_full, (nblk - 1) & 1);
-    tc_fence_after();
-    // everything is relative to m_used; the reference's l is relative to m_true (or to max(m_true, sink))
-    float m_fin = m_true;
-    float sink_term = 0.f;
-    if (p.sinks != nullptr) {
-      const float sk = p.sinks[h] * kLog2e;
-      m_fin = fmaxf(m_fin, sk);
-      sink_term = ex2(sk - m_fin);
-    }
-    const float f = (m_used == -INFINITY) ? 0.f : ex2(m_used - m_fin);
-    const float inv = 1.f / (l * f + sink_term + 1e-6f);
-    const float oscale = f * inv;
-    uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + (int64_t)(q_start + row0 + r) * p.out_stride + (int64_t)h * D;
-    const bool vec_ok = (p.out_stride % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+        const int kv0 = (j0 + it) * BK;
+        float m_blk = -INFINITY;
+        // blocks wholly inside every row's [row_lo, row_hi) of this warp need no mask (the common case away from
+        // the causal diagonal and the window edge)
+        const bool need_mask = __any_sync(0xffffffffu, kv0 < row_lo || kv0 + BK > row_hi);
+        if (need_mask) {
 #pragma unroll
-    for (int c0 = 0; c0 < D; c0 += 32) {
-      uint32_t v[32];
-      tmem_ld<32>(tmem_base + lane_addr + TM_O + c0, v);
-      if (r < nrows && row_hi > 0) {
-        uint32_t o[16];
-#pragma unroll
-        for (int q = 0; q < 16; ++q)
-          o[q] = pack2(__uint_as_float(v[2 * q]) * oscale, __uint_as_float(v[2 * q + 1]) * oscale, p.is_fp16);
-        if (vec_ok) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q)
-            *reinterpret_cast<uint4*>(orow + c0 + 8 * q) = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+          for (int c = 0; c < BK; ++c) {
+            float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out : s[c] * sc;
+            const int kv = kv0 + c;
+            x = (kv >= row_lo && kv < row_hi) ? x : -INFINITY;
+            s[c] = x;
+            m_blk = fmaxf(m_blk, x);
+          }
         } else {
 #pragma unroll
-          for (int q = 0; q < 16; ++q) *reinterpret_cast<uint32_t*>(orow + c0 + 2 * q) = o[q];
+          for (int c = 0; c < BK; ++c) {
+            const float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out : s[c] * sc;
+            s[c] = x;
+            m_blk = fmaxf(m_blk, x);
+          }
+        }
+        m_true = fmaxf(m_true, m_blk);
+        const float m_new = (m_blk > m_used + kRescaleThreshold) ? m_blk : m_used;
+        const float alpha = (m_used == -INFINITY) ? 0.f : ex2(m_used - m_new);
+        const float m_eff = (m_new == -INFINITY) ? 0.f : m_new;
+        float sum = 0.f;
+        uint32_t pk[BK / 2];
+#pragma unroll
+        for (int c = 0; c < BK; c += 2) {
+          const float p0 = ex2(s[c] - m_eff), p1 = ex2(s[c + 1] - m_eff);
+          sum += p0 + p1;
+          pk[c >> 1] = pack2(p0, p1, p.is_fp16);
+        }
+        l = l * alpha + sum;
+        // O_i belongs to PV_i of the previous block until that has completed (it had: S_i(it) was issued after it)
+        if (it > 0) {
+          mbar_wait(bar_o_full + 8 * ti, (it - 1) & 1);
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, m_new != m_used)) {
+#pragma unroll
+            for (int c0 = 0; c0 < D; c0 += 32) {
+              uint32_t v[32];
+              tmem_ld<32>(t_o + c0, v);
+#pragma unroll
+              for (int q = 0; q < 32; ++q) v[q] = __float_as_uint(__uint_as_float(v[q]) * alpha);
+              tmem_st32(t_o + c0, v);
+            }
+          }
+        }
+        m_used = m_new;
+        tmem_st32(t_sp, pk);        // P_i over the first half of S_i's columns (every thread has read its S row)
+        tmem_st32(t_sp + 32, pk + 32);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_p_full + 8 * ti);
+      }
+      // ---- epilogue: sink fold (pagedattention_tiled.metal sinks, pagedattention.metal:1318-1328), normalise, store
+      mbar_wait(bar_o_full + 8 * ti, (nblk - 1) & 1);
+      tc_fence_after();
+      // everything is relative to m_used; the reference's l is relative to m_true (or to max(m_true, sink))
+      float m_fin = m_true;
+      float sink_term = 0.f;
+      if (p.sinks != nullptr) {
+        const float sk = p.sinks[h] * kLog2e;
+        m_fin = fmaxf(m_fin, sk);
+        sink_term = ex2(sk - m_fin);
+      }
+      const float f = (m_used == -INFINITY) ? 0.f : ex2(m_used - m_fin);
+      const float inv = 1.f / (l * f + sink_term + 1e-6f);
+      const float oscale = f * inv;
+      uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + (int64_t)(q_start + row0 + ti * BQ + r) * p.out_stride + (int64_t)h * D;
+      const bool vec_ok = (p.out_stride % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+#pragma unroll
+      for (int c0 = 0; c0 < D; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld<32>(t_o + c0, v);
+        if (r < nrows && row_hi > 0) {
+          uint32_t o[16];
+#pragma unroll
+          for (int q = 0; q < 16; ++q)
+            o[q] = pack2(__uint_as_float(v[2 * q]) * oscale, __uint_as_float(v[2 * q + 1]) * oscale, p.is_fp16);
+          if (vec_ok) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              *reinterpret_cast<uint4*>(orow + c0 + 8 * q) = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+          } else {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) *reinterpret_cast<uint32_t*>(orow + c0 + 2 * q) = o[q];
+          }
         }
       }
     }
@@ -453,7 +462,7 @@ static int launch(const b200_paged_attn_args& a, int min_qlen, cudaStream_t st) 
   p.softcap = a.softcap;
   p.is_fp16 = a.dtype == B200_F16 ? 1 : 0;
   // upper bound on Q tiles: every sequence adds at most one partial tile (reference grid T/BQ + S)
-  dim3 grid((unsigned)(a.num_q_tokens / BQ + a.num_seqs), (unsigned)a.num_q_heads);
+  dim3 grid((unsigned)(a.num_q_tokens / BQ2 + a.num_seqs), (unsigned)a.num_q_heads);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(THREADS);
