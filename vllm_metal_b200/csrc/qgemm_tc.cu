@@ -111,13 +111,20 @@ __device__ __forceinline__ uint4 dequant_word4(uint32_t w, typename Cvt<T>::T2 s
   }
   return o;
 }
-// 4 bytes of one packed word -> 4 values (fp32 fma, then one rounding to T).
+// 4 bytes of one packed word -> 4 fp16 values s*q+b: a byte under the exponent byte 0x64 reads 1024 + q exactly
+// (q < 1024), the subtraction is exact and the FMA rounds once -- the same single rounding as an fp32 fma followed
+// by a conversion, in 2 PRMT + 2 HADD2 + 2 HFMA2 instead of 4 I2F + 4 FFMA + 2 F2F per word (the int8 GEMM at
+// M >= 256 was dequant-bound on the conversions: 0.28-0.47 of the bf16 peak, profiles/r02_gemm_bigm.txt).
 template <typename T>
 __device__ __forceinline__ uint2 dequant_word8(uint32_t w, float s, float b) {
-  using C = Cvt<T>;
+  const __half2 s2 = __float2half2_rn(s), b2 = __float2half2_rn(b), off = __float2half2_rn(-1024.f);
+  const uint32_t lo = __byte_perm(w, 0x64646464u, 0x5140), hi = __byte_perm(w, 0x64646464u, 0x7362);
+  const __half2 q0 = __hadd2(*reinterpret_cast<const __half2*>(&lo), off);
+  const __half2 q1 = __hadd2(*reinterpret_cast<const __half2*>(&hi), off);
+  const __half2 r0 = __hfma2(s2, q0, b2), r1 = __hfma2(s2, q1, b2);
   uint2 o;
-  o.x = C::f2(fmaf(s, (float)(w & 0xFFu), b), fmaf(s, (float)((w >> 8) & 0xFFu), b));
-  o.y = C::f2(fmaf(s, (float)((w >> 16) & 0xFFu), b), fmaf(s, (float)(w >> 24), b));
+  o.x = *reinterpret_cast<const uint32_t*>(&r0);
+  o.y = *reinterpret_cast<const uint32_t*>(&r1);
   return o;
 }
 
