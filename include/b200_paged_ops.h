@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 1
+#define B200_ABI_VERSION 2
 
 /* Element types of activations / caches (reference: dtype_to_metal,
  * paged_ops.cpp:185-196 -- float, half, bfloat16 are the supported set). */
@@ -159,6 +159,8 @@ typedef struct b200_paged_attn_args {
   int64_t num_blocks;
   float scale;
   float softcap;
+  int32_t out_dtype; /* 0 or `dtype`: out has the query dtype; B200_F16 with dtype = B200_BF16: the bf16-rounded
+                        result is stored as fp16 (feeds the fp16-operand o_proj without a cast launch) */
 } b200_paged_attn_args;
 
 size_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args* args);

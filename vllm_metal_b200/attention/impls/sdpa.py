@@ -219,7 +219,13 @@ def sdpa_forward(
         k_cache = k_cache.reshape(-1, meta.block_size, kvh, d)
         v_cache = v_cache.reshape(-1, meta.block_size, kvh, d)
 
-    out = torch.empty((t, n_heads, cache_hd), dtype=q.dtype, device=q.device)
+    # fp16 output straight from the attention kernels when o_proj runs a tensor-core kernel (fp16 operands) and
+    # nothing sits in between: the same bf16-rounded values, no cast launch
+    o_proj = inner.o_proj
+    plain_tail = hd == cache_hd and gate is None and not (getattr(inner, "gating", False) and hasattr(inner, "g_proj"))
+    f16_out = plain_tail and q.dtype == torch.bfloat16 and (
+        getattr(o_proj, "weight_blob", None) is not None or getattr(o_proj, "weight_tc", None) is not None)
+    out = torch.empty((t, n_heads, cache_hd), dtype=torch.float16 if f16_out else q.dtype, device=q.device)
     ops.paged_attention_primitive(
         q, k_cache, v_cache, kv_cache.kv_heads_per_layer[layer_idx], float(scale), 0.0,
         meta.block_tables, meta.seq_lens, meta.cu_seqlens_q, meta.block_size, meta.max_seq_len,

@@ -16,7 +16,17 @@ struct SplitWorkspace {
   int num_partitions;  // P
   int partition_size;  // tokens
   int skip_qlen;       // > 0: rows of sequences with q_len >= skip_qlen belong to the tile kernel (left untouched here)
+  int out_f16;         // bf16 call whose `out` buffer is fp16: store the bf16-rounded value as fp16 (args.out_dtype)
 };
+
+// One output element: rounded to the call's dtype T; with out_f16 (T = bf16) that value is stored as fp16 -- exact
+// below 65504 -- so the o_proj that follows (fp16 tensor-core operands) needs no cast launch.
+template <typename T>
+__device__ __forceinline__ void store_out(T* row, int d, float v, int out_f16) {
+  const T t = from_float<T>(v);
+  if (out_f16) reinterpret_cast<__half*>(row)[d] = __float2half_rn(fminf(fmaxf(to_float(t), -65504.f), 65504.f));
+  else row[d] = t;
+}
 
 inline size_t split_workspace_bytes(int64_t T, int64_t Hq, int64_t P, int64_t D) {
   return (size_t)(T * Hq * P * (D + 2)) * sizeof(float);
@@ -31,6 +41,7 @@ inline SplitWorkspace carve_workspace(void* ws, int64_t T, int64_t Hq, int64_t P
   w.num_partitions = (int)P;
   w.partition_size = partition_size;
   w.skip_qlen = 0;
+  w.out_f16 = 0;
   return w;
 }
 
@@ -75,6 +86,7 @@ __device__ __forceinline__ RowInfo row_info(const int32_t* __restrict__ cu,
 // Launchers implemented in paged_attention_generic.cu / paged_attention_decode.cu.
 // `ws == nullptr` => single pass.
 int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st, int skip_qlen = 0);
+inline int out_is_f16(const b200_paged_attn_args& a) { return a.out_dtype == B200_F16 && a.dtype == B200_BF16 ? 1 : 0; }
 bool decode_mma_supported(const b200_paged_attn_args& a);
 int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st, int skip_qlen = 0);
 int launch_split_reduce(const b200_paged_attn_args& a, const SplitWorkspace& ws, cudaStream_t st);

@@ -341,7 +341,7 @@ paged_decode_mma_kernel(const DecodeParams p) {
         L = L * c + exp2f(sk - M2);
       }
       T* op = reinterpret_cast<T*>(p.out) + (int64_t)t * p.out_stride + (int64_t)h * D;
-      op[d] = from_float<T>(acc * c / (L + 1e-6f));  // :1383
+      store_out<T>(op, d, acc * c / (L + 1e-6f), p.ws.out_f16);  // :1383
     }
   }
 }
@@ -412,6 +412,7 @@ int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, c
   p.ws = SplitWorkspace{};
   if (ws) p.ws = *ws;
   p.ws.skip_qlen = skip_qlen;
+  p.ws.out_f16 = out_is_f16(a);
   dim3 grid(a.num_kv_heads, a.num_q_tokens, ws ? ws->num_partitions : 1);
   if (a.dtype == B200_BF16) {
     if (a.head_dim == 128) return launch_one<__nv_bfloat16, 128, 3>(p, grid, st);

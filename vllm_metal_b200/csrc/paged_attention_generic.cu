@@ -147,7 +147,7 @@ paged_attention_generic_kernel(T* __restrict__ out, const T* __restrict__ query,
     float acc = 0.f;
 #pragma unroll
     for (int w = 0; w < kGenericWarps; ++w) acc += sm_o[w * head_dim + d] * wgt[w];
-    op[d] = from_float<T>(acc * inv);
+    store_out<T>(op, d, acc * inv, ws.out_f16);
   }
 }
 
@@ -191,7 +191,7 @@ split_reduce_kernel(T* __restrict__ out, const int32_t* __restrict__ seq_lens,
       const float mj = ws.max_l2[row + j];
       if (mj != -INFINITY) acc += ws.tmp_out[(row + j) * head_dim + d] * exp2f(mj - M);
     }
-    op[d] = from_float<T>(acc * inv);
+    store_out<T>(op, d, acc * inv, ws.out_f16);
   }
 }
 
@@ -207,6 +207,7 @@ int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cuda
   SplitWorkspace w{};
   if (ws) w = *ws;
   w.skip_qlen = skip_qlen;
+  w.out_f16 = out_is_f16(a);
   dim3 grid(a.num_q_heads, a.num_q_tokens, ws ? ws->num_partitions : 1);
   return B200_DISPATCH_DTYPE(a.dtype, T, [&]() -> int {
     launch_pdl(paged_attention_generic_kernel<T>, dim3(grid), dim3(kGenericWarps * 32), smem, st, 
@@ -250,6 +251,8 @@ static int validate(const b200_paged_attn_args* a) {
   B200_CHECK_ARG(a->dtype == B200_F32 || a->dtype == B200_F16 || a->dtype == B200_BF16,
                  "paged_attention: unsupported dtype code %d", a->dtype);
   B200_CHECK_ARG(a->num_blocks > 0, "paged_attention: num_blocks must be > 0");
+  B200_CHECK_ARG(a->out_dtype == 0 || a->out_dtype == a->dtype || (a->out_dtype == B200_F16 && a->dtype == B200_BF16),
+                 "paged_attention: out_dtype must be 0 / the query dtype, or fp16 for a bf16 call");
   return B200_OK;
 }
 
@@ -405,7 +408,10 @@ extern "C" int b200_paged_attention(const b200_paged_attn_args* a, void* stream)
     }
   }
   const SplitWorkspace* wsp = parts > 1 ? &ws : nullptr;
-  if (wsp) ws.skip_qlen = skip_qlen;
+  if (wsp) {
+    ws.skip_qlen = skip_qlen;
+    ws.out_f16 = out_is_f16(*a);
+  }
   rc = mma ? launch_decode_mma(*a, wsp, st, skip_qlen) : launch_generic(*a, wsp, st, skip_qlen);
   if (rc != B200_OK) return rc;
   if (wsp) rc = launch_split_reduce(*a, ws, st);

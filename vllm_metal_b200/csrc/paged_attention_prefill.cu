@@ -43,6 +43,7 @@ struct Params {
   int64_t out_stride;
   float scale, softcap;
   int is_fp16;
+  int out_f16;  // bf16 call storing its (bf16-rounded) output as fp16
 };
 
 // MN-major SWIZZLE_128B operand (cute::UMMA canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units):
@@ -396,8 +397,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
         if (r < nrows && row_hi > 0) {
           uint32_t o[16];
 #pragma unroll
-          for (int q = 0; q < 16; ++q)
+          for (int q = 0; q < 16; ++q) {
             o[q] = pack2(__uint_as_float(v[2 * q]) * oscale, __uint_as_float(v[2 * q + 1]) * oscale, p.is_fp16);
+            if (p.out_f16) {  // the bf16 pair, re-stored as fp16 (exact below 65504)
+              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&o[q]));
+              o[q] = pack2(fminf(fmaxf(f.x, -65504.f), 65504.f), fminf(fmaxf(f.y, -65504.f), 65504.f), 1);
+            }
+          }
           if (vec_ok) {
 #pragma unroll
             for (int q = 0; q < 4; ++q)
@@ -461,6 +467,7 @@ static int launch(const b200_paged_attn_args& a, int min_qlen, cudaStream_t st) 
   p.scale = a.scale;
   p.softcap = a.softcap;
   p.is_fp16 = a.dtype == B200_F16 ? 1 : 0;
+  p.out_f16 = out_is_f16(a);
   // upper bound on Q tiles: every sequence adds at most one partial tile (reference grid T/BQ + S)
   dim3 grid((unsigned)(a.num_q_tokens / BQ2 + a.num_seqs), (unsigned)a.num_q_heads);
   cudaLaunchConfig_t cfg{};

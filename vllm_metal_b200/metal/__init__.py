@@ -75,6 +75,7 @@ class PagedAttnArgs(ctypes.Structure):
         ("num_blocks", ctypes.c_int64),
         ("scale", ctypes.c_float),
         ("softcap", ctypes.c_float),
+        ("out_dtype", ctypes.c_int32),
     ]
 
 
@@ -374,7 +375,8 @@ class _Ops:
             raise ValueError("key_cache/value_cache must both be [num_blocks, block_size, H_kv, D]")
         if query.dtype != key_cache.dtype or value_cache.dtype != key_cache.dtype:
             raise ValueError("query and the KV caches must share one dtype (sdpa.py:542-544 casts q/k/v to it)")
-        if out.shape != query.shape or out.dtype != query.dtype:
+        f16_out = out.dtype == torch.float16 and query.dtype == torch.bfloat16  # B200 extension: feeds the fp16-operand o_proj
+        if out.shape != query.shape or (out.dtype != query.dtype and not f16_out):
             raise ValueError("out must have the shape and dtype of query (paged_ops.cpp:918-920)")
         t_total, h_q, d = query.shape
         nb, cbs, h_kv, d_c = key_cache.shape
@@ -416,6 +418,7 @@ class _Ops:
         a.kv_block_stride, a.kv_token_stride, a.kv_head_stride = key_cache.stride()[:3]
         a.num_blocks = nb
         a.scale, a.softcap = float(scale), float(softcap)
+        a.out_dtype = _dtype_code("out", out)
         need = self._lib.b200_paged_attention_workspace_bytes(ctypes.byref(a))
         ws = self._workspace(query.device, need)
         a.workspace = _ptr(ws)
