@@ -327,10 +327,14 @@ def test_full_size_decode_properties(ops):
 @pytest.mark.parametrize("kernel,fp", [(0, 0), (GENERIC, 1), (MMA, 1), (MMA, 2), (3, 0)])
 def test_fp16_output_of_a_bf16_call_is_the_same_values(ops, kernel, fp):
     """args.out_dtype = fp16 on a bf16 call (every kernel: generic, tensor-core decode single pass / split +
-    merge, tcgen05 tile): the bf16-rounded result stored as fp16, bit for bit the bf16 output's values."""
+    merge, tcgen05 tile): the bf16-rounded result stored as fp16 -- the bf16 output's values exactly, except that
+    magnitudes below fp16's smallest subnormal (2^-24) round to it or to zero."""
     seqs = [(1, 700), (1, 33)] if kernel != 3 else [(140, 300), (20, 20)]
     c = make_paged_case(seqs, 8, 2, 128, 16, "bfloat16", seed=11, sinks=True)
     ref = run_attention(ops, c, force_partitions=fp, kernel=kernel)
     out16 = torch.zeros(c["q"].shape, dtype=torch.float16, device="cuda")
     got = run_attention(ops, c, force_partitions=fp, kernel=kernel, out=out16)
-    assert got.dtype == torch.float16 and torch.equal(got.float(), ref.float())
+    assert got.dtype == torch.float16
+    diff = (got.float() - ref.float()).abs()
+    assert diff.max().item() <= 2.0 ** -24
+    assert torch.equal(got.float()[ref.float().abs() >= 2.0 ** -14], ref.float()[ref.float().abs() >= 2.0 ** -14])
