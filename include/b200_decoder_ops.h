@@ -103,11 +103,14 @@ int b200_allreduce_sum(void* x, int64_t numel, int dtype, void* const* symm_ptrs
 /* Fused tensor-parallel epilogue of a decoder sub-block: s = all-reduce(x) (as above, x [rows, hidden] contiguous,
  * left untouched), residual += s (in place, rounded to dtype), out = rms_norm(residual) * weight -- bit-identical
  * to b200_allreduce_sum followed by b200_rms_norm(x, residual, ...), in one launch.  Shares buffers, flags and
- * epochs with b200_allreduce_sum (same `grid`); hidden % 8 == 0, hidden <= 8192; out_dtype as in b200_rms_norm. */
+ * epochs with b200_allreduce_sum (same `grid`); hidden % 8 == 0, hidden <= 8192; out_dtype as in b200_rms_norm.
+ * twoshot != 0: row r is reduced + normed on rank r % world only and the results are gathered (less NVLink traffic,
+ * one more flag exchange; same bits): the staging buffers must then be 6 * half_bytes (2 halves of partials + 2 x 2
+ * halves of results) and the flag arrays 2 * grid * world. */
 int b200_allreduce_add_rmsnorm(void* x, void* residual, const void* weight, void* out, int rows, int hidden,
                                float eps, int dtype, int out_dtype, void* const* symm_ptrs,
                                void* const* flag_ptrs, void* epoch, int rank, int world,
-                               int64_t half_bytes, int grid, void* stream);
+                               int64_t half_bytes, int grid, int twoshot, void* stream);
 
 #ifdef __cplusplus
 }

@@ -121,9 +121,16 @@ def main() -> None:
         want = ops.rms_norm(s_, w, 1e-5, residual=res_ref, out_dtype=odt if hidden >= 512 else None)
         for _ in range(2):
             res = res0.clone()
-            got = ar.fused_add_rmsnorm(part.clone(), res, w, 1e-5, odt)
+            got = ar.fused_add_rmsnorm(part.clone(), res, w, 1e-5, odt, twoshot=False)
+        for _ in range(3):  # owner-reduces-and-gathers form: same bits as the one-shot form, on every rank
+            res2 = res0.clone()
+            got2 = ar.fused_add_rmsnorm(part.clone(), res2, w, 1e-5, odt, twoshot=True)
         torch.cuda.synchronize()
-        assert got is not None, (rows, hidden)
+        assert got is not None and got2 is not None, (rows, hidden)
+        if not (torch.equal(got2, got) and torch.equal(res2, res)):
+            ok = False
+            print(f"[rank {rank}] two-shot fused add+norm differs from one-shot rows={rows} hidden={hidden}: out max diff "
+                  f"{(got2.float() - got.float()).abs().max().item()}, residual equal {torch.equal(res2, res)}", flush=True)
         same_map = hidden in (4096, 8192)
         good = torch.equal(res, res_ref) and (torch.equal(got, want) if same_map else
                                                bool((got.float() - want.float()).abs().max() <= 2.0 ** -6 * want.float().abs().max()))
@@ -134,7 +141,10 @@ def main() -> None:
     parts = [x0.clone() for _ in range(16)]
     resid = x0.clone()
     wn = torch.ones((4096,), device=dev).bfloat16()
-    timed(lambda t: ar.fused_add_rmsnorm(t, resid, wn, 1e-5, torch.float16), "nvlink one-shot fused with residual add + RMSNorm")
+    timed(lambda t: ar.fused_add_rmsnorm(t, resid, wn, 1e-5, torch.float16, twoshot=False),
+          "nvlink one-shot fused with residual add + RMSNorm")
+    timed(lambda t: ar.fused_add_rmsnorm(t, resid, wn, 1e-5, torch.float16, twoshot=True),
+          "nvlink two-shot (owner reduces + norms, results gathered) fused with residual add + RMSNorm")
 
     def two_step(t):
         ar(t)

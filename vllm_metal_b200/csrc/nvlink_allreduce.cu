@@ -145,6 +145,7 @@ struct FusedParams {
   int rows, hidden;
   float eps;
   int out_f16;
+  int twoshot;  // rows are reduced + normed by their OWNER rank (row % world) only and the results gathered
 };
 
 __device__ __forceinline__ float block_sum_512(float v, float* red) {
@@ -158,7 +159,14 @@ __device__ __forceinline__ float block_sum_512(float v, float* red) {
   return t;
 }
 
-template <typename T, int WORLD>
+// TWOSHOT (8 ranks): the one-shot form makes every rank pull every row from 7 peers (3.5 MiB in per call at the
+// headline shape) and norm all 64 rows 8 times over.  Here row r belongs to rank r % WORLD: the owner gathers it,
+// adds, norms and publishes the new residual row and the normalised row in a second staging area; after a second
+// flag exchange everybody copies the rows it does not own from their owners (0.45 + 0.9 MiB in).  Same arithmetic
+// on the owner, plain copies elsewhere: bit-identical to the one-shot form on every rank.
+// Staging per rank: [2 parities][half_bytes] partials | [2 parities][2: residual, out][half_bytes] results;
+// flags: [grid][world] exchange 1 | [grid][world] exchange 2.
+template <typename T, int WORLD, bool TWOSHOT>
 __global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_kernel(const FusedParams f) {
   pdl_trigger();
   pdl_wait();
@@ -190,7 +198,11 @@ __global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_kernel(const F
   uint4* rv = reinterpret_cast<uint4*>(f.residual);
   uint4* ov = reinterpret_cast<uint4*>(f.out);
   const uint4* wv = reinterpret_cast<const uint4*>(f.weight);
+  const int64_t res_off = 2 * p.half_bytes + (int64_t)(e & 1u) * 2 * p.half_bytes;  // this call's result area
+  uint4* my_h = reinterpret_cast<uint4*>(p.symm[p.rank] + res_off);
+  uint4* my_o = reinterpret_cast<uint4*>(p.symm[p.rank] + res_off + p.half_bytes);
   for (int r = b; r < f.rows; r += G) {
+    if (TWOSHOT && (r % WORLD) != p.rank) continue;
     float h[NV][8];
     float ss = 0.f;
 #pragma unroll
@@ -219,6 +231,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_kernel(const F
           ss += h[j][i] * h[j][i];
         }
         rv[idx] = hn;
+        if (TWOSHOT) my_h[idx] = hn;
       }
     }
     ss = block_sum_512(ss, red);
@@ -244,6 +257,34 @@ __global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_kernel(const F
           for (int i = 0; i < 8; ++i) hh[i] = __float2half_rn(fminf(fmaxf(to_float(ce[i]), -65504.f), 65504.f));
         }
         ov[(int64_t)r * nvec + v] = c;
+        if (TWOSHOT) my_o[(int64_t)r * nvec + v] = c;
+      }
+    }
+  }
+  if constexpr (TWOSHOT) {
+    __syncthreads();
+    // 5. second exchange: my owned rows of this CTA's slice are published
+    if (threadIdx.x < WORLD && (int)threadIdx.x != p.rank) {
+      const int peer = threadIdx.x;
+      st_release_sys(p.flags[peer] + (size_t)(G + b) * WORLD + p.rank, e);
+      const uint32_t* slot = p.flags[p.rank] + (size_t)(G + b) * WORLD + peer;
+      uint32_t spins = 0;
+      while ((int32_t)(ld_acquire_sys(slot) - e) < 0) {
+        if (++spins > (1u << 27)) __trap();
+      }
+    }
+    __syncthreads();
+    // 6. copy the rows other ranks own
+    for (int r = b; r < f.rows; r += G) {
+      const int owner = r % WORLD;
+      if (owner == p.rank) continue;
+      const uint4* oh = reinterpret_cast<const uint4*>(p.symm[owner] + res_off);
+      const uint4* oo = reinterpret_cast<const uint4*>(p.symm[owner] + res_off + p.half_bytes);
+      for (int v = threadIdx.x; v < nvec; v += kThreads) {
+        const int64_t idx = (int64_t)r * nvec + v;
+        const uint4 a = ld_peer_u4(oh + idx), c = ld_peer_u4(oo + idx);
+        rv[idx] = a;
+        ov[idx] = c;
       }
     }
   }
@@ -254,9 +295,18 @@ __global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_kernel(const F
 template <typename T>
 static int launch_fused(const FusedParams& f, int grid, cudaStream_t st) {
   switch (f.ar.world) {
-    case 2: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 2>, dim3(grid), dim3(kThreads), 0, st, f)); break;
-    case 4: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 4>, dim3(grid), dim3(kThreads), 0, st, f)); break;
-    case 8: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 8>, dim3(grid), dim3(kThreads), 0, st, f)); break;
+    case 2:
+      if (f.twoshot) B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 2, true>, dim3(grid), dim3(kThreads), 0, st, f));
+      else B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 2, false>, dim3(grid), dim3(kThreads), 0, st, f));
+      break;
+    case 4:
+      if (f.twoshot) B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 4, true>, dim3(grid), dim3(kThreads), 0, st, f));
+      else B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 4, false>, dim3(grid), dim3(kThreads), 0, st, f));
+      break;
+    case 8:
+      if (f.twoshot) B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 8, true>, dim3(grid), dim3(kThreads), 0, st, f));
+      else B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_kernel<T, 8, false>, dim3(grid), dim3(kThreads), 0, st, f));
+      break;
     default: return set_error(B200_ERR_INVALID_ARGUMENT, "allreduce: world size must be 2, 4 or 8, got %d", f.ar.world);
   }
   return check_launch("allreduce_add_rmsnorm_kernel");
@@ -331,7 +381,7 @@ int b200_allreduce_sum(void* x, int64_t numel, int dtype, void* const* symm_ptrs
 
 int b200_allreduce_add_rmsnorm(void* x, void* residual, const void* weight, void* out, int rows, int hidden, float eps,
                                int dtype, int out_dtype, void* const* symm_ptrs, void* const* flag_ptrs, void* epoch,
-                               int rank, int world, int64_t half_bytes, int grid, void* stream) {
+                               int rank, int world, int64_t half_bytes, int grid, int twoshot, void* stream) {
   using namespace b200;
   if (rows == 0) return B200_OK;
   B200_CHECK_ARG(x && residual && out && symm_ptrs && flag_ptrs && epoch && rows > 0, "allreduce_add_rmsnorm: bad arguments");
@@ -365,6 +415,7 @@ int b200_allreduce_add_rmsnorm(void* x, void* residual, const void* weight, void
   f.hidden = hidden;
   f.eps = eps;
   f.out_f16 = (out_dtype == B200_F16 && dtype == B200_BF16) ? 1 : 0;
+  f.twoshot = twoshot ? 1 : 0;
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_BF16) return ar::launch_fused<__nv_bfloat16>(f, grid, st);
   return ar::launch_fused<__half>(f, grid, st);

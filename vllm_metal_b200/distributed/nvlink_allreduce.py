@@ -10,6 +10,7 @@ raises if the CUDA library or peer access is unavailable.
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 import torch.distributed as dist
@@ -44,12 +45,17 @@ class NVLinkAllReduce:
                                                    ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_int, ctypes.c_int,
                                                    ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
                                                    ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int64,
-                                                   ctypes.c_int, ctypes.c_void_p]
+                                                   ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+        # fused all-reduce+norm: the owner-reduces-and-gathers (two-shot) form from this many ranks up.  Measured SLOWER at
+        # every size on one NVSwitch box (2 ranks 18.8 vs 11.4 us, 8 ranks 27.4 vs 23.8: the second flag exchange costs
+        # more than the 2.2 MiB of pulls it saves), so it is off by default (profiles/r02_allreduce_tp{2,8}.txt)
+        self.twoshot_from = int(os.environ.get("B200_ALLREDUCE_TWOSHOT_FROM", "16"))
         self.half_bytes = (int(max_bytes) + 255) // 256 * 256
         self.grid = int(grid)
         with torch.cuda.device(self.device):
-            self._own_symm, h_symm = self._alloc(2 * self.half_bytes)
-            self._own_flags, h_flags = self._alloc(self.grid * self.world * 4)
+            # [2 halves of partials][2 x 2 halves of two-shot results]; [grid][world] flags x 2 exchanges
+            self._own_symm, h_symm = self._alloc(6 * self.half_bytes)
+            self._own_flags, h_flags = self._alloc(2 * self.grid * self.world * 4)
             self.epoch = torch.zeros((self.grid,), dtype=torch.int32, device=self.device)
             handles: list = [None] * self.world
             dist.all_gather_object(handles, (h_symm, h_flags), group=group)
@@ -97,7 +103,7 @@ class NVLinkAllReduce:
         return x
 
     def fused_add_rmsnorm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor | None, eps: float,
-                          out_dtype: torch.dtype | None = None) -> torch.Tensor | None:
+                          out_dtype: torch.dtype | None = None, twoshot: bool | None = None) -> torch.Tensor | None:
         """``residual += allreduce(x); return rms_norm(residual) * weight`` in one kernel (x is left holding this
         rank's partial).  Returns ``None`` when the shape does not qualify -- the caller then runs the two-step
         sequence, which gives the same bits."""
@@ -115,7 +121,7 @@ class NVLinkAllReduce:
             x2.data_ptr(), r2.data_ptr(), None if weight is None else weight.data_ptr(), out.data_ptr(), x2.shape[0],
             hidden, float(eps), _DTYPE_CODE[x.dtype], _DTYPE_CODE[out.dtype], self._symm, self._flags,
             self.epoch.data_ptr(), self.rank, self.world, self.half_bytes, self.grid,
-            torch.cuda.current_stream().cuda_stream)
+            int(self.world >= self.twoshot_from if twoshot is None else twoshot), torch.cuda.current_stream().cuda_stream)
         self.ops._check(rc)
         self.ops.launches += 1
         self.calls += 1
