@@ -282,70 +282,77 @@ qgemm_tc_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant
   if (threadIdx.x == 0) trace_stamp(p, 1);  // setup done (barriers, TMEM)
 
   if (warp == W_TMA) {
-    // ===== packed-weight TMA producer =====
-    if (lane == 0) {
-      for (int ps = 0; ps < my_ps; ++ps) {
-        const int st = ps % PS;
-        if constexpr (SBT) {
-          // scale/bias stages sit on the GLOBAL grid of 8 groups (TMA needs the inner start
-          // coordinate 16-byte aligned); a cluster rank may start in the middle of one
-          const int gps = gps0 + ps;
-          if (ps == 0 || gps % SB_PER == 0) {
-            const int sbi = gps / SB_PER - gps0 / SB_PER, sst = sbi % SBS;
-            mbar_wait(bar_empty_sb + 8 * sst, ((sbi / SBS) & 1) ^ 1);
+    // ===== packed-weight TMA producer (whole-warp loop, issue under elect_one(): see tcgen05.cuh) =====
+    for (int ps = 0; ps < my_ps; ++ps) {
+      const int st = ps % PS;
+      if constexpr (SBT) {
+        // scale/bias stages sit on the GLOBAL grid of 8 groups (TMA needs the inner start
+        // coordinate 16-byte aligned); a cluster rank may start in the middle of one
+        const int gps = gps0 + ps;
+        if (ps == 0 || gps % SB_PER == 0) {
+          const int sbi = gps / SB_PER - gps0 / SB_PER, sst = sbi % SBS;
+          mbar_wait(bar_empty_sb + 8 * sst, ((sbi / SBS) & 1) ^ 1);
+          const int g0 = (gps / SB_PER) * 8;
+          if (elect_one()) {
             mbar_expect_tx(bar_full_sb + 8 * sst, SB_STAGE_BYTES);
-            const int g0 = (gps / SB_PER) * 8;
             tma_load_2d(sm_sb + sst * SB_STAGE_BYTES, &s_map, bar_full_sb + 8 * sst, g0, n0);
             tma_load_2d(sm_sb + sst * SB_STAGE_BYTES + ROWS * 16, &b_map, bar_full_sb + 8 * sst, g0, n0);
           }
+          __syncwarp();
         }
-        mbar_wait(bar_empty_p + 8 * st, ((ps / PS) & 1) ^ 1);
+      }
+      mbar_wait(bar_empty_p + 8 * st, ((ps / PS) & 1) ^ 1);
 #ifdef QGEMM_LOOP_TRACE
-        if (ps < 16) trace_stamp(p, 32 + ps);  // issue time of packed stage ps
+      if (lane == 0 && ps < 16) trace_stamp(p, 32 + ps);  // issue time of packed stage ps
 #endif
+      if (elect_one()) {
         mbar_expect_tx(bar_full_p + 8 * st, P_STAGE_BYTES);
         tma_load_2d(sm_p + st * P_STAGE_BYTES, &w_map, bar_full_p + 8 * st,
                     (kb_begin + ps * KB_PER_P) * (KB * BITS / 32), n0);
       }
+      __syncwarp();
     }
-    __syncwarp();
   } else if (warp == W_X) {
     // ===== x tile TMA producer =====
-    if (lane == 0) {
-      pdl_wait();  // x is the previous kernel's output
-      trace_stamp(p, 2);  // previous kernel complete
-      for (int kb = 0; kb < my_kb; ++kb) {
-        const int st = kb % NS;
-        mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
+    pdl_wait();  // x is the previous kernel's output
+    if (lane == 0) trace_stamp(p, 2);  // previous kernel complete
+    for (int kb = 0; kb < my_kb; ++kb) {
+      const int st = kb % NS;
+      mbar_wait(bar_empty_ab + 8 * st, ((kb / NS) & 1) ^ 1);
+      if (elect_one()) {
         mbar_expect_tx(bar_full_ab + 8 * st, B_STAGE_BYTES);
         tma_load_2d(sm_b + st * B_STAGE_BYTES, &x_map, bar_full_ab + 8 * st, (kb_begin + kb) * KB, m0);
       }
+      __syncwarp();
     }
-    __syncwarp();
   } else if (warp == W_MMA) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(C::kFmt, ROWS, NB);
-      for (int kb = 0; kb < my_kb; ++kb) {
-        const int st = kb % NS;
-        mbar_wait(bar_full_ab + 8 * st, (kb / NS) & 1);
-        tc_fence_after();
+    // ===== MMA issuer: whole-warp loop with warp-uniform operands, issue under elect_one().  Under `if (lane == 0)`
+    // ptxas wrapped every tcgen05.mma in an ELECT + R2UR waterfall (~80 cycles per MMA): at NB = 64 (32 cycles of
+    // tensor pipe per MMA) that WAS the "0.3 us per k block whatever the math" of round 1's ablation. =====
+    constexpr uint32_t idesc = make_idesc(C::kFmt, ROWS, NB);
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    for (int kb = 0; kb < my_kb; ++kb) {
+      const int st = kb % NS;
+      mbar_wait(bar_full_ab + 8 * st, (kb / NS) & 1);
+      tc_fence_after();
+      if (elect_one()) {
         const uint64_t db = make_smem_desc(sm_b + st * B_STAGE_BYTES);
         if constexpr (TA) {
-          const uint32_t ta = tmem_base + ACC_COLS + st * A_COLS;
+          const uint32_t ta = tb + ACC_COLS + st * A_COLS;
 #pragma unroll
           for (int k = 0; k < KB / 16; ++k)  // 16 elements = 8 TMEM columns of A, 32 B of the B row
-            tc_mma_f16_ts(tmem_base, ta + 8 * k, db + 2 * k, idesc, (kb | k) != 0);
+            tc_mma_f16_ts(tb, ta + 8 * k, db + 2 * k, idesc, (kb | k) != 0);
         } else {
           const uint64_t da = make_smem_desc(sm_a + st * A_STAGE_BYTES);
 #pragma unroll
           for (int k = 0; k < KB / 16; ++k)  // +32 B (16 elements) inside the 128 B swizzle row
-            tc_mma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            tc_mma_f16(tb, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
         }
         tc_commit(bar_empty_ab + 8 * st);
       }
-      tc_commit(bar_tmem_full);
+      __syncwarp();
     }
+    if (elect_one()) tc_commit(bar_tmem_full);
     __syncwarp();
   } else {
     // ===== dequant warps: row n0 + r is shared by TPR threads (hsel picks the chunk share) =====
