@@ -302,54 +302,67 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_consta
       const int row_lo = p.sliding_window >= 0 ? max(0, qabs + 1 - p.sliding_window) : 0;
       const float sc = p.scale * kLog2e;
       const float cap_in = SOFTCAP ? p.scale / p.softcap : 0.f, cap_out = SOFTCAP ? p.softcap * kLog2e : 0.f;  // tanh(s*scale/c)*c
-      (void)cap_in; (void)cap_out;
+      const float inv_sc = SOFTCAP ? 1.f / sc : 0.f;
+      (void)cap_in; (void)cap_out; (void)inv_sc;
       const uint32_t t_sp = tmem_base + lane_addr + TM_SP + ti * BK, t_o = tmem_base + lane_addr + TM_O + ti * D;
       float m_used = -INFINITY, m_true = -INFINITY, l = 0.f;
       for (int it = 0; it < nblk; ++it) {
         mbar_wait(bar_s_full + 8 * ti, it & 1);
         tc_fence_after();
         float s[BK];
+        {
+          // all four 32-column loads in flight, ONE wait: a wait per load exposed the TMEM latency four times
+          uint32_t v0[32], v1[32], v2[32], v3[32];
+          tmem_ld32_nowait(t_sp, v0);
+          tmem_ld32_nowait(t_sp + 32, v1);
+          tmem_ld32_nowait(t_sp + 64, v2);
+          tmem_ld32_nowait(t_sp + 96, v3);
+          tmem_ld_wait();
 #pragma unroll
-        for (int c0 = 0; c0 < BK; c0 += 32) {
-          uint32_t v[32];
-          tmem_ld<32>(t_sp + c0, v);
-#pragma unroll
-          for (int q = 0; q < 32; ++q) s[c0 + q] = __uint_as_float(v[q]);
+          for (int q = 0; q < 32; ++q) {
+            s[q] = __uint_as_float(v0[q]);
+            s[32 + q] = __uint_as_float(v1[q]);
+            s[64 + q] = __uint_as_float(v2[q]);
+            s[96 + q] = __uint_as_float(v3[q]);
+          }
         }
         const int kv0 = (j0 + it) * BK;
-        float m_blk = -INFINITY;
+        // The softmax threads are instruction-issue bound (a polynomial ex2 on the FMA pipe made the kernel 20% SLOWER),
+        // so the row is touched as little as possible: the max is taken over the RAW scores (scale > 0 commutes with
+        // max), the scale and the max subtraction are one packed FFMA2 per column pair, the row sum one packed FADD2.
+        float m_raw = -INFINITY;
         // blocks wholly inside every row's [row_lo, row_hi) of this warp need no mask (the common case away from
         // the causal diagonal and the window edge)
         const bool need_mask = __any_sync(0xffffffffu, kv0 < row_lo || kv0 + BK > row_hi);
-        if (need_mask) {
+        if (SOFTCAP || need_mask) {
 #pragma unroll
           for (int c = 0; c < BK; ++c) {
-            float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out : s[c] * sc;
+            float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out * inv_sc : s[c];  // back in raw-score units
             const int kv = kv0 + c;
             x = (kv >= row_lo && kv < row_hi) ? x : -INFINITY;
             s[c] = x;
-            m_blk = fmaxf(m_blk, x);
+            m_raw = fmaxf(m_raw, x);
           }
         } else {
 #pragma unroll
-          for (int c = 0; c < BK; ++c) {
-            const float x = SOFTCAP ? tanh_approx(s[c] * cap_in) * cap_out : s[c] * sc;
-            s[c] = x;
-            m_blk = fmaxf(m_blk, x);
-          }
+          for (int c = 0; c < BK; ++c) m_raw = fmaxf(m_raw, s[c]);
         }
+        const float m_blk = m_raw * sc;  // log2 domain (-inf stays -inf: sc > 0)
         m_true = fmaxf(m_true, m_blk);
         const float m_new = (m_blk > m_used + kRescaleThreshold) ? m_blk : m_used;
         const float alpha = (m_used == -INFINITY) ? 0.f : ex2(m_used - m_new);
         const float m_eff = (m_new == -INFINITY) ? 0.f : m_new;
-        float sum = 0.f;
+        const float2 sc2 = make_float2(sc, sc), nm2 = make_float2(-m_eff, -m_eff);
+        float2 sum2 = make_float2(0.f, 0.f);
         uint32_t pk[BK / 2];
 #pragma unroll
         for (int c = 0; c < BK; c += 2) {
-          const float p0 = ex2(s[c] - m_eff), p1 = ex2(s[c + 1] - m_eff);
-          sum += p0 + p1;
-          pk[c >> 1] = pack2(p0, p1, p.is_fp16);
+          const float2 x2 = __ffma2_rn(make_float2(s[c], s[c + 1]), sc2, nm2);  // s * scale*log2e - m
+          const float2 p2 = make_float2(ex2(x2.x), ex2(x2.y));
+          sum2 = __fadd2_rn(sum2, p2);
+          pk[c >> 1] = pack2(p2.x, p2.y, p.is_fp16);
         }
+        const float sum = sum2.x + sum2.y;
         l = l * alpha + sum;
         // O_i belongs to PV_i of the previous block until that has completed (it had: S_i(it) was issued after it)
         if (it > 0) {
