@@ -112,6 +112,18 @@ int b200_allreduce_add_rmsnorm(void* x, void* residual, const void* weight, void
                                void* const* flag_ptrs, void* epoch, int rank, int world,
                                int64_t half_bytes, int grid, int twoshot, void* stream);
 
+/* Greedy token of a vocab-parallel head (lm_head column-parallel over the vocabulary +
+ * a tiny (max, index) exchange instead of gathering logits).  `logits` [rows, shard_vocab] is this rank's slice
+ * (global token id = vocab_offset + column); out[r] = index of the first maximum over ALL ranks' slices -- what
+ * b200_argmax / mx.argmax (v1/sampling_batch.py:342-348) gives on the gathered row -- identical on every rank.
+ *   slot_ptrs[r] : rank r's slot table, 2 * world * max_rows * 16 bytes, zero-initialised (own pointer at [rank],
+ *                  peers mapped through b200_ipc_open); epoch: local uint32 [max_rows], zero-initialised.
+ * Two launches (arg-max of the slice, then the exchange: every rank stores its winner into all peers' tables and
+ * polls its own).  Every rank must call it in the same order with the same `rows`. */
+int b200_argmax_vocab_parallel(const void* logits, int32_t* out, int rows, int shard_vocab, int64_t stride,
+                               int dtype, int vocab_offset, void* const* slot_ptrs, void* epoch, int rank,
+                               int world, int max_rows, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

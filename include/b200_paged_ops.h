@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 2
+#define B200_ABI_VERSION 3
 
 /* Element types of activations / caches (reference: dtype_to_metal,
  * paged_ops.cpp:185-196 -- float, half, bfloat16 are the supported set). */
@@ -161,6 +161,12 @@ typedef struct b200_paged_attn_args {
   float softcap;
   int32_t out_dtype; /* 0 or `dtype`: out has the query dtype; B200_F16 with dtype = B200_BF16: the bf16-rounded
                         result is stored as fp16 (feeds the fp16-operand o_proj without a cast launch) */
+  int32_t window_seqlen_q; /* 0 / 1: per-row dispatch.  > 1: spec-verify window hint of the reference binding
+                              (paged_ops.cpp:841-899): must equal the longest cu_seqlens_q segment (the caller checks,
+                              as the reference does host-side); the batch runs the decode kernel in window mode --
+                              floor(16 / (H_q/H_kv)) query rows of one sequence per CTA share every KV read
+                              (pagedattention.metal:1396-1914) -- and never the tile kernel (paged_ops.cpp:468-476).
+                              Results are bitwise those of the expanded one-row-per-segment dispatch. */
 } b200_paged_attn_args;
 
 size_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args* args);

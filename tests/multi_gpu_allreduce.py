@@ -94,7 +94,7 @@ def main() -> None:
         t = torch.tensor([us], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         if rank == 0:
-            print(f"{label}: {t.item():.2f} us per 512 KiB all-reduce (graph replay, max over {world} ranks)", flush=True)
+            print(f"{label}: {t.item():.2f} us per call (64 x 4096 bf16 = 512 KiB unless noted; graph replay, max over {world} ranks)", flush=True)
 
     for b in bufs:
         b.copy_(x0)
@@ -169,6 +169,42 @@ def main() -> None:
     if not torch.equal(a, b):
         ok = False
         print(f"[rank {rank}] graph replay differs from eager", flush=True)
+    # ---- vocab-parallel greedy head: (max, id) exchange vs arg-max of the gathered logits --------------------------
+    gen = torch.Generator(device=dev).manual_seed(100)  # same stream on every rank: the full logits are known everywhere
+
+    def first_max(t):  # index of the FIRST maximum per row (mx.argmax / numpy; bf16 rows do repeat their maximum)
+        f = t.float()
+        cols = torch.arange(f.shape[-1], device=f.device).expand_as(f)
+        hit = f == f.max(dim=-1, keepdim=True).values
+        return torch.where(hit, cols, torch.full_like(cols, f.shape[-1])).min(dim=-1).values.to(torch.int32)
+
+    shard = 16032  # 128256 / 8
+    for it, (rows, dt) in enumerate([(64, torch.bfloat16), (1, torch.bfloat16), (257, torch.float16), (64, torch.bfloat16),
+                                     (3, torch.float32), (64, torch.bfloat16), (64, torch.bfloat16)]):
+        full = torch.randn((rows, shard * world), device=dev, generator=gen).to(dt)
+        if it % 2 == 0:  # exact ties across ranks and inside a slice: the lowest token id must win
+            top = full.float().max().item() + 1.0
+            for r in range(rows):
+                cols = torch.randint(0, shard * world, (3,), device=dev, generator=gen)
+                full[r, cols] = top
+        want = first_max(full)
+        mine = full[:, rank * shard:(rank + 1) * shard]  # strided view: row stride = the full vocab
+        got = ar.argmax_vocab_parallel(mine, rank * shard)
+        if not torch.equal(got, want):
+            ok = False
+            bad = (got != want).nonzero().flatten()[:4].tolist()
+            print(f"[rank {rank}] vocab-parallel argmax differs (call {it}, rows {rows}, {dt}): rows {bad} got "
+                  f"{got[bad].tolist()} want {want[bad].tolist()}", flush=True)
+    full = torch.randn((64, shard * world), device=dev, generator=gen).bfloat16()
+    mine = full[:, rank * shard:(rank + 1) * shard].contiguous()
+    toks = torch.empty((64,), dtype=torch.int32, device=dev)
+    timed(lambda t: ar.argmax_vocab_parallel(mine, rank * shard, out=toks),
+          "vocab-parallel greedy: slice arg-max + NVLink (max, id) exchange, 64 rows x 16032")
+    torch.cuda.synchronize()
+    if not torch.equal(toks, first_max(full)):
+        ok = False
+        print(f"[rank {rank}] vocab-parallel argmax differs after the timed replays", flush=True)
+
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:

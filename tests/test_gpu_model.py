@@ -241,3 +241,52 @@ def test_worker_with_vllm_scheduler_outputs_matches_oracle():
         else:
             step([], {r: 1 for r in live})
     assert len(known["A"]) == 40 + 17 and len(known["B"]) == 21 + 12
+
+
+def test_spec_verify_windows_match_expanded_and_oracle():
+    """A K+1-row verification step through ``PagedModelRunner.verify``: the window-mode layout (one segment per
+    request, KV shared between the rows of a window) gives the logits of the expanded layout bit for bit
+    (reference tests/test_spec_window_parity.py at the model level), and every row's greedy token is the oracle's."""
+    from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
+    from vllm_metal_b200.lm.decoder import PRESETS, Model
+    from vllm_metal_b200.v1.model_runner import PagedModelRunner
+
+    args = dataclasses.replace(PRESETS["tiny"], sliding_window=24, layer_types=["sliding_attention", "full_attention"])
+    model = Model(args, torch.bfloat16, "cuda", seed=3)
+    prompt_lens, windows, bs = [45, 130, 7], [4, 6, 1], 16
+    blocks_per_seq = (max(prompt_lens) + max(windows) + bs) // bs
+    nb = 1 + blocks_per_seq * len(prompt_lens)
+    rng = np.random.default_rng(5)
+    perm = rng.permutation(nb - 1) + 1
+    tables = [perm[i * blocks_per_seq:(i + 1) * blocks_per_seq].tolist() for i in range(len(prompt_lens))]
+    prompts = [rng.integers(0, args.vocab, n).tolist() for n in prompt_lens]
+    flat = [t for p in prompts for t in p]
+    pre = [(tables[i], len(p), 0) for i, p in enumerate(prompts)]
+    drafts = [rng.integers(0, args.vocab, w).tolist() for w in windows]
+    win_ids = [t for d in drafts for t in d]
+    reqs = [(tables[i], prompt_lens[i], windows[i]) for i in range(len(prompts))]
+
+    logits = {}
+    for merged in (False, True):
+        cache = B200PagedKVCache(args.num_layers, args.n_kv_heads, args.head_dim, nb, bs, torch.bfloat16, "cuda",
+                                 sliding_window_per_layer=args.sliding_window_per_layer())
+        runner = PagedModelRunner(model, cache, max_batch=8, max_model_len=256, use_cuda_graph=False)
+        runner.merge_verify_windows = merged
+        runner.execute(flat, [], pre)
+        toks = runner.verify(win_ids, reqs)
+        assert [len(t) for t in toks] == windows
+        logits[merged] = (runner.last_verify_logits.clone(), toks)
+    assert torch.equal(logits[False][0], logits[True][0])
+    assert logits[False][1] == logits[True][1]
+
+    oracle = oracle_from_model(model, nb, bs)
+    oracle.forward(flat, [], pre)
+    ologits = oracle.forward(win_ids, reqs, [])  # expanded layout: one segment (= one logits row) per window row
+    assert ologits.shape[0] == sum(windows)
+    got = to_np(logits[True][0])
+    np.testing.assert_allclose(got, ologits, atol=2e-2 + 1e-2 * np.abs(ologits).max(), rtol=0)
+    want = oracle.greedy(ologits).tolist()
+    flat_got = [t for row in logits[True][1] for t in row]
+    for i, (g, w) in enumerate(zip(flat_got, want, strict=True)):
+        if g != w:  # documented near-tie rule
+            assert float(ologits[i, w] - ologits[i, g]) <= 2e-2 + 1e-2 * abs(float(ologits[i, w]))

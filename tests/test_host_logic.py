@@ -169,14 +169,15 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(EXPORTED_SYMBOLS)
     for name in sorted(declared):
         assert hasattr(lib, name), f"{name} declared in include/*.h but not exported"
-    assert lib.b200_abi_version() == 2  # round 2: x_dtype / out_dtype arguments, args.out_dtype
+    assert lib.b200_abi_version() == 3  # round 2: x_dtype / out_dtype arguments, args.out_dtype, args.window_seqlen_q
     assert lib.b200_partition_size() == 512
 
 
 def test_args_struct_matches_header_layout():
-    # 10 pointers/size_t + 12 int32 + 6 int64 + 2 float + 1 int32 (out_dtype), padded to the 8-byte alignment
+    # 10 pointers/size_t + 12 int32 + 6 int64 + 2 float + 2 int32 (out_dtype, window_seqlen_q)
     assert ctypes.sizeof(PagedAttnArgs) == 10 * 8 + 12 * 4 + 6 * 8 + 2 * 4 + 4 + 4
     assert PagedAttnArgs.out_dtype.offset == 10 * 8 + 12 * 4 + 6 * 8 + 2 * 4
+    assert PagedAttnArgs.window_seqlen_q.offset == PagedAttnArgs.out_dtype.offset + 4
     assert PagedAttnArgs.q_stride.offset == 10 * 8 + 12 * 4
     assert PagedAttnArgs.scale.offset == 10 * 8 + 12 * 4 + 6 * 8
 

@@ -230,7 +230,7 @@ def sdpa_forward(
         q, k_cache, v_cache, kv_cache.kv_heads_per_layer[layer_idx], float(scale), 0.0,
         meta.block_tables, meta.seq_lens, meta.cu_seqlens_q, meta.block_size, meta.max_seq_len,
         kv_cache.sliding_window_per_layer[layer_idx], out,
-        window_seqlen_q=1, sinks=sinks)
+        window_seqlen_q=getattr(ctx, "verify_window_q", 1), sinks=sinks)  # sdpa.py:713,730
     if hd < cache_hd:
         out = out[..., :hd]  # strip the pad before o_proj (truncate_padded_output)
     out = out.reshape(t, n_heads * hd)

@@ -312,10 +312,108 @@ static int launch_fused(const FusedParams& f, int grid, cudaStream_t st) {
   return check_launch("allreduce_add_rmsnorm_kernel");
 }
 
+// ---- vocab-parallel greedy head: (max logit, token) exchange (lm_head row) ----------------
+// Every rank holds the logits of its own vocab slice; the greedy token is the arg-max over all slices.  Each rank
+// PUSHES its per-row winner (value, global index) into every peer's slot table with two 8-byte stores that carry
+// the call's epoch in their upper word (NCCL's LL idea: the data is its own flag, no separate signal and no fence),
+// then polls its own table -- local memory -- until all `world` entries of the row show the epoch.  One NVLink
+// one-way latency per call.  Slots alternate by epoch parity: a rank can run at most one call ahead of a peer (it
+// needs the peer's entry of call n to leave call n), so the entry a slow rank is still polling is never overwritten.
+// Ties go to the lowest global index, exactly as one arg-max over the gathered logits would (mx.argmax).
+struct ArgmaxXParams {
+  const void* logits;
+  int32_t* out;       // in: local arg-max per row (b200_argmax over the slice); out: global token id
+  uint2* slots[kMaxWorld];
+  uint32_t* epoch;    // local uint32 [max_rows]
+  int64_t stride;
+  int rows, max_rows, vocab_offset, rank, world;
+};
+
+__device__ __forceinline__ void st_relaxed_sys_v2(uint2* p, uint32_t a, uint32_t b) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ uint2 ld_relaxed_sys_v2(const uint2* p) {
+  uint2 v;
+  asm volatile("ld.relaxed.sys.global.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+  return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(32) argmax_exchange_kernel(const ArgmaxXParams p) {
+  pdl_trigger();
+  pdl_wait();
+  const int r = blockIdx.x, lane = threadIdx.x;
+  const uint32_t e = p.epoch[r] + 1;
+  const int li = p.out[r];
+  const float v = to_float(reinterpret_cast<const T*>(p.logits)[(int64_t)r * p.stride + li]);
+  const int gi = p.vocab_offset + li;
+  __syncwarp();
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  if (lane < p.world) {
+    const size_t half = (size_t)(e & 1u) * p.world;
+    uint2* dst = p.slots[lane] + ((half + p.rank) * p.max_rows + r) * 2;  // entry [parity][this rank][row] on rank `lane`
+    st_relaxed_sys_v2(dst, __float_as_uint(v), e);
+    st_relaxed_sys_v2(dst + 1, (uint32_t)gi, e);
+    const uint2* src = p.slots[p.rank] + ((half + lane) * p.max_rows + r) * 2;  // rank `lane`'s entry in my table
+    uint2 a, b;
+    uint32_t spins = 0;
+    do {
+      a = ld_relaxed_sys_v2(src);
+      b = ld_relaxed_sys_v2(src + 1);
+      if (++spins > (1u << 27)) __trap();  // a dead peer must fault this rank, not hang the box
+    } while (a.y != e || b.y != e);
+    best = __uint_as_float(a.x);
+    bi = (int)b.x;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) {
+      best = ov;
+      bi = oi;
+    }
+  }
+  if (lane == 0) {
+    p.out[r] = bi == 0x7fffffff ? 0 : bi;
+    p.epoch[r] = e;
+  }
+}
+
 }  // namespace ar
 }  // namespace b200
 
 extern "C" {
+
+int b200_argmax_vocab_parallel(const void* logits, int32_t* out, int rows, int shard_vocab, int64_t stride, int dtype,
+                               int vocab_offset, void* const* slot_ptrs, void* epoch, int rank, int world,
+                               int max_rows, void* stream) {
+  using namespace b200;
+  if (rows == 0) return B200_OK;
+  B200_CHECK_ARG(logits && out && slot_ptrs && epoch && rows > 0 && shard_vocab > 0, "argmax_vocab_parallel: bad arguments");
+  B200_CHECK_ARG(rank >= 0 && rank < world && world >= 1 && world <= ar::kMaxWorld,
+                 "argmax_vocab_parallel: rank %d of world %d", rank, world);
+  B200_CHECK_ARG(rows <= max_rows, "argmax_vocab_parallel: %d rows exceed the slot table (%d)", rows, max_rows);
+  int rc = b200_argmax(logits, out, rows, shard_vocab, stride, dtype, stream);  // winner of this rank's slice
+  if (rc != B200_OK) return rc;
+  ar::ArgmaxXParams p{};
+  p.logits = logits;
+  p.out = out;
+  for (int r = 0; r < world; ++r) p.slots[r] = reinterpret_cast<uint2*>(slot_ptrs[r]);
+  p.epoch = reinterpret_cast<uint32_t*>(epoch);
+  p.stride = stride;
+  p.rows = rows;
+  p.max_rows = max_rows;
+  p.vocab_offset = vocab_offset;
+  p.rank = rank;
+  p.world = world;
+  cudaStream_t st = (cudaStream_t)stream;
+  return B200_DISPATCH_DTYPE(dtype, T, [&]() -> int {
+    launch_pdl(ar::argmax_exchange_kernel<T>, dim3(rows), dim3(32), 0, st, p);
+    return check_launch("argmax_exchange_kernel");
+  });
+}
 
 int b200_ipc_alloc(int64_t bytes, void** ptr, unsigned char* handle64) {
   using namespace b200;

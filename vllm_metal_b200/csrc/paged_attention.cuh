@@ -89,6 +89,7 @@ int launch_generic(const b200_paged_attn_args& a, const SplitWorkspace* ws, cuda
 inline int out_is_f16(const b200_paged_attn_args& a) { return a.out_dtype == B200_F16 && a.dtype == B200_BF16 ? 1 : 0; }
 bool decode_mma_supported(const b200_paged_attn_args& a);
 int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st, int skip_qlen = 0);
+int decode_window_rows(const b200_paged_attn_args& a);  // > 1: window mode (query rows of one sequence per CTA)
 int launch_split_reduce(const b200_paged_attn_args& a, const SplitWorkspace& ws, cudaStream_t st);
 // Tile kernel (paged_attention_prefill.cu): sequences with q_len >= min_qlen, one CTA per (128-row Q tile, q head).
 bool prefill_tc_supported(const b200_paged_attn_args& a);

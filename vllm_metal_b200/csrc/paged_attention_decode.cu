@@ -14,6 +14,16 @@
 //
 // HBM-bound: 2 * L * D * esize bytes per (row, kv head); the MMA work
 // (4*L*16*D flop) is <2% of the tensor pipe at roofline.
+//
+// Window mode (WIN; reference pagedattention.metal:1396-1914, host paged_ops.cpp:468-476,508-515): with a
+// `window_seqlen_q` hint (spec-decode verification, every segment a K+1-row window) one CTA owns
+// floor(16 / G) consecutive query rows of ONE sequence -- they fill the MMA rows the GQA group leaves empty -- and
+// streams the KV once for all of them.  Each MMA row keeps its own [lo, hi) range (causal staircase, window start,
+// partition clip), tiles are dealt to warps by ABSOLUTE tile index and the split-KV plan is keyed on the row count,
+// so every row's arithmetic is the one the expanded (one row per CTA) dispatch does: the two are bitwise equal
+// (reference tests/test_spec_window_parity.py).  Tiles on which the rows' masks differ do P.V one query row at a
+// time against a V fragment zeroed outside that row's range, so a non-finite V at a position only later rows may see
+// cannot reach earlier rows through 0 * inf (test_windowed_skips_masked_inf_v).
 #include "paged_attention.cuh"
 
 namespace b200 {
@@ -97,9 +107,10 @@ struct DecodeParams {
   float scale, softcap;
   SplitWorkspace ws;
   int partitioned;
+  int win_rows, win_subs;  // window mode: query rows per CTA, CTAs per sequence
 };
 
-template <typename T, int D, int STAGES>
+template <typename T, int D, int STAGES, bool WIN>
 __global__ void __launch_bounds__(kDecodeWarps * 32, (D >= 128 ? 2 : 3))
 paged_decode_mma_kernel(const DecodeParams p) {
   pdl_trigger();
@@ -117,37 +128,104 @@ paged_decode_mma_kernel(const DecodeParams p) {
   __shared__ float sm_m[kDecodeWarps][16];
   __shared__ float sm_l[kDecodeWarps][16];
 
-  const int kvh = blockIdx.x, t = blockIdx.y, part = blockIdx.z;
+  const int kvh = blockIdx.x, part = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, tq = lane & 3;
   const int G = p.group;
 
-  const RowInfo ri = row_info(p.cu_seqlens_q, p.seq_lens, p.num_seqs, t, p.sliding_window, p.ws.skip_qlen);
-  const int s = ri.seq, eff = ri.eff;  // pagedattention.metal:913
-  if (eff <= 0) return;                // :917-920
-  int beg = ri.beg, end = eff;         // window: :1129-1133
-  const int base = ri.base;
-  if (p.partitioned) {
-    const int pstart = base + part * p.ws.partition_size;
-    if (pstart >= eff) return;  // empty partition (:922-926)
-    beg = max(beg, pstart);
-    end = min(end, pstart + p.ws.partition_size);
+  // ---- the CTA's query rows: one (t0), or in window mode nrows consecutive rows of sequence s ----
+  int s, t0, nrows, eff0;  // eff0 = KV positions row t0 may see (pagedattention.metal:913); row t0+i sees eff0+i
+  if constexpr (WIN) {
+    s = blockIdx.y / p.win_subs;
+    const int r0 = (blockIdx.y - s * p.win_subs) * p.win_rows;
+    const int q_start = p.cu_seqlens_q[s];
+    const int q_len = p.cu_seqlens_q[s + 1] - q_start;
+    if (r0 >= q_len) return;  // shorter segment than the hint: nothing in this sub-window
+    nrows = min(p.win_rows, q_len - r0);
+    t0 = q_start + r0;
+    eff0 = p.seq_lens[s] - q_len + r0 + 1;
+  } else {
+    t0 = blockIdx.y;
+    const RowInfo ri = row_info(p.cu_seqlens_q, p.seq_lens, p.num_seqs, t0, p.sliding_window, p.ws.skip_qlen);
+    s = ri.seq;
+    nrows = 1;
+    eff0 = ri.eff;
+    if (eff0 <= 0) return;  // :917-920
+  }
+  // KV range [lo, hi) of row t0+qi inside this CTA's partition.  0: the row does not exist (never written),
+  // 1: its partition is empty (:922-926), 2: live.
+  auto row_range = [&](int qi, int& lo, int& hi) -> int {
+    lo = hi = 0;
+    const int eff = eff0 + qi;
+    if (qi >= nrows || eff <= 0) return 0;
+    int beg = 0, base = 0, end = eff;
+    if (p.sliding_window >= 0) {  // window: :1129-1133; partitions start at the window's first tile (RowInfo)
+      beg = max(0, eff - p.sliding_window);
+      base = beg & ~15;
+    }
+    if (p.partitioned) {
+      const int pstart = base + part * p.ws.partition_size;
+      if (pstart >= eff) return 1;
+      beg = max(beg, pstart);
+      end = min(end, pstart + p.ws.partition_size);
+    }
+    lo = beg;
+    hi = max(end, beg);
+    return 2;
+  };
+  // union of the rows' ranges (what is streamed) and their intersection (where no row masks anything)
+  int beg, end, ulo = 0, uhi = 0x7fffffff;
+  {
+    int umin = 0x7fffffff, umax = 0, live = 0;
+    for (int qi = 0; qi < nrows; ++qi) {
+      int lo, hi;
+      const int st = row_range(qi, lo, hi);
+      if (st == 0) continue;
+      live |= st == 2;
+      if (hi > lo) {
+        umin = min(umin, lo);
+        umax = max(umax, hi);
+      }
+      ulo = max(ulo, lo);
+      uhi = min(uhi, hi);
+    }
+    if (!live) return;
+    beg = umax > umin ? umin : 0;
+    end = umax > umin ? umax : 0;
   }
   const int first_tile = beg >> 4;
   const int n_tiles = end > beg ? ((end - 1) >> 4) - first_tile + 1 : 0;
 
-  // ---- Q fragments (rows = heads of the GQA group, zero beyond G) ------------
+  // ---- this thread's two MMA rows (g and g+8): query row, head within the group, KV range ----
+  int qi0 = 0, qi1 = 0, hl0 = g, hl1 = g + 8;
+  if constexpr (WIN) {
+    qi0 = g / G;
+    hl0 = g - qi0 * G;
+    qi1 = (g + 8) / G;
+    hl1 = g + 8 - qi1 * G;
+  }
+  const bool rv0 = WIN ? qi0 < nrows : g < G;
+  const bool rv1 = WIN ? qi1 < nrows : g + 8 < G;
+  int lo0 = beg, hi0 = end, lo1 = beg, hi1 = end;
+  if constexpr (WIN) {
+    row_range(rv0 ? qi0 : nrows, lo0, hi0);
+    row_range(rv1 ? qi1 : nrows, lo1, hi1);
+  }
+
+  // ---- Q fragments (rows = heads of the GQA group [x query rows], zero beyond) ------------
   uint32_t qf[KSTEPS][4];
   {
-    const T* qb = reinterpret_cast<const T*>(p.query) + (int64_t)t * p.q_stride +
-                  (int64_t)kvh * G * D;
+    const T* q0 = reinterpret_cast<const T*>(p.query) + (int64_t)(t0 + qi0) * p.q_stride +
+                  ((int64_t)kvh * G + hl0) * D;
+    const T* q1 = reinterpret_cast<const T*>(p.query) + (int64_t)(t0 + qi1) * p.q_stride +
+                  ((int64_t)kvh * G + hl1) * D;
 #pragma unroll
     for (int ks = 0; ks < KSTEPS; ++ks) {
       const int c = ks * 16 + 2 * tq;
-      qf[ks][0] = g < G ? *reinterpret_cast<const uint32_t*>(qb + g * D + c) : 0u;
-      qf[ks][1] = g + 8 < G ? *reinterpret_cast<const uint32_t*>(qb + (g + 8) * D + c) : 0u;
-      qf[ks][2] = g < G ? *reinterpret_cast<const uint32_t*>(qb + g * D + c + 8) : 0u;
-      qf[ks][3] = g + 8 < G ? *reinterpret_cast<const uint32_t*>(qb + (g + 8) * D + c + 8) : 0u;
+      qf[ks][0] = rv0 ? *reinterpret_cast<const uint32_t*>(q0 + c) : 0u;
+      qf[ks][1] = rv1 ? *reinterpret_cast<const uint32_t*>(q1 + c) : 0u;
+      qf[ks][2] = rv0 ? *reinterpret_cast<const uint32_t*>(q0 + c + 8) : 0u;
+      qf[ks][3] = rv1 ? *reinterpret_cast<const uint32_t*>(q1 + c + 8) : 0u;
     }
   }
 
@@ -191,11 +269,14 @@ paged_decode_mma_kernel(const DecodeParams p) {
 
   const float sc_mul = p.softcap > 0.f ? p.scale : p.scale * kLog2e;
 
+  // tiles are dealt to warps by absolute index (tile & 3 == warp), so a row's tile -> warp map does not depend on
+  // where the CTA's range starts
+  const int j0 = (warp - first_tile) & (kDecodeWarps - 1);
 #pragma unroll
-  for (int st = 0; st < STAGES - 1; ++st) issue_tile(warp + st * kDecodeWarps, st);
+  for (int st = 0; st < STAGES - 1; ++st) issue_tile(j0 + st * kDecodeWarps, st);
 
   int stage = 0;
-  for (int j = warp; j < n_tiles; j += kDecodeWarps) {
+  for (int j = j0; j < n_tiles; j += kDecodeWarps) {
     cp_async_wait<STAGES - 2>();
     __syncwarp();
     {
@@ -229,7 +310,8 @@ paged_decode_mma_kernel(const DecodeParams p) {
         float v = sacc[nt][e] * sc_mul;
         if (p.softcap > 0.f) v = tanhf(v / p.softcap) * p.softcap * kLog2e;  // :1120-1122,1138
         const int tok = tok0 + nt * 8 + (e & 1);
-        sacc[nt][e] = (tok >= beg && tok < end) ? v : -INFINITY;
+        const bool in = e < 2 ? (tok >= lo0 && tok < hi0) : (tok >= lo1 && tok < hi1);
+        sacc[nt][e] = in ? v : -INFINITY;
       }
     }
     float mx0 = fmaxf(fmaxf(sacc[0][0], sacc[0][1]), fmaxf(sacc[1][0], sacc[1][1]));
@@ -269,7 +351,10 @@ paged_decode_mma_kernel(const DecodeParams p) {
     pa[1] = Mma<T>::pack(sacc[0][2], sacc[0][3]);
     pa[2] = Mma<T>::pack(sacc[1][0], sacc[1][1]);
     pa[3] = Mma<T>::pack(sacc[1][2], sacc[1][3]);
-    {
+    const int tile_beg = (first_tile + j) * kTileTokens;
+    // every streamed token of this tile is inside every row's range?  (tokens outside [beg, end) are zero-filled)
+    const bool uniform = !WIN || (max(tile_beg, beg) >= ulo && min(tile_beg + kTileTokens, end) <= uhi);
+    if (uniform) {
       const int mj = lane >> 3, r = lane & 7;
       const int trow = (mj & 1) * 8 + r;
 #pragma unroll
@@ -279,6 +364,31 @@ paged_decode_mma_kernel(const DecodeParams p) {
         ldmatrix_x4_trans(v0, v1, v2, v3, vt + trow * ROW_BYTES + ((chunk ^ r) << 4));
         Mma<T>::run(o[2 * n2], pa, v0, v1);
         Mma<T>::run(o[2 * n2 + 1], pa, v2, v3);
+      }
+    } else {
+      // the rows' masks differ on this tile: one query row at a time, V zeroed outside that row's range -- what the
+      // expanded dispatch's zero-filled load gives that row; the other rows add exact zeros
+      const int mj = lane >> 3, r = lane & 7;
+      const int trow = (mj & 1) * 8 + r;
+      const int tk = tile_beg + 2 * tq;  // this lane's B-fragment tokens: tk, tk+1 (b0) and tk+8, tk+9 (b1)
+      for (int qi = 0; qi < nrows; ++qi) {
+        int lo, hi;
+        row_range(qi, lo, hi);
+        const uint32_t m01 = ((tk >= lo && tk < hi) ? 0x0000FFFFu : 0u) | ((tk + 1 >= lo && tk + 1 < hi) ? 0xFFFF0000u : 0u);
+        const uint32_t m89 = ((tk + 8 >= lo && tk + 8 < hi) ? 0x0000FFFFu : 0u) | ((tk + 9 >= lo && tk + 9 < hi) ? 0xFFFF0000u : 0u);
+        uint32_t pq[4];
+        pq[0] = (rv0 && qi0 == qi) ? pa[0] : 0u;
+        pq[1] = (rv1 && qi1 == qi) ? pa[1] : 0u;
+        pq[2] = (rv0 && qi0 == qi) ? pa[2] : 0u;
+        pq[3] = (rv1 && qi1 == qi) ? pa[3] : 0u;
+#pragma unroll
+        for (int n2 = 0; n2 < KSTEPS; ++n2) {
+          const int chunk = n2 * 2 + (mj >> 1);
+          uint32_t v0, v1, v2, v3;
+          ldmatrix_x4_trans(v0, v1, v2, v3, vt + trow * ROW_BYTES + ((chunk ^ r) << 4));
+          Mma<T>::run(o[2 * n2], pq, v0 & m01, v1 & m89);
+          Mma<T>::run(o[2 * n2 + 1], pq, v2 & m01, v3 & m89);
+        }
       }
     }
     if (++stage == STAGES) stage = 0;
@@ -300,14 +410,17 @@ paged_decode_mma_kernel(const DecodeParams p) {
   }
 #pragma unroll
   for (int i = 0; i < D / 8; ++i) {
-    if (g < G) *reinterpret_cast<float2*>(so + g * D + i * 8 + 2 * tq) = make_float2(o[i][0], o[i][1]);
-    if (g + 8 < G)
+    if (rv0) *reinterpret_cast<float2*>(so + g * D + i * 8 + 2 * tq) = make_float2(o[i][0], o[i][1]);
+    if (rv1)
       *reinterpret_cast<float2*>(so + (g + 8) * D + i * 8 + 2 * tq) = make_float2(o[i][2], o[i][3]);
   }
   __syncthreads();
 
-  for (int idx = threadIdx.x; idx < G * D; idx += blockDim.x) {
-    const int row = idx / D, d = idx - row * D;
+  for (int idx = threadIdx.x; idx < nrows * G * D; idx += blockDim.x) {
+    const int row = idx / D, d = idx - row * D;  // MMA row = query row * G + head within the group
+    const int qi = WIN ? row / G : 0;
+    const int t = t0 + qi;
+    if (WIN && eff0 + qi <= 0) continue;  // :917-920
     float M = -INFINITY;
 #pragma unroll
     for (int w = 0; w < kDecodeWarps; ++w) M = fmaxf(M, sm_m[w][row]);
@@ -323,7 +436,7 @@ paged_decode_mma_kernel(const DecodeParams p) {
         acc += sw[row * D + d] * wgt;
       }
     }
-    const int h = kvh * G + row;
+    const int h = kvh * G + (row - qi * G);
     if (p.partitioned) {
       const int64_t prow = ((int64_t)t * p.num_q_heads + h) * p.ws.num_partitions + part;
       p.ws.tmp_out[prow * D + d] = acc;
@@ -367,20 +480,35 @@ bool decode_mma_supported(const b200_paged_attn_args& a) {
   return true;
 }
 
-template <typename T, int D, int STAGES>
-static int launch_one(const DecodeParams& p, dim3 grid, cudaStream_t st) {
+template <typename T, int D, int STAGES, bool WIN>
+static int launch_one_mode(const DecodeParams& p, dim3 grid, cudaStream_t st) {
   constexpr int smem = kDecodeWarps * STAGES * 2 * kTileTokens * D * 2;
   static bool configured_dev[16] = {false};  // cudaFuncSetAttribute is per device
   int dev_ = 0;
   B200_CUDA_OK(cudaGetDevice(&dev_));
   bool& configured = configured_dev[dev_ & 15];
   if (!configured) {
-    B200_CUDA_OK(cudaFuncSetAttribute(paged_decode_mma_kernel<T, D, STAGES>,
+    B200_CUDA_OK(cudaFuncSetAttribute(paged_decode_mma_kernel<T, D, STAGES, WIN>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  launch_pdl(paged_decode_mma_kernel<T, D, STAGES>, dim3(grid), dim3(kDecodeWarps * 32), smem, st, p);
+  launch_pdl(paged_decode_mma_kernel<T, D, STAGES, WIN>, dim3(grid), dim3(kDecodeWarps * 32), smem, st, p);
   return check_launch("paged_decode_mma_kernel");
+}
+
+template <typename T, int D, int STAGES>
+static int launch_one(const DecodeParams& p, dim3 grid, cudaStream_t st) {
+  if (p.win_rows > 1) return launch_one_mode<T, D, STAGES, true>(p, grid, st);
+  return launch_one_mode<T, D, STAGES, false>(p, grid, st);
+}
+
+// Window mode (a `window_seqlen_q` hint > 1): query rows of one sequence that share a CTA -- the MMA rows the GQA
+// group leaves free.  1 = per-row dispatch.
+int decode_window_rows(const b200_paged_attn_args& a) {
+  if (a.window_seqlen_q <= 1) return 1;
+  const int G = a.num_q_heads / a.num_kv_heads;
+  const int r = G > 0 ? 16 / G : 1;
+  return r < 1 ? 1 : (r > a.window_seqlen_q ? a.window_seqlen_q : r);
 }
 
 int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, cudaStream_t st, int skip_qlen) {
@@ -414,6 +542,12 @@ int launch_decode_mma(const b200_paged_attn_args& a, const SplitWorkspace* ws, c
   p.ws.skip_qlen = skip_qlen;
   p.ws.out_f16 = out_is_f16(a);
   dim3 grid(a.num_kv_heads, a.num_q_tokens, ws ? ws->num_partitions : 1);
+  p.win_rows = skip_qlen > 0 ? 1 : decode_window_rows(a);
+  p.win_subs = 1;
+  if (p.win_rows > 1) {  // one CTA per (sequence, sub-window of win_rows rows); paged_ops.cpp:508-515
+    p.win_subs = (a.window_seqlen_q + p.win_rows - 1) / p.win_rows;
+    grid.y = (unsigned)(a.num_seqs * p.win_subs);
+  }
   if (a.dtype == B200_BF16) {
     if (a.head_dim == 128) return launch_one<__nv_bfloat16, 128, 3>(p, grid, st);
     return launch_one<__nv_bfloat16, 64, 4>(p, grid, st);

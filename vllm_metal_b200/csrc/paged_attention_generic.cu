@@ -251,6 +251,8 @@ static int validate(const b200_paged_attn_args* a) {
   B200_CHECK_ARG(a->dtype == B200_F32 || a->dtype == B200_F16 || a->dtype == B200_BF16,
                  "paged_attention: unsupported dtype code %d", a->dtype);
   B200_CHECK_ARG(a->num_blocks > 0, "paged_attention: num_blocks must be > 0");
+  B200_CHECK_ARG(a->window_seqlen_q >= 0, "paged_attention: window_seqlen_q must be >= 1 (1 = per-token decode), got %d",
+                 a->window_seqlen_q);
   B200_CHECK_ARG(a->out_dtype == 0 || a->out_dtype == a->dtype || (a->out_dtype == B200_F16 && a->dtype == B200_BF16),
                  "paged_attention: out_dtype must be 0 / the query dtype, or fp16 for a bf16 call");
   return B200_OK;
@@ -309,7 +311,9 @@ static int plan_partitions(const b200_paged_attn_args& a, bool mma, int* parts) 
     }
   }
   // Reference gate (paged_ops.cpp:539-541): pure decode && grid below occupancy bound.
-  const bool pure_decode = a.num_q_tokens == a.num_seqs;
+  // Window batches keep split-KV eligibility on the split-equivalent grid (one row per token, :528-541), so the
+  // windowed and the expanded dispatch of a verification step take the same decision.
+  const bool pure_decode = a.num_q_tokens == a.num_seqs || a.window_seqlen_q > 1;
   const int gate = b200_min_decode_grid();
   if (pure_decode && gate > 0 && (int64_t)a.num_q_heads * a.num_q_tokens < gate)
     *parts = max_parts;
@@ -341,7 +345,11 @@ static AttnPlan make_plan(const b200_paged_attn_args& a) {
   // with at least kTileMinQlen query rows run on the tcgen05 tile kernel, the remaining (decode) rows of a mixed
   // batch on the per-row kernels, which leave the tile kernel's sequences untouched.
   const bool tile_ok = prefill_tc_supported(a);
-  pl.tile = a.kernel == 3 || (a.kernel == 0 && tile_ok && a.num_q_tokens - a.num_seqs + 1 >= kTileMinQlen);
+  // A spec-verify batch (window hint) never takes the tile kernel (paged_ops.cpp:468-476): K+1-row windows waste a
+  // 128-row tile and lose the split-KV parallelism; the decode kernel runs it in window mode.
+  const bool window_batch = a.window_seqlen_q > 1;
+  pl.tile = a.kernel == 3 ||
+            (a.kernel == 0 && tile_ok && !window_batch && a.num_q_tokens - a.num_seqs + 1 >= kTileMinQlen);
   // kernel == 3 pins every sequence to the tile kernel (parity tests); auto keeps short ones on the row kernels
   pl.skip_qlen = pl.tile ? (a.kernel == 3 ? 1 : kTileMinQlen) : 0;
   pl.rows = a.kernel != 3;

@@ -50,26 +50,36 @@ class NVLinkAllReduce:
         # every size on one NVSwitch box (2 ranks 18.8 vs 11.4 us, 8 ranks 27.4 vs 23.8: the second flag exchange costs
         # more than the 2.2 MiB of pulls it saves), so it is off by default (profiles/r02_allreduce_tp{2,8}.txt)
         self.twoshot_from = int(os.environ.get("B200_ALLREDUCE_TWOSHOT_FROM", "16"))
+        lib.b200_argmax_vocab_parallel.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                                   ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+                                                   ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p, ctypes.c_int,
+                                                   ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
         self.half_bytes = (int(max_bytes) + 255) // 256 * 256
         self.grid = int(grid)
+        self.max_rows = 1024  # rows of one vocab-parallel arg-max call (slot table: 2 parities x world x rows x 16 B)
         with torch.cuda.device(self.device):
             # [2 halves of partials][2 x 2 halves of two-shot results]; [grid][world] flags x 2 exchanges
             self._own_symm, h_symm = self._alloc(6 * self.half_bytes)
             self._own_flags, h_flags = self._alloc(2 * self.grid * self.world * 4)
+            self._own_slots, h_slots = self._alloc(2 * self.world * self.max_rows * 16)
             self.epoch = torch.zeros((self.grid,), dtype=torch.int32, device=self.device)
+            self.argmax_epoch = torch.zeros((self.max_rows,), dtype=torch.int32, device=self.device)
             handles: list = [None] * self.world
-            dist.all_gather_object(handles, (h_symm, h_flags), group=group)
+            dist.all_gather_object(handles, (h_symm, h_flags, h_slots), group=group)
             self._opened: list[int] = []
-            symm, flags = [], []
-            for r, (hs, hf) in enumerate(handles):
+            symm, flags, slots = [], [], []
+            for r, (hs, hf, hl) in enumerate(handles):
                 if r == self.rank:
                     symm.append(self._own_symm)
                     flags.append(self._own_flags)
+                    slots.append(self._own_slots)
                 else:
                     symm.append(self._open(hs))
                     flags.append(self._open(hf))
+                    slots.append(self._open(hl))
             self._symm = (ctypes.c_void_p * self.world)(*symm)
             self._flags = (ctypes.c_void_p * self.world)(*flags)
+            self._slots = (ctypes.c_void_p * self.world)(*slots)
             torch.cuda.synchronize(self.device)
         dist.barrier(group=group)  # every rank has zeroed and mapped everything before the first call
         self.calls = 0
@@ -127,12 +137,35 @@ class NVLinkAllReduce:
         self.calls += 1
         return out.reshape(x.shape)
 
+    def argmax_vocab_parallel(self, logits: torch.Tensor, vocab_offset: int, out: torch.Tensor | None = None) -> torch.Tensor:
+        """Greedy tokens of a vocab-parallel head: ``logits`` [rows, vocab / world] is this rank's slice starting at
+        token ``vocab_offset``; returns int32 [rows], the arg-max over every rank's slice (lowest id on ties), the
+        same on all ranks.  Two launches: arg-max of the slice, then a (value, id) exchange pushed into the peers'
+        slot tables over NVLink."""
+        x2 = logits.reshape(-1, logits.shape[-1])
+        if x2.stride(1) != 1:
+            x2 = x2.contiguous()
+        rows = x2.shape[0]
+        if rows > self.max_rows:
+            raise ValueError(f"argmax_vocab_parallel: {rows} rows exceed the slot table ({self.max_rows})")
+        if out is None:
+            out = torch.empty((rows,), dtype=torch.int32, device=x2.device)
+        elif out.dtype != torch.int32 or out.numel() != rows or not out.is_contiguous():
+            raise ValueError("argmax_vocab_parallel: out must be a contiguous int32 [rows]")
+        rc = self.lib.b200_argmax_vocab_parallel(
+            x2.data_ptr(), out.data_ptr(), rows, x2.shape[1], x2.stride(0), _DTYPE_CODE[x2.dtype], int(vocab_offset),
+            self._slots, self.argmax_epoch.data_ptr(), self.rank, self.world, self.max_rows,
+            torch.cuda.current_stream().cuda_stream)
+        self.ops._check(rc)
+        self.ops.launches += 2
+        return out
+
     def close(self) -> None:
         torch.cuda.synchronize(self.device)
         for p in self._opened:
             self.lib.b200_ipc_close(p)
         self._opened = []
-        for p in (self._own_symm, self._own_flags):
+        for p in (self._own_symm, self._own_flags, self._own_slots):
             if p:
                 self.lib.b200_ipc_free(p)
-        self._own_symm = self._own_flags = 0
+        self._own_symm = self._own_flags = self._own_slots = 0

@@ -161,11 +161,19 @@ class Model(nn.Module):
 
     def __init__(self, args: ModelArgs, dtype=torch.bfloat16, device="cuda", seed: int = 0,
                  rank: int = 0, world: int = 1, allreduce=None, prepack: bool = True,
-                 prefill_layout: bool = False) -> None:
+                 prefill_layout: bool = False, vocab_parallel: bool | None = None) -> None:
         super().__init__()
         self.args = args
         self.rank, self.world = rank, world
         self._allreduce = allreduce
+        # Vocab-parallel head: each rank keeps vocab / world rows of the head and the greedy token comes
+        # from a (max, id) exchange (``greedy``); ``forward`` then returns this rank's logits slice only.
+        if vocab_parallel is None:
+            vocab_parallel = world > 1 and hasattr(allreduce, "argmax_vocab_parallel") and args.vocab % world == 0
+        if vocab_parallel and (world < 2 or args.vocab % world):
+            raise ValueError(f"vocab-parallel head needs world > 1 and vocab ({args.vocab}) divisible by it ({world})")
+        self.vocab_parallel = bool(vocab_parallel)
+        self.vocab_offset = rank * (args.vocab // world) if self.vocab_parallel else 0
         gen = torch.Generator(device=device).manual_seed(seed)
         emb = torch.empty((args.vocab, args.hidden), dtype=torch.float32, device=device).normal_(0, 0.02, generator=gen)
         self.embed_tokens = QuantizedEmbedding.from_dense(emb.to(dtype), args.group_size, args.bits, dtype)
@@ -177,6 +185,8 @@ class Model(nn.Module):
             self.lm_head = None
         else:
             self.lm_head = _rand_qlinear(args.hidden, args.vocab, args, gen, dtype, device)
+            if self.vocab_parallel:
+                self.lm_head = self.lm_head.shard_rows(rank, world)
         self._f16_acts = False
         self._prefill_layout = prefill_layout
         if prepack:
@@ -193,7 +203,8 @@ class Model(nn.Module):
                     and getattr(m, "weight_tc", None) is None:
                 m.prepack(keep_mlx_layout=False, prefill_layout=self._prefill_layout and m is not self.lm_head)
         if self.lm_head is None:
-            self.embed_tokens.prepack()
+            n = self.args.vocab // self.world
+            self.embed_tokens.prepack(rows=(self.rank * n, (self.rank + 1) * n) if self.vocab_parallel else None)
         # norms feed the stream-K linears fp16 directly (their operand type) when every consumer is one
         self._f16_acts = all(getattr(m, "weight_blob", None) is not None or getattr(m, "weight_tc", None) is not None
                              for m in self.modules() if isinstance(m, QuantizedLinear)) and (
@@ -232,6 +243,13 @@ class Model(nn.Module):
         if logits_rows is not None:
             x = x.index_select(0, logits_rows)
         return self.embed_tokens.as_linear(x) if self.lm_head is None else self.lm_head(x)
+
+    def greedy(self, logits: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        """Greedy token per logits row (v1/sampling_batch.py:342-348: first maximum).  With a vocab-parallel head the
+        rows are this rank's slice and the winner comes out of the NVLink (max, id) exchange, the same on every rank."""
+        if self.vocab_parallel:
+            return self._allreduce.argmax_vocab_parallel(logits, self.vocab_offset, out=out)
+        return get_ops().argmax(logits, out=out)
 
     def weight_bytes(self) -> int:
         return sum(b.numel() * b.element_size() for b in self.buffers())

@@ -28,7 +28,7 @@ from typing import Any
 import torch
 
 from . import constants
-from .constants import DTYPE_BF16, DTYPE_F16, DTYPE_F32, PARTITION_SIZE
+from .constants import DTYPE_BF16, DTYPE_F16, DTYPE_F32, PA_WINDOW_MAX_HEAD_SIZE as PA_WINDOW_MAX_HEAD, PARTITION_SIZE
 
 logger = logging.getLogger(__name__)
 
@@ -76,6 +76,7 @@ class PagedAttnArgs(ctypes.Structure):
         ("scale", ctypes.c_float),
         ("softcap", ctypes.c_float),
         ("out_dtype", ctypes.c_int32),
+        ("window_seqlen_q", ctypes.c_int32),
     ]
 
 
@@ -122,6 +123,7 @@ EXPORTED_SYMBOLS = (
     "b200_ipc_free",
     "b200_allreduce_sum",
     "b200_allreduce_add_rmsnorm",
+    "b200_argmax_vocab_parallel",
 )
 
 
@@ -273,6 +275,35 @@ class _Ops:
             _require_cuda(n, t)
         if key.dim() != 3 or value.shape != key.shape:
             raise ValueError(f"key/value must both be [T, H_kv, D], got {tuple(key.shape)} / {tuple(value.shape)}")
+        if window_seqlen_q > 1:
+            # paged_ops.cpp:855-899: the hint must equal the longest segment of a structurally valid cu_seqlens_q
+            # (an understated one leaves window rows unwritten); only the spec-verify path passes it and its
+            # cu_seqlens_q is a small host-built array, so reading it back is cheap
+            if query.shape[2] > PA_WINDOW_MAX_HEAD:
+                raise ValueError(
+                    f"window_seqlen_q={window_seqlen_q} requires head_size <= {PA_WINDOW_MAX_HEAD}, got "
+                    f"{query.shape[2]}; wider heads must keep the expanded per-token verify layout "
+                    "(window-mode register state scales with rows * head_size)")
+            if cu_seqlens_q.dtype != torch.int32:
+                raise ValueError("cu_seqlens_q must be int32 for window-mode validation")
+            cu = cu_seqlens_q.tolist()
+            nseg = len(cu) - 1
+            if nseg < 1 or cu[0] != 0 or cu[nseg] != query.shape[0]:
+                raise ValueError(
+                    f"cu_seqlens_q must start at 0 and end at the query row count ({query.shape[0]}), got "
+                    f"{nseg} segment(s)")
+            longest = 0
+            for i in range(nseg):
+                seg = cu[i + 1] - cu[i]
+                if seg < 1:
+                    raise ValueError(
+                        f"cu_seqlens_q segment {i} is empty ({cu[i]} -> {cu[i + 1]}); every window-mode segment "
+                        "needs at least one query row")
+                longest = max(longest, seg)
+            if longest != window_seqlen_q:
+                raise ValueError(
+                    f"window_seqlen_q={window_seqlen_q} does not match the longest cu_seqlens_q segment "
+                    f"({longest}); an understated value leaves window rows unwritten")
         if key_cache.dim() != 4 or value_cache.shape != key_cache.shape:
             raise ValueError("key_cache/value_cache must both be [num_blocks, block_size, H_kv, D]")
         if key_cache.shape[2:] != key.shape[1:]:
@@ -419,6 +450,7 @@ class _Ops:
         a.num_blocks = nb
         a.scale, a.softcap = float(scale), float(softcap)
         a.out_dtype = _dtype_code("out", out)
+        a.window_seqlen_q = int(window_seqlen_q)
         need = self._lib.b200_paged_attention_workspace_bytes(ctypes.byref(a))
         ws = self._workspace(query.device, need)
         a.workspace = _ptr(ws)

@@ -201,11 +201,17 @@ class QuantizedEmbedding(nn.Module):
         return get_ops().dequantize(self.weight, self.scales, self.biases, self.group_size, self.bits,
                                     ids=ids, dtype=self.scales.dtype)
 
-    def prepack(self) -> QuantizedEmbedding:
-        """Streaming blob for the tied lm_head (``as_linear``); the row gather keeps the MLX layout."""
+    head_rows: tuple[int, int] | None = None  # vocab-parallel tied head: the rows ``as_linear`` multiplies by
+
+    def prepack(self, rows: tuple[int, int] | None = None) -> QuantizedEmbedding:
+        """Streaming blob for the tied lm_head (``as_linear``); the row gather keeps the MLX layout.  ``rows`` =
+        (lo, hi): a vocab-parallel rank's slice of the head -- ``as_linear`` then returns logits [.., hi - lo]."""
+        self.head_rows = rows
+        lo, hi = rows if rows is not None else (0, self.scales.shape[0])
         if self.scales.dtype in (torch.bfloat16, torch.float16):
             try:
-                blob = get_ops().qstream_prepack(self.weight, self.scales, self.biases, self.group_size, self.bits)
+                blob = get_ops().qstream_prepack(self.weight[lo:hi], self.scales[lo:hi], self.biases[lo:hi],
+                                                 self.group_size, self.bits)
             except ValueError:
                 return self
             self.register_buffer("weight_blob", blob, persistent=False)
@@ -213,10 +219,11 @@ class QuantizedEmbedding(nn.Module):
 
     def as_linear(self, x: torch.Tensor) -> torch.Tensor:
         blob = getattr(self, "weight_blob", None)
-        n, k = self.scales.shape[0], self.scales.shape[1] * self.group_size
+        lo, hi = self.head_rows if self.head_rows is not None else (0, self.scales.shape[0])
+        k = self.scales.shape[1] * self.group_size
         if blob is not None and x.dtype in (torch.bfloat16, torch.float16):
-            return get_ops().qstream_linear(x, blob, n, k, self.group_size, self.bits, out_dtype=self.scales.dtype)
+            return get_ops().qstream_linear(x, blob, hi - lo, k, self.group_size, self.bits, out_dtype=self.scales.dtype)
         if x.dtype != self.scales.dtype:
             x = x.to(self.scales.dtype)
-        return get_ops().quantized_matmul(x, self.weight, self.scales, self.biases, transpose=True,
+        return get_ops().quantized_matmul(x, self.weight[lo:hi], self.scales[lo:hi], self.biases[lo:hi], transpose=True,
                                           group_size=self.group_size, bits=self.bits)

@@ -92,6 +92,10 @@ class PagedModelRunner:
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
+    def _greedy(self, logits, out=None):
+        greedy = getattr(self.model, "greedy", None)  # vocab-parallel heads exchange (max, id) between the ranks
+        return greedy(logits, out=out) if greedy is not None else get_ops().argmax(logits, out=out)
+
     # -- generic (eager) path: any mix of prefill chunks and decode rows -----------
     def execute(self, input_ids: Sequence[int], decode_requests, prefill_requests) -> list[int]:
         """One packed forward; returns the greedy token of every segment's last row.
@@ -110,7 +114,7 @@ class PagedModelRunner:
             last_rows = torch.tensor([c - 1 for c in ctx.cu_seqlens[1:]], dtype=torch.int64).pin_memory().to(
                 self.device, non_blocking=True)
             logits = self.model(ids, ctx, self.kv_cache, logits_rows=last_rows)
-            toks = get_ops().argmax(logits)
+            toks = self._greedy(logits)
             out = toks.cpu().tolist()
             # bytes that crossed PCIe for this step: ids + logit rows + the kernel metadata sdpa uploads once
             # (slot_mapping int64 [T], seq_lens / cu_seqlens int32, block tables int32), token ids back
@@ -119,6 +123,39 @@ class PagedModelRunner:
             self.h2d_bytes += ids.numel() * 4 + last_rows.numel() * 8 + len(ctx.slot_mapping) * 8 + \
                 (2 * nseq + 1) * 4 + nseq * maxb * 4 + len(ctx.slot_mapping) * 4
             self.d2h_bytes += len(out) * 4
+            return out
+        finally:
+            clear_context()
+
+    # -- speculative verification: K+1-row decode windows ------------------------------
+    # Window-mode layout (one cu_seqlens segment per request; reference runner property ``merge_verify_windows``,
+    # attention/context.py:187-197): the decode kernel then shares every KV read between a window's rows.  False
+    # gives the expanded one-row-per-segment layout -- the same numbers bit for bit, K+1 times the KV traffic.
+    merge_verify_windows: bool = True
+
+    def verify(self, input_ids: Sequence[int], decode_requests) -> list[list[int]]:
+        """One verification step.  ``decode_requests``: ``(block_ids, seq_len, num_tokens)`` with ``seq_len`` tokens
+        already cached and ``num_tokens`` = 1 + drafts; ``input_ids``: the packed window tokens (last accepted token,
+        then the drafts).  Returns the greedy token after EVERY window row, one list per request: row j's token
+        verifies draft j+1 and the first mismatch (or the last row) yields the bonus token."""
+        reqs = [(r[0], r[1], r[2] if len(r) > 2 else 1) for r in decode_requests]
+        if self.group_block_sizes is not None:
+            prepare_grouped(reqs, [], self.group_block_sizes, merge_verify_windows=self.merge_verify_windows)
+        else:
+            prepare_unified(reqs, [], self.block_size, merge_verify_windows=self.merge_verify_windows)
+        ctx = get_context()
+        try:
+            ids = torch.tensor(list(input_ids), dtype=torch.int32).pin_memory().to(self.device, non_blocking=True)
+            self.last_verify_logits = self.model(ids, ctx, self.kv_cache, logits_rows=None)
+            toks = self._greedy(self.last_verify_logits).cpu().tolist()
+            nseq = len(ctx.cu_seqlens) - 1
+            maxb = max((len(t) for t in (ctx.block_tables or [])), default=0)
+            self.h2d_bytes += ids.numel() * 4 + len(ctx.slot_mapping) * 12 + (2 * nseq + 1) * 4 + nseq * maxb * 4
+            self.d2h_bytes += len(toks) * 4
+            out, at = [], 0
+            for r in reqs:
+                out.append(toks[at:at + r[2]])
+                at += r[2]
             return out
         finally:
             clear_context()
@@ -139,7 +176,7 @@ class PagedModelRunner:
     def _forward_decode(self, batch: int, max_seq_len: int, advance: bool = False) -> None:
         meta = self._meta(batch, max_seq_len)
         logits = self.model(self.buf.view("input_ids")[:batch], None, self.kv_cache, meta=meta)
-        get_ops().argmax(logits, out=self.buf.out_tokens[:batch])
+        self._greedy(logits, out=self.buf.out_tokens[:batch])
         if advance:
             self.advance_on_device(batch)
 
