@@ -77,6 +77,28 @@ def _worker(rank: int, world: int, port: int, bits: int, group: int, out: dict) 
         assert (n_kv // world) * (n_heads // n_kv) == per
         with pytest.raises(ValueError):
             QuantizedLinear.from_dense(torch.randn((64, 192), generator=g), None, 64, bits).shard_cols(rank, world)
+
+        # vocab-parallel head: each rank's logits slice -> (max, global id) -> exchange -> first maximum overall
+        # (csrc/nvlink_allreduce.cu argmax_exchange_kernel does this step over NVLink; the arithmetic is pinned here)
+        vocab = 96
+        head = QuantizedLinear.from_dense(torch.randn((vocab, hidden), generator=g) * 0.05, None, group, bits)
+        head_r = head.shard_rows(rank, world)
+        logits = torch.from_numpy(x @ _dense(head).T).bfloat16().double()  # bf16 rows repeat their maximum
+        logits[1, [5, 70]] = logits.max() + 1.0                             # an exact tie across the two ranks
+        logits[2, [60, 61]] = logits.max() + 1.0                            # and one inside rank 1's slice
+        n = vocab // world
+        mine = logits[:, rank * n:(rank + 1) * n]
+        np.testing.assert_array_equal(_dense(head_r), _dense(head)[rank * n:(rank + 1) * n])
+        val, idx = mine.max(dim=-1).values, torch.from_numpy(np.argmax(mine.numpy(), axis=-1)) + rank * n
+        pair = torch.stack([val, idx.double()], dim=-1)
+        pairs = [torch.empty_like(pair) for _ in range(world)]
+        dist.all_gather(pairs, pair)
+        best_v, best_i = pairs[0][:, 0].clone(), pairs[0][:, 1].clone()
+        for pr in pairs[1:]:
+            take = (pr[:, 0] > best_v) | ((pr[:, 0] == best_v) & (pr[:, 1] < best_i))
+            best_v, best_i = torch.where(take, pr[:, 0], best_v), torch.where(take, pr[:, 1], best_i)
+        np.testing.assert_array_equal(best_i.long().numpy(), np.argmax(logits.numpy(), axis=-1))  # numpy: first maximum
+        assert int(best_i[1]) == 5 and int(best_i[2]) == 60
         out[rank] = "ok"
     finally:
         dist.destroy_process_group()

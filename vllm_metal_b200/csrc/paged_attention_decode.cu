@@ -367,7 +367,7 @@ paged_decode_mma_kernel(const DecodeParams p) {
       }
     } else {
       // the rows' masks differ on this tile: one query row at a time, V zeroed outside that row's range -- what the
-      // expanded dispatch's zero-filled load gives that row; the other rows add exact zeros
+      // expanded dispatch's zero-filled load gives that row; the other rows keep their accumulators
       const int mj = lane >> 3, r = lane & 7;
       const int trow = (mj & 1) * 8 + r;
       const int tk = tile_beg + 2 * tq;  // this lane's B-fragment tokens: tk, tk+1 (b0) and tk+8, tk+9 (b1)
@@ -376,18 +376,32 @@ paged_decode_mma_kernel(const DecodeParams p) {
         row_range(qi, lo, hi);
         const uint32_t m01 = ((tk >= lo && tk < hi) ? 0x0000FFFFu : 0u) | ((tk + 1 >= lo && tk + 1 < hi) ? 0xFFFF0000u : 0u);
         const uint32_t m89 = ((tk + 8 >= lo && tk + 8 < hi) ? 0x0000FFFFu : 0u) | ((tk + 9 >= lo && tk + 9 < hi) ? 0xFFFF0000u : 0u);
+        // only query row qi's MMA rows take this pass's result: a zero P row times a non-finite V is NaN, not 0
+        const bool t0_ = rv0 && qi0 == qi, t1_ = rv1 && qi1 == qi;
         uint32_t pq[4];
-        pq[0] = (rv0 && qi0 == qi) ? pa[0] : 0u;
-        pq[1] = (rv1 && qi1 == qi) ? pa[1] : 0u;
-        pq[2] = (rv0 && qi0 == qi) ? pa[2] : 0u;
-        pq[3] = (rv1 && qi1 == qi) ? pa[3] : 0u;
+        pq[0] = t0_ ? pa[0] : 0u;
+        pq[1] = t1_ ? pa[1] : 0u;
+        pq[2] = t0_ ? pa[2] : 0u;
+        pq[3] = t1_ ? pa[3] : 0u;
 #pragma unroll
         for (int n2 = 0; n2 < KSTEPS; ++n2) {
           const int chunk = n2 * 2 + (mj >> 1);
           uint32_t v0, v1, v2, v3;
           ldmatrix_x4_trans(v0, v1, v2, v3, vt + trow * ROW_BYTES + ((chunk ^ r) << 4));
-          Mma<T>::run(o[2 * n2], pq, v0 & m01, v1 & m89);
-          Mma<T>::run(o[2 * n2 + 1], pq, v2 & m01, v3 & m89);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            float (&oo)[4] = o[2 * n2 + h];
+            float d[4] = {oo[0], oo[1], oo[2], oo[3]};
+            Mma<T>::run(d, pq, (h ? v2 : v0) & m01, (h ? v3 : v1) & m89);
+            if (t0_) {
+              oo[0] = d[0];
+              oo[1] = d[1];
+            }
+            if (t1_) {
+              oo[2] = d[2];
+              oo[3] = d[3];
+            }
+          }
         }
       }
     }

@@ -275,35 +275,6 @@ class _Ops:
             _require_cuda(n, t)
         if key.dim() != 3 or value.shape != key.shape:
             raise ValueError(f"key/value must both be [T, H_kv, D], got {tuple(key.shape)} / {tuple(value.shape)}")
-        if window_seqlen_q > 1:
-            # paged_ops.cpp:855-899: the hint must equal the longest segment of a structurally valid cu_seqlens_q
-            # (an understated one leaves window rows unwritten); only the spec-verify path passes it and its
-            # cu_seqlens_q is a small host-built array, so reading it back is cheap
-            if query.shape[2] > PA_WINDOW_MAX_HEAD:
-                raise ValueError(
-                    f"window_seqlen_q={window_seqlen_q} requires head_size <= {PA_WINDOW_MAX_HEAD}, got "
-                    f"{query.shape[2]}; wider heads must keep the expanded per-token verify layout "
-                    "(window-mode register state scales with rows * head_size)")
-            if cu_seqlens_q.dtype != torch.int32:
-                raise ValueError("cu_seqlens_q must be int32 for window-mode validation")
-            cu = cu_seqlens_q.tolist()
-            nseg = len(cu) - 1
-            if nseg < 1 or cu[0] != 0 or cu[nseg] != query.shape[0]:
-                raise ValueError(
-                    f"cu_seqlens_q must start at 0 and end at the query row count ({query.shape[0]}), got "
-                    f"{nseg} segment(s)")
-            longest = 0
-            for i in range(nseg):
-                seg = cu[i + 1] - cu[i]
-                if seg < 1:
-                    raise ValueError(
-                        f"cu_seqlens_q segment {i} is empty ({cu[i]} -> {cu[i + 1]}); every window-mode segment "
-                        "needs at least one query row")
-                longest = max(longest, seg)
-            if longest != window_seqlen_q:
-                raise ValueError(
-                    f"window_seqlen_q={window_seqlen_q} does not match the longest cu_seqlens_q segment "
-                    f"({longest}); an understated value leaves window rows unwritten")
         if key_cache.dim() != 4 or value_cache.shape != key_cache.shape:
             raise ValueError("key_cache/value_cache must both be [num_blocks, block_size, H_kv, D]")
         if key_cache.shape[2:] != key.shape[1:]:
@@ -402,6 +373,35 @@ class _Ops:
             raise ValueError(
                 f"window_seqlen_q must be >= 1 (1 = per-token decode), got {window_seqlen_q}; "
                 "a non-positive hint would silently select non-window routing")
+        if window_seqlen_q > 1:
+            # paged_ops.cpp:855-899: the hint must equal the longest segment of a structurally valid cu_seqlens_q
+            # (an understated one leaves window rows unwritten); only the spec-verify path passes it and its
+            # cu_seqlens_q is a small host-built array, so reading it back is cheap
+            if query.shape[2] > PA_WINDOW_MAX_HEAD:
+                raise ValueError(
+                    f"window_seqlen_q={window_seqlen_q} requires head_size <= {PA_WINDOW_MAX_HEAD}, got "
+                    f"{query.shape[2]}; wider heads must keep the expanded per-token verify layout "
+                    "(window-mode register state scales with rows * head_size)")
+            if cu_seqlens_q.dtype != torch.int32:
+                raise ValueError("cu_seqlens_q must be int32 for window-mode validation")
+            cu = cu_seqlens_q.tolist()
+            nseg = len(cu) - 1
+            if nseg < 1 or cu[0] != 0 or cu[nseg] != query.shape[0]:
+                raise ValueError(
+                    f"cu_seqlens_q must start at 0 and end at the query row count ({query.shape[0]}), got "
+                    f"{nseg} segment(s)")
+            longest = 0
+            for i in range(nseg):
+                seg = cu[i + 1] - cu[i]
+                if seg < 1:
+                    raise ValueError(
+                        f"cu_seqlens_q segment {i} is empty ({cu[i]} -> {cu[i + 1]}); every window-mode segment "
+                        "needs at least one query row")
+                longest = max(longest, seg)
+            if longest != window_seqlen_q:
+                raise ValueError(
+                    f"window_seqlen_q={window_seqlen_q} does not match the longest cu_seqlens_q segment "
+                    f"({longest}); an understated value leaves window rows unwritten")
         if key_cache.dim() != 4 or value_cache.shape != key_cache.shape:
             raise ValueError("key_cache/value_cache must both be [num_blocks, block_size, H_kv, D]")
         if query.dtype != key_cache.dtype or value_cache.dtype != key_cache.dtype:
