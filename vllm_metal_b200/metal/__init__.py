@@ -384,7 +384,11 @@ class _Ops:
                     "(window-mode register state scales with rows * head_size)")
             if cu_seqlens_q.dtype != torch.int32:
                 raise ValueError("cu_seqlens_q must be int32 for window-mode validation")
-            cu = cu_seqlens_q.tolist()
+            # the segment check reads cu_seqlens_q back; a stream under CUDA-graph capture cannot, and the eager
+            # warm-up call that precedes every capture has already checked the same metadata
+            capturing = torch.cuda.is_current_stream_capturing()
+            cu = [0, query.shape[0]] if capturing else cu_seqlens_q.tolist()
+            window_check = not capturing
             nseg = len(cu) - 1
             if nseg < 1 or cu[0] != 0 or cu[nseg] != query.shape[0]:
                 raise ValueError(
@@ -398,7 +402,7 @@ class _Ops:
                         f"cu_seqlens_q segment {i} is empty ({cu[i]} -> {cu[i + 1]}); every window-mode segment "
                         "needs at least one query row")
                 longest = max(longest, seg)
-            if longest != window_seqlen_q:
+            if window_check and longest != window_seqlen_q:
                 raise ValueError(
                     f"window_seqlen_q={window_seqlen_q} does not match the longest cu_seqlens_q segment "
                     f"({longest}); an understated value leaves window rows unwritten")
