@@ -175,6 +175,19 @@ size_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args* args);
 int b200_paged_attention_num_launches(const b200_paged_attn_args* args);
 int b200_paged_attention(const b200_paged_attn_args* args, void* stream);
 
+/* Allocation-free variant of b200_paged_attention.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, routing, kernels and results as b200_paged_attention, except that
+ * args->workspace / workspace_bytes are ignored: the split-KV partials live in a file-scope device array of
+ * B200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  A call whose split-KV plan needs
+ * more (b200_paged_attention_workspace_bytes(args) > B200_STATIC_SCRATCH_BYTES) is rejected with
+ * B200_ERR_INVALID_ARGUMENT; single-pass plans need none.  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine).  All calls on a device share the one array, which keeps the last call's contents
+ * (nothing in it has to start at zero: each call writes every slot it reads); calls that overlap on the GPU --
+ * different streams, or graph branches without a dependency -- RACE on it and must be serialised by the caller. */
+#define B200_STATIC_SCRATCH_BYTES (32u << 20)
+int b200_paged_attention_static_scratch(const b200_paged_attn_args* args, void* stream);
+
 /* ---------------------------------------------------------------------------
  * Affine group-quantized linears -- replace the MLX calls the reference makes:
  * `mx.quantized_matmul(x, w, scales, biases, transpose=True, group_size, bits)`

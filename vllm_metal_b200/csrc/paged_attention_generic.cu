@@ -425,3 +425,52 @@ extern "C" int b200_paged_attention(const b200_paged_attn_args* a, void* stream)
   if (wsp) rc = launch_split_reduce(*a, ws, st);
   return rc;
 }
+
+// ---- allocation-free variant (no counterpart in the reference) -------
+// Split-KV scratch in a file-scope device array for callers that cannot allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the array until exit.  In host
+// code `g_static_scratch` is only the host-side stand-in of the symbol: its device address is looked up once per
+// device, with that device current, through cudaGetSymbolAddress.
+namespace b200 {
+constexpr size_t kStaticScratchBytes = (size_t)B200_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+static int static_scratch_ptr(void** out) {
+  static void* ptr_of_dev[16] = {nullptr};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 16) return set_error(B200_ERR_UNSUPPORTED, "static scratch: device index %d out of range", dev);
+  if (ptr_of_dev[dev] == nullptr) {
+    void* p = nullptr;
+    B200_CUDA_OK(cudaGetSymbolAddress(&p, g_static_scratch));
+    if (p == nullptr) return set_error(B200_ERR_CUDA, "static scratch: cudaGetSymbolAddress returned a null address");
+    ptr_of_dev[dev] = p;
+  }
+  *out = ptr_of_dev[dev];
+  return B200_OK;
+}
+}  // namespace b200
+
+extern "C" int b200_paged_attention_static_scratch(const b200_paged_attn_args* a, void* stream) {
+  using namespace b200;
+  int rc = validate(a);
+  if (rc != B200_OK) return rc;
+  if (a->num_q_tokens == 0 || a->num_seqs == 0) return B200_OK;
+  b200_paged_attn_args c = *a;  // the caller's workspace fields are ignored
+  c.workspace = nullptr;
+  c.workspace_bytes = 0;
+  const size_t need = b200_paged_attention_workspace_bytes(&c);  // 0 when the plan is a single pass
+  if (need > kStaticScratchBytes)
+    return set_error(B200_ERR_INVALID_ARGUMENT,
+                     "paged_attention_static_scratch: this call's split-KV plan needs %zu scratch bytes, the built-in "
+                     "array holds %zu (B200_STATIC_SCRATCH_BYTES); use b200_paged_attention with a caller workspace",
+                     need, kStaticScratchBytes);
+  void* scratch = nullptr;
+  rc = static_scratch_ptr(&scratch);
+  if (rc != B200_OK) return rc;
+  // Nothing in the scratch has to start at zero: the partition kernels write every (row, head, partition) slot the
+  // merge kernel reads in the same call, so the previous call's contents are never observed.
+  c.workspace = scratch;
+  c.workspace_bytes = kStaticScratchBytes;
+  return b200_paged_attention(&c, stream);
+}

@@ -94,6 +94,7 @@ EXPORTED_SYMBOLS = (
     "b200_paged_attention_workspace_bytes",
     "b200_paged_attention_num_launches",
     "b200_paged_attention",
+    "b200_paged_attention_static_scratch",
     "b200_qlinear",
     "b200_qlinear_prepack",
     "b200_qlinear_prepacked",
@@ -165,6 +166,7 @@ def load_library() -> ctypes.CDLL:
     lib.b200_paged_attention_workspace_bytes.argtypes = [ctypes.POINTER(PagedAttnArgs)]
     lib.b200_paged_attention_num_launches.argtypes = [ctypes.POINTER(PagedAttnArgs)]
     lib.b200_paged_attention.argtypes = [ctypes.POINTER(PagedAttnArgs), ctypes.c_void_p]
+    lib.b200_paged_attention_static_scratch.argtypes = [ctypes.POINTER(PagedAttnArgs), ctypes.c_void_p]
     vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
     lib.b200_reshape_and_cache.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i32, vp]
     lib.b200_copy_blocks.argtypes = [vp, vp, vp, vp, i32, i64, i64, vp]
