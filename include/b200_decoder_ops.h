@@ -112,6 +112,22 @@ int b200_allreduce_add_rmsnorm(void* x, void* residual, const void* weight, void
                                void* const* flag_ptrs, void* epoch, int rank, int world,
                                int64_t half_bytes, int grid, int twoshot, void* stream);
 
+/* Push form of the fused tensor-parallel epilogue with a ROW-SHARDED residual stream: row r belongs to rank
+ * r % world.  Non-owners store their partial of r into the owner's packet buffer; the owner adds the partials in rank
+ * order (the arithmetic of b200_allreduce_add_rmsnorm, bit for bit), adds its residual row in place, norms, and
+ * stores the normed row into every peer's buffer.  On return (stream order) `out` holds every normed row on every
+ * rank; `residual` is updated -- and must have been valid -- on the rows this rank owns ONLY (the other rows are
+ * neither read nor written: a caller keeps using this entry point, or re-materialises the stream, consistently
+ * within a forward pass).  Packets are 8-byte words {4 bytes of data, call epoch}: no flag arrays, no fences, two
+ * one-way NVLink trips per call.
+ *   box_ptrs[r] : rank r's packet buffer of box_bytes, zero-initialised (own pointer at [rank], peers mapped);
+ *                 box_bytes >= 4 * ceil(rows / world) * world * hidden * 4 (2 parities x inbox + outbox)
+ *   epoch       : local uint32 [grid], zero-initialised, used by this entry point only; grid % world == 0
+ * Every rank must call it in the same order with the same rows / hidden. */
+int b200_allreduce_add_rmsnorm_push(const void* x, void* residual, const void* weight, void* out, int rows,
+                                    int hidden, float eps, int dtype, int out_dtype, void* const* box_ptrs,
+                                    int64_t box_bytes, void* epoch, int rank, int world, int grid, void* stream);
+
 /* Greedy token of a vocab-parallel head (lm_head column-parallel over the vocabulary +
  * a tiny (max, index) exchange instead of gathering logits).  `logits` [rows, shard_vocab] is this rank's slice
  * (global token id = vocab_offset + column); out[r] = index of the first maximum over ALL ranks' slices -- what

@@ -131,6 +131,21 @@ def main() -> None:
             ok = False
             print(f"[rank {rank}] two-shot fused add+norm differs from one-shot rows={rows} hidden={hidden}: out max diff "
                   f"{(got2.float() - got.float()).abs().max().item()}, residual equal {torch.equal(res2, res)}", flush=True)
+        # push form, row-sharded residual: every normed row = the pull form's bits on every rank; the residual is
+        # updated on the rows this rank owns (r % world) and left alone elsewhere
+        for _ in range(3):
+            res3 = res0.clone()
+            got3 = ar.fused_add_rmsnorm_sharded(part.clone(), res3, w, 1e-5, odt)
+        torch.cuda.synchronize()
+        assert got3 is not None, (rows, hidden)
+        mine_rows = torch.arange(rows, device=dev) % world == rank
+        if not (torch.equal(got3, got) and torch.equal(res3[mine_rows], res[mine_rows])
+                and torch.equal(res3[~mine_rows], res0[~mine_rows])):
+            ok = False
+            print(f"[rank {rank}] push fused add+norm differs rows={rows} hidden={hidden} f16={f16}: out max diff "
+                  f"{(got3.float() - got.float()).abs().max().item()}, owned residual equal "
+                  f"{torch.equal(res3[mine_rows], res[mine_rows])}, other rows untouched "
+                  f"{torch.equal(res3[~mine_rows], res0[~mine_rows])}", flush=True)
         same_map = hidden in (4096, 8192)
         good = torch.equal(res, res_ref) and (torch.equal(got, want) if same_map else
                                                bool((got.float() - want.float()).abs().max() <= 2.0 ** -6 * want.float().abs().max()))
@@ -145,6 +160,9 @@ def main() -> None:
           "nvlink one-shot fused with residual add + RMSNorm")
     timed(lambda t: ar.fused_add_rmsnorm(t, resid, wn, 1e-5, torch.float16, twoshot=True),
           "nvlink two-shot (owner reduces + norms, results gathered) fused with residual add + RMSNorm")
+
+    timed(lambda t: ar.fused_add_rmsnorm_sharded(t, resid, wn, 1e-5, torch.float16),
+          "nvlink push (LL packets, row-sharded residual) fused with residual add + RMSNorm")
 
     def two_step(t):
         ar(t)

@@ -312,6 +312,189 @@ static int launch_fused(const FusedParams& f, int grid, cudaStream_t st) {
   return check_launch("allreduce_add_rmsnorm_kernel");
 }
 
+// ---- push form: reduce-scatter + norm on the row's owner, all-gather of the normed rows (LL packets) ------------
+// The pull kernels above pay, per call, a release fence + a flag store + the peers' acquire polls + NVLink
+// round-trip loads (24 us at 8 ranks, where the 3.5 MiB of pulls is also latency-, not bandwidth-, limited).  Here
+// nothing is pulled and nothing is fenced.  Row r belongs to rank r % WORLD, which is also the only rank that keeps
+// the residual stream of that row (the stream is row-sharded between the fused calls of a forward pass; every rank
+// still gets every NORMED row, which is all the linears that follow consume):
+//   phase 1  a rank that does not own row r stores its partial of r straight into the owner's inbox
+//   owner    polls its inbox (local memory) until the W-1 partials of r are there, adds them to its own in RANK
+//            ORDER in fp32, rounds to T, adds the residual, norms -- the arithmetic of the kernels above, bit for
+//            bit -- and stores the normed row into every peer's outbox
+//   phase 2  the other ranks poll their outbox (local memory) and copy the row to `out`
+// Every store is an LL packet: 16 bytes = two 8-byte words {4 bytes of data, the call's epoch}.  A naturally
+// aligned 8-byte scalar word is single-copy atomic, so a word whose upper half shows the epoch carries this call's
+// data: the data is its own flag.  Wire bytes are 2x the payload, but the payload is 1/4 of the pull form's at 8
+// ranks (a rank sends 7/8 of [M, hidden] once as partials and 1/8 of it seven times as results) and the latency
+// chain is two one-way NVLink trips.  Inbox / outbox alternate by epoch parity; a rank can be at most one call ahead
+// of a peer (it needs the peer's phase-2 rows of call n to leave call n, and the peer sends those only after it
+// has consumed every phase-1 packet of call n), so a packet still being polled is never overwritten.
+struct LLParams {
+  const void* x;         // [rows, hidden] this rank's partial
+  void* residual;        // [rows, hidden] in place; only rows this rank owns are read and written
+  const void* weight;    // [hidden] or null
+  void* out;             // [rows, hidden]
+  char* box[kMaxWorld];  // every rank's packet buffer (peer-mapped): [2 parities][inbox | outbox], `phase_bytes` each
+  uint32_t* epoch;       // local [grid]
+  int64_t phase_bytes;
+  int rows, hidden, rank, world;
+  float eps;
+  int out_f16;
+};
+
+__device__ __forceinline__ void ll_store(char* dst, const uint4& v, uint32_t e) {
+  const uint64_t f = (uint64_t)e << 32;
+  asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1,%2};" ::"l"(dst), "l"(f | v.x), "l"(f | v.y) : "memory");
+  asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1,%2};" ::"l"(dst + 16), "l"(f | v.z), "l"(f | v.w) : "memory");
+}
+// one probe of a 32-byte packet pair; true when all four words carry epoch e
+__device__ __forceinline__ bool ll_probe(const char* src, uint32_t e, uint4& v) {
+  uint64_t a, b, c, d;
+  asm volatile("ld.relaxed.sys.global.v2.u64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "l"(src) : "memory");
+  asm volatile("ld.relaxed.sys.global.v2.u64 {%0,%1}, [%2];" : "=l"(c), "=l"(d) : "l"(src + 16) : "memory");
+  v = make_uint4((uint32_t)a, (uint32_t)b, (uint32_t)c, (uint32_t)d);
+  return (uint32_t)(a >> 32) == e && (uint32_t)(b >> 32) == e && (uint32_t)(c >> 32) == e && (uint32_t)(d >> 32) == e;
+}
+
+template <typename T, int WORLD>
+__global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_ll_kernel(const LLParams f) {
+  pdl_trigger();
+  pdl_wait();
+  constexpr int NV = 2;  // vectors per thread: hidden <= 512 * 8 * 2
+  __shared__ float red[32];
+  const int b = blockIdx.x, G = gridDim.x;  // G % WORLD == 0: every row of a CTA has the same owner
+  const uint32_t e = f.epoch[b] + 1u;
+  const int nvec = f.hidden >> 3;
+  const int owner = b % WORLD;
+  const int64_t par_off = (int64_t)(e & 1u) * 2 * f.phase_bytes;
+  const uint4* xv = reinterpret_cast<const uint4*>(f.x);
+  uint4* ov = reinterpret_cast<uint4*>(f.out);
+  // inbox slot of (row r, source s) on r's owner: packet row (r / WORLD) * WORLD + s; outbox slot of row r: packet row r
+  if (owner != f.rank) {
+    // ---- phase 1: my partial rows go to their owner ----
+    char* inbox = f.box[owner] + par_off;
+    for (int r = b; r < f.rows; r += G) {
+      const int64_t slot = ((int64_t)(r / WORLD) * WORLD + f.rank) * nvec;
+      for (int v = threadIdx.x; v < nvec; v += kThreads) ll_store(inbox + (slot + v) * 32, xv[(int64_t)r * nvec + v], e);
+    }
+    // ---- phase 2: the normed rows come back ----
+    const char* outbox = f.box[f.rank] + par_off + f.phase_bytes;
+    for (int r = b; r < f.rows; r += G) {
+      for (int v = threadIdx.x; v < nvec; v += kThreads) {
+        const int64_t idx = (int64_t)r * nvec + v;
+        uint4 c;
+        uint32_t spins = 0;
+        while (!ll_probe(outbox + idx * 32, e, c)) {
+          if (++spins > (1u << 27)) __trap();  // a dead peer must fault this rank, not hang the box
+        }
+        ov[idx] = c;
+      }
+    }
+  } else {
+    const char* inbox = f.box[f.rank] + par_off;
+    uint4* rv = reinterpret_cast<uint4*>(f.residual);
+    const uint4* wv = reinterpret_cast<const uint4*>(f.weight);
+    for (int r = b; r < f.rows; r += G) {
+      float h[NV][8];
+      float ss = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const int v = threadIdx.x + j * kThreads;
+        if (v < nvec) {
+          const int64_t idx = (int64_t)r * nvec + v;
+          uint4 part[WORLD];
+          bool have[WORLD];
+          const uint4 own = xv[idx];
+#pragma unroll
+          for (int q = 0; q < WORLD; ++q) {
+            have[q] = q == f.rank;
+            if (q == f.rank) part[q] = own;
+          }
+          const int64_t slot0 = (int64_t)(r / WORLD) * WORLD * nvec + v;
+          uint32_t spins = 0;
+          bool all;
+          do {  // every outstanding packet is probed in one batch: one local-memory latency per round, not W-1
+            all = true;
+#pragma unroll
+            for (int q = 0; q < WORLD; ++q) {
+              if (!have[q]) {
+                uint4 t;
+                if (ll_probe(inbox + (slot0 + (int64_t)q * nvec) * 32, e, t)) {
+                  part[q] = t;
+                  have[q] = true;
+                } else {
+                  all = false;
+                }
+              }
+            }
+            if (++spins > (1u << 27)) __trap();
+          } while (!all);
+          float acc[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+          for (int q = 0; q < WORLD; ++q) accumulate<T>(acc, part[q]);
+          const uint4 res = rv[idx];
+          const T* re = reinterpret_cast<const T*>(&res);
+          uint4 hn;
+          T* he = reinterpret_cast<T*>(&hn);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float a = to_float(from_float<T>(acc[i]));  // the all-reduce's own rounding
+            he[i] = from_float<T>(a + to_float(re[i]));       // residual stream kept in T
+            h[j][i] = to_float(he[i]);
+            ss += h[j][i] * h[j][i];
+          }
+          rv[idx] = hn;
+        }
+      }
+      ss = block_sum_512(ss, red);
+      const float inv = rsqrtf(ss / (float)f.hidden + f.eps);
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const int v = threadIdx.x + j * kThreads;
+        if (v < nvec) {
+          uint4 c;
+          T* ce = reinterpret_cast<T*>(&c);
+          if (wv) {
+            const uint4 w = __ldg(wv + v);
+            const T* we = reinterpret_cast<const T*>(&w);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ce[i] = from_float<T>(h[j][i] * inv * to_float(we[i]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ce[i] = from_float<T>(h[j][i] * inv);
+          }
+          if (f.out_f16) {
+            __half* hh = reinterpret_cast<__half*>(&c);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) hh[i] = __float2half_rn(fminf(fmaxf(to_float(ce[i]), -65504.f), 65504.f));
+          }
+          const int64_t idx = (int64_t)r * nvec + v;
+#pragma unroll
+          for (int q = 0; q < WORLD; ++q)
+            if (q != f.rank) ll_store(f.box[q] + par_off + f.phase_bytes + idx * 32, c, e);
+          ov[idx] = c;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) f.epoch[b] = e;
+}
+
+template <typename T>
+static int launch_ll(const LLParams& f, int grid, cudaStream_t st) {
+  switch (f.world) {
+    case 2: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 2>, dim3(grid), dim3(kThreads), 0, st, f)); break;
+    case 4: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 4>, dim3(grid), dim3(kThreads), 0, st, f)); break;
+    case 8: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 8>, dim3(grid), dim3(kThreads), 0, st, f)); break;
+    default: return set_error(B200_ERR_INVALID_ARGUMENT, "allreduce: world size must be 2, 4 or 8, got %d", f.world);
+  }
+  return check_launch("allreduce_add_rmsnorm_ll_kernel");
+}
+
 // ---- vocab-parallel greedy head: (max logit, token) exchange (lm_head row) ----------------
 // Every rank holds the logits of its own vocab slice; the greedy token is the arg-max over all slices.  Each rank
 // PUSHES its per-row winner (value, global index) into every peer's slot table with two 8-byte stores that carry
@@ -385,6 +568,46 @@ __global__ void __launch_bounds__(32) argmax_exchange_kernel(const ArgmaxXParams
 }  // namespace b200
 
 extern "C" {
+
+int b200_allreduce_add_rmsnorm_push(const void* x, void* residual, const void* weight, void* out, int rows, int hidden,
+                                    float eps, int dtype, int out_dtype, void* const* box_ptrs, int64_t box_bytes,
+                                    void* epoch, int rank, int world, int grid, void* stream) {
+  using namespace b200;
+  if (rows == 0) return B200_OK;
+  B200_CHECK_ARG(x && residual && out && box_ptrs && epoch && rows > 0, "allreduce_add_rmsnorm_push: bad arguments");
+  B200_CHECK_ARG(dtype == B200_BF16 || dtype == B200_F16, "allreduce_add_rmsnorm_push: dtype must be bf16 or fp16");
+  B200_CHECK_ARG(out_dtype == dtype || (out_dtype == B200_F16 && dtype == B200_BF16),
+                 "allreduce_add_rmsnorm_push: out dtype must be the input dtype, or fp16 for bf16 input");
+  B200_CHECK_ARG(hidden % 8 == 0 && hidden <= ar::kThreads * 8 * 2,
+                 "allreduce_add_rmsnorm_push: hidden %d must be a multiple of 8, <= %d", hidden, ar::kThreads * 8 * 2);
+  B200_CHECK_ARG(rank >= 0 && rank < world && world <= ar::kMaxWorld, "allreduce: rank %d of world %d", rank, world);
+  B200_CHECK_ARG(grid > 0 && grid <= 1024 && grid % world == 0,
+                 "allreduce_add_rmsnorm_push: grid %d must be a positive multiple of the world size %d", grid, world);
+  B200_CHECK_ARG((((uintptr_t)x | (uintptr_t)residual | (uintptr_t)out | (uintptr_t)weight) & 15) == 0,
+                 "allreduce_add_rmsnorm_push: pointers must be 16-byte aligned");
+  const int64_t phase_bytes = (box_bytes / 4) & ~(int64_t)255;  // [2 parities][inbox | outbox]
+  const int64_t packet_rows = ((int64_t)rows + world - 1) / world * world;
+  B200_CHECK_ARG(packet_rows * hidden * 4 <= phase_bytes,
+                 "allreduce_add_rmsnorm_push: %d rows x %d need %lld packet bytes per phase, the buffer has %lld", rows,
+                 hidden, (long long)(packet_rows * hidden * 4), (long long)phase_bytes);
+  ar::LLParams f{};
+  f.x = x;
+  f.residual = residual;
+  f.weight = weight;
+  f.out = out;
+  for (int r = 0; r < world; ++r) f.box[r] = reinterpret_cast<char*>(box_ptrs[r]);
+  f.epoch = reinterpret_cast<uint32_t*>(epoch);
+  f.phase_bytes = phase_bytes;
+  f.rows = rows;
+  f.hidden = hidden;
+  f.rank = rank;
+  f.world = world;
+  f.eps = eps;
+  f.out_f16 = (out_dtype == B200_F16 && dtype == B200_BF16) ? 1 : 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_BF16) return ar::launch_ll<__nv_bfloat16>(f, grid, st);
+  return ar::launch_ll<__half>(f, grid, st);
+}
 
 int b200_argmax_vocab_parallel(const void* logits, int32_t* out, int rows, int shard_vocab, int64_t stride, int dtype,
                                int vocab_offset, void* const* slot_ptrs, void* epoch, int rank, int world,

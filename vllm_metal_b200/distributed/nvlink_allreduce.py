@@ -54,6 +54,14 @@ class NVLinkAllReduce:
                                                    ctypes.c_int64, ctypes.c_int, ctypes.c_int,
                                                    ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p, ctypes.c_int,
                                                    ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+        lib.b200_allreduce_add_rmsnorm_push.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                        ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_int,
+                                                        ctypes.c_int, ctypes.POINTER(ctypes.c_void_p), ctypes.c_int64,
+                                                        ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                        ctypes.c_void_p]
+        # push form with a row-sharded residual stream (fused_add_rmsnorm_sharded); B200_ALLREDUCE_PUSH=0 keeps the
+        # decoder on the pull kernel
+        self.push = os.environ.get("B200_ALLREDUCE_PUSH", "1") != "0"
         self.half_bytes = (int(max_bytes) + 255) // 256 * 256
         self.grid = int(grid)
         self.max_rows = 1024  # rows of one vocab-parallel arg-max call (slot table: 2 parities x world x rows x 16 B)
@@ -62,21 +70,28 @@ class NVLinkAllReduce:
             self._own_symm, h_symm = self._alloc(6 * self.half_bytes)
             self._own_flags, h_flags = self._alloc(2 * self.grid * self.world * 4)
             self._own_slots, h_slots = self._alloc(2 * self.world * self.max_rows * 16)
+            # packets are 2x the payload; [2 parities][inbox | outbox], rows rounded up to the world size
+            self.box_bytes = 4 * (2 * self.half_bytes + self.world * 8192 * 4 + 256)
+            self._own_box, h_box = self._alloc(self.box_bytes)
+            self.push_epoch = torch.zeros((self.grid,), dtype=torch.int32, device=self.device)
             self.epoch = torch.zeros((self.grid,), dtype=torch.int32, device=self.device)
             self.argmax_epoch = torch.zeros((self.max_rows,), dtype=torch.int32, device=self.device)
             handles: list = [None] * self.world
-            dist.all_gather_object(handles, (h_symm, h_flags, h_slots), group=group)
+            dist.all_gather_object(handles, (h_symm, h_flags, h_slots, h_box), group=group)
             self._opened: list[int] = []
-            symm, flags, slots = [], [], []
-            for r, (hs, hf, hl) in enumerate(handles):
+            symm, flags, slots, boxes = [], [], [], []
+            for r, (hs, hf, hl, hb) in enumerate(handles):
                 if r == self.rank:
                     symm.append(self._own_symm)
                     flags.append(self._own_flags)
                     slots.append(self._own_slots)
+                    boxes.append(self._own_box)
                 else:
                     symm.append(self._open(hs))
                     flags.append(self._open(hf))
                     slots.append(self._open(hl))
+                    boxes.append(self._open(hb))
+            self._boxes = (ctypes.c_void_p * self.world)(*boxes)
             self._symm = (ctypes.c_void_p * self.world)(*symm)
             self._flags = (ctypes.c_void_p * self.world)(*flags)
             self._slots = (ctypes.c_void_p * self.world)(*slots)
@@ -137,6 +152,33 @@ class NVLinkAllReduce:
         self.calls += 1
         return out.reshape(x.shape)
 
+    def fused_add_rmsnorm_sharded(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor | None, eps: float,
+                                  out_dtype: torch.dtype | None = None) -> torch.Tensor | None:
+        """Push form of ``fused_add_rmsnorm`` with a ROW-SHARDED residual stream: returns ``rms_norm(residual +
+        allreduce(x)) * weight`` for every row, the same bits as ``fused_add_rmsnorm``, but ``residual`` is read and
+        updated only on the rows this rank owns (row r -> rank r % world); the other rows are left alone.  A forward
+        pass must use this form for all of its sums or for none.  ``None`` when the shape does not qualify."""
+        hidden = x.shape[-1]
+        x2, r2 = x.reshape(-1, hidden), residual.reshape(-1, hidden)
+        rows = x2.shape[0]
+        if not self.push or self.grid % self.world or rows > 4 * self.grid:
+            return None
+        packet_rows = (rows + self.world - 1) // self.world * self.world
+        if (x.dtype not in (torch.bfloat16, torch.float16) or not x2.is_contiguous() or not r2.is_contiguous()
+                or hidden % 8 or hidden > 8192 or packet_rows * hidden * 4 > (self.box_bytes // 4) // 256 * 256
+                or x2.data_ptr() % 16 or r2.data_ptr() % 16
+                or (weight is not None and (weight.dtype != x.dtype or weight.data_ptr() % 16))):
+            return None
+        out = torch.empty(x2.shape, dtype=out_dtype or x.dtype, device=x.device)
+        rc = self.lib.b200_allreduce_add_rmsnorm_push(
+            x2.data_ptr(), r2.data_ptr(), None if weight is None else weight.data_ptr(), out.data_ptr(), rows, hidden,
+            float(eps), _DTYPE_CODE[x.dtype], _DTYPE_CODE[out.dtype], self._boxes, self.box_bytes,
+            self.push_epoch.data_ptr(), self.rank, self.world, self.grid, torch.cuda.current_stream().cuda_stream)
+        self.ops._check(rc)
+        self.ops.launches += 1
+        self.calls += 1
+        return out.reshape(x.shape)
+
     def argmax_vocab_parallel(self, logits: torch.Tensor, vocab_offset: int, out: torch.Tensor | None = None) -> torch.Tensor:
         """Greedy tokens of a vocab-parallel head: ``logits`` [rows, vocab / world] is this rank's slice starting at
         token ``vocab_offset``; returns int32 [rows], the arg-max over every rank's slice (lowest id on ties), the
@@ -165,7 +207,7 @@ class NVLinkAllReduce:
         for p in self._opened:
             self.lib.b200_ipc_close(p)
         self._opened = []
-        for p in (self._own_symm, self._own_flags, self._own_slots):
+        for p in (self._own_symm, self._own_flags, self._own_slots, self._own_box):
             if p:
                 self.lib.b200_ipc_free(p)
-        self._own_symm = self._own_flags = self._own_slots = 0
+        self._own_symm = self._own_flags = self._own_slots = self._own_box = 0

@@ -221,6 +221,14 @@ class Model(nn.Module):
         otherwise all-reduce, then the fused add + norm."""
         if part is None:  # first layer: nothing to add yet
             return norm(h, out_f16=self._f16_acts)
+        # push form first: the residual stream stays valid only on the rows this rank owns (r % world) -- nothing
+        # but these sums reads it, and every sum of a forward pass takes the same branch (same shapes throughout)
+        sharded = getattr(self._allreduce, "fused_add_rmsnorm_sharded", None) if self.world > 1 else None
+        if sharded is not None:
+            f16 = self._f16_acts and part.dtype == torch.bfloat16
+            x = sharded(part, h, norm.weight, norm.eps, torch.float16 if f16 else None)
+            if x is not None:
+                return x
         fused = getattr(self._allreduce, "fused_add_rmsnorm", None) if self.world > 1 else None
         if fused is not None:
             f16 = self._f16_acts and part.dtype == torch.bfloat16

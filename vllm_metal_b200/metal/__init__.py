@@ -124,6 +124,7 @@ EXPORTED_SYMBOLS = (
     "b200_ipc_free",
     "b200_allreduce_sum",
     "b200_allreduce_add_rmsnorm",
+    "b200_allreduce_add_rmsnorm_push",
     "b200_argmax_vocab_parallel",
 )
 
