@@ -122,7 +122,7 @@ int b200_allreduce_add_rmsnorm(void* x, void* residual, const void* weight, void
  * one-way NVLink trips per call.
  *   box_ptrs[r] : rank r's packet buffer of box_bytes, zero-initialised (own pointer at [rank], peers mapped);
  *                 box_bytes >= 4 * ceil(rows / world) * world * hidden * 4 (2 parities x inbox + outbox)
- *   epoch       : local uint32 [grid], zero-initialised, used by this entry point only; grid % world == 0
+ *   epoch       : local uint32 [grid], zero-initialised, used by this entry point only; grid % world == 0 (clusters of `world` CTAs)
  * Every rank must call it in the same order with the same rows / hidden. */
 int b200_allreduce_add_rmsnorm_push(const void* x, void* residual, const void* weight, void* out, int rows,
                                     int hidden, float eps, int dtype, int out_dtype, void* const* box_ptrs,

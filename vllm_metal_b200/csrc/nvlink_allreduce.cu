@@ -357,82 +357,81 @@ __device__ __forceinline__ bool ll_probe(const char* src, uint32_t e, uint4& v) 
   return (uint32_t)(a >> 32) == e && (uint32_t)(b >> 32) == e && (uint32_t)(c >> 32) == e && (uint32_t)(d >> 32) == e;
 }
 
+// Work split: every CTA of every rank takes an equal share of all three steps, so no single SM has to issue a whole
+// row's packets to W-1 peers (a first version with one CTA per owned row spent its time there: 15.4 us at 8 ranks).
+// Clusters of W CTAs own a row together: cluster CTA c runs threads [c * 512 / W, (c + 1) * 512 / W) of the pull kernel's
+// 512-thread row mapping (same vectors per thread, same warp butterflies), the 16 warp sums of squares meet in
+// every CTA's shared memory through DSMEM and are added in the pull kernel's order -- the same bits.
+// The cluster size is the world size: with rows == grid every rank owns grid / W rows = its number of clusters, one
+// row per cluster at 2, 4 and 8 ranks alike (a fixed 8 made 2-rank runs walk 4 rows per cluster: 14.6 us vs 9.3).
+constexpr int kPushThreads = 256;
+
 template <typename T, int WORLD>
-__global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_ll_kernel(const LLParams f) {
+__global__ void __cluster_dims__(WORLD, 1, 1) __launch_bounds__(kPushThreads)
+allreduce_add_rmsnorm_ll_kernel(const LLParams f) {
+  constexpr int kPushCluster = WORLD;
+  constexpr int kPushOwn = kThreads / kPushCluster;  // threads of a CTA that do the owner step (256 / 128 / 64)
+  static_assert(kPushOwn <= kPushThreads && kPushOwn % 32 == 0, "owner threads");
   pdl_trigger();
   pdl_wait();
-  constexpr int NV = 2;  // vectors per thread: hidden <= 512 * 8 * 2
-  __shared__ float red[32];
-  const int b = blockIdx.x, G = gridDim.x;  // G % WORLD == 0: every row of a CTA has the same owner
+  constexpr int NV = 2;  // vectors per (pull-kernel) thread: hidden <= 512 * 8 * 2
+  __shared__ float red[2][kThreads / 32];
+  const int b = blockIdx.x, G = gridDim.x;
+  const int c = b % kPushCluster, cl = b / kPushCluster, ncl = G / kPushCluster;  // clusters span x: c = cluster rank
   const uint32_t e = f.epoch[b] + 1u;
   const int nvec = f.hidden >> 3;
-  const int owner = b % WORLD;
   const int64_t par_off = (int64_t)(e & 1u) * 2 * f.phase_bytes;
   const uint4* xv = reinterpret_cast<const uint4*>(f.x);
   uint4* ov = reinterpret_cast<uint4*>(f.out);
+  const int64_t total = (int64_t)f.rows * nvec;
   // inbox slot of (row r, source s) on r's owner: packet row (r / WORLD) * WORLD + s; outbox slot of row r: packet row r
-  if (owner != f.rank) {
-    // ---- phase 1: my partial rows go to their owner ----
-    char* inbox = f.box[owner] + par_off;
-    for (int r = b; r < f.rows; r += G) {
-      const int64_t slot = ((int64_t)(r / WORLD) * WORLD + f.rank) * nvec;
-      for (int v = threadIdx.x; v < nvec; v += kThreads) ll_store(inbox + (slot + v) * 32, xv[(int64_t)r * nvec + v], e);
-    }
-    // ---- phase 2: the normed rows come back ----
-    const char* outbox = f.box[f.rank] + par_off + f.phase_bytes;
-    for (int r = b; r < f.rows; r += G) {
-      for (int v = threadIdx.x; v < nvec; v += kThreads) {
-        const int64_t idx = (int64_t)r * nvec + v;
-        uint4 c;
-        uint32_t spins = 0;
-        while (!ll_probe(outbox + idx * 32, e, c)) {
-          if (++spins > (1u << 27)) __trap();  // a dead peer must fault this rank, not hang the box
-        }
-        ov[idx] = c;
-      }
-    }
-  } else {
-    const char* inbox = f.box[f.rank] + par_off;
-    uint4* rv = reinterpret_cast<uint4*>(f.residual);
-    const uint4* wv = reinterpret_cast<const uint4*>(f.weight);
-    for (int r = b; r < f.rows; r += G) {
-      float h[NV][8];
-      float ss = 0.f;
+
+  // ---- phase 1: my partials of the rows I do not own go to their owners ----
+  for (int64_t j = (int64_t)b * kPushThreads + threadIdx.x; j < total; j += (int64_t)G * kPushThreads) {
+    const int r = (int)(j / nvec), v = (int)(j - (int64_t)r * nvec);
+    const int o = r % WORLD;
+    if (o == f.rank) continue;
+    const int64_t slot = ((int64_t)(r / WORLD) * WORLD + f.rank) * nvec + v;
+    ll_store(f.box[o] + par_off + slot * 32, xv[j], e);
+  }
+
+  // ---- owner step: rows rank, rank + W, ...; one cluster per row ----
+  const char* inbox = f.box[f.rank] + par_off;
+  uint4* rv = reinterpret_cast<uint4*>(f.residual);
+  const uint4* wv = reinterpret_cast<const uint4*>(f.weight);
+  const int n_owned = f.rows > f.rank ? (f.rows - f.rank + WORLD - 1) / WORLD : 0;
+  const bool own_thread = threadIdx.x < kPushOwn;
+  const int ot = c * kPushOwn + threadIdx.x;  // thread id in the pull kernel's row mapping
+  int it = 0;
+  for (int i = cl; i < n_owned; i += ncl, ++it) {
+    const int r = f.rank + i * WORLD;
+    float h[NV][8];
+    float ss = 0.f;
+    if (own_thread) {
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
-        const int v = threadIdx.x + j * kThreads;
+        const int v = ot + j * kThreads;
         if (v < nvec) {
           const int64_t idx = (int64_t)r * nvec + v;
           uint4 part[WORLD];
-          bool have[WORLD];
           const uint4 own = xv[idx];
-#pragma unroll
-          for (int q = 0; q < WORLD; ++q) {
-            have[q] = q == f.rank;
-            if (q == f.rank) part[q] = own;
-          }
           const int64_t slot0 = (int64_t)(r / WORLD) * WORLD * nvec + v;
           uint32_t spins = 0;
           bool all;
-          do {  // every outstanding packet is probed in one batch: one local-memory latency per round, not W-1
+          do {  // all W-1 packets are probed in one batch: one local-memory latency per round, not W-1
             all = true;
 #pragma unroll
             for (int q = 0; q < WORLD; ++q) {
-              if (!have[q]) {
-                uint4 t;
-                if (ll_probe(inbox + (slot0 + (int64_t)q * nvec) * 32, e, t)) {
-                  part[q] = t;
-                  have[q] = true;
-                } else {
-                  all = false;
-                }
-              }
+              uint4 t = own;
+              const bool okq = q == f.rank || ll_probe(inbox + (slot0 + (int64_t)q * nvec) * 32, e, t);
+              part[q] = t;
+              all = all && okq;
             }
-            if (++spins > (1u << 27)) __trap();
+            if (++spins > (1u << 27)) __trap();  // a dead peer must fault this rank, not hang the box
           } while (!all);
           float acc[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+          for (int k = 0; k < 8; ++k) acc[k] = 0.f;
 #pragma unroll
           for (int q = 0; q < WORLD; ++q) accumulate<T>(acc, part[q]);
           const uint4 res = rv[idx];
@@ -440,45 +439,75 @@ __global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_ll_kernel(cons
           uint4 hn;
           T* he = reinterpret_cast<T*>(&hn);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float a = to_float(from_float<T>(acc[i]));  // the all-reduce's own rounding
-            he[i] = from_float<T>(a + to_float(re[i]));       // residual stream kept in T
-            h[j][i] = to_float(he[i]);
-            ss += h[j][i] * h[j][i];
+          for (int k = 0; k < 8; ++k) {
+            const float a = to_float(from_float<T>(acc[k]));  // the all-reduce's own rounding
+            he[k] = from_float<T>(a + to_float(re[k]));       // residual stream kept in T
+            h[j][k] = to_float(he[k]);
+            ss += h[j][k] * h[j][k];
           }
           rv[idx] = hn;
         }
       }
-      ss = block_sum_512(ss, red);
-      const float inv = rsqrtf(ss / (float)f.hidden + f.eps);
+      // block_sum_512 of the pull kernel, spread over the cluster: warp butterfly, 16 warp sums into every CTA
+      ss = warp_sum(ss);
+      if ((threadIdx.x & 31) == 0) {
+        const uint32_t local = (uint32_t)__cvta_generic_to_shared(&red[it & 1][ot >> 5]);
+#pragma unroll
+        for (int q = 0; q < kPushCluster; ++q) {
+          uint32_t remote;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(q));
+          asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(ss) : "memory");
+        }
+      }
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (own_thread) {
+      const int lane = threadIdx.x & 31;
+      float t = lane < (kThreads >> 5) ? red[it & 1][lane] : 0.f;
+      t = warp_sum(t);
+      const float inv = rsqrtf(t / (float)f.hidden + f.eps);
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
-        const int v = threadIdx.x + j * kThreads;
+        const int v = ot + j * kThreads;
         if (v < nvec) {
-          uint4 c;
-          T* ce = reinterpret_cast<T*>(&c);
+          uint4 cvec;
+          T* ce = reinterpret_cast<T*>(&cvec);
           if (wv) {
             const uint4 w = __ldg(wv + v);
             const T* we = reinterpret_cast<const T*>(&w);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) ce[i] = from_float<T>(h[j][i] * inv * to_float(we[i]));
+            for (int k = 0; k < 8; ++k) ce[k] = from_float<T>(h[j][k] * inv * to_float(we[k]));
           } else {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) ce[i] = from_float<T>(h[j][i] * inv);
+            for (int k = 0; k < 8; ++k) ce[k] = from_float<T>(h[j][k] * inv);
           }
           if (f.out_f16) {
-            __half* hh = reinterpret_cast<__half*>(&c);
+            __half* hh = reinterpret_cast<__half*>(&cvec);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) hh[i] = __float2half_rn(fminf(fmaxf(to_float(ce[i]), -65504.f), 65504.f));
+            for (int k = 0; k < 8; ++k) hh[k] = __float2half_rn(fminf(fmaxf(to_float(ce[k]), -65504.f), 65504.f));
           }
           const int64_t idx = (int64_t)r * nvec + v;
 #pragma unroll
           for (int q = 0; q < WORLD; ++q)
-            if (q != f.rank) ll_store(f.box[q] + par_off + f.phase_bytes + idx * 32, c, e);
-          ov[idx] = c;
+            if (q != f.rank) ll_store(f.box[q] + par_off + f.phase_bytes + idx * 32, cvec, e);
+          ov[idx] = cvec;
         }
       }
     }
+  }
+
+  // ---- phase 2: the normed rows of the other owners arrive in my outbox ----
+  const char* outbox = f.box[f.rank] + par_off + f.phase_bytes;
+  for (int64_t j = (int64_t)b * kPushThreads + threadIdx.x; j < total; j += (int64_t)G * kPushThreads) {
+    const int r = (int)(j / nvec);
+    if (r % WORLD == f.rank) continue;
+    uint4 cvec;
+    uint32_t spins = 0;
+    while (!ll_probe(outbox + j * 32, e, cvec)) {
+      if (++spins > (1u << 27)) __trap();
+    }
+    ov[j] = cvec;
   }
   __syncthreads();
   if (threadIdx.x == 0) f.epoch[b] = e;
@@ -487,9 +516,9 @@ __global__ void __launch_bounds__(kThreads) allreduce_add_rmsnorm_ll_kernel(cons
 template <typename T>
 static int launch_ll(const LLParams& f, int grid, cudaStream_t st) {
   switch (f.world) {
-    case 2: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 2>, dim3(grid), dim3(kThreads), 0, st, f)); break;
-    case 4: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 4>, dim3(grid), dim3(kThreads), 0, st, f)); break;
-    case 8: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 8>, dim3(grid), dim3(kThreads), 0, st, f)); break;
+    case 2: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 2>, dim3(grid), dim3(kPushThreads), 0, st, f)); break;
+    case 4: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 4>, dim3(grid), dim3(kPushThreads), 0, st, f)); break;
+    case 8: B200_CUDA_OK(launch_pdl(allreduce_add_rmsnorm_ll_kernel<T, 8>, dim3(grid), dim3(kPushThreads), 0, st, f)); break;
     default: return set_error(B200_ERR_INVALID_ARGUMENT, "allreduce: world size must be 2, 4 or 8, got %d", f.world);
   }
   return check_launch("allreduce_add_rmsnorm_ll_kernel");
@@ -582,7 +611,8 @@ int b200_allreduce_add_rmsnorm_push(const void* x, void* residual, const void* w
                  "allreduce_add_rmsnorm_push: hidden %d must be a multiple of 8, <= %d", hidden, ar::kThreads * 8 * 2);
   B200_CHECK_ARG(rank >= 0 && rank < world && world <= ar::kMaxWorld, "allreduce: rank %d of world %d", rank, world);
   B200_CHECK_ARG(grid > 0 && grid <= 1024 && grid % world == 0,
-                 "allreduce_add_rmsnorm_push: grid %d must be a positive multiple of the world size %d", grid, world);
+                 "allreduce_add_rmsnorm_push: grid %d must be a positive multiple of the world size %d (CTAs per cluster)",
+                 grid, world);
   B200_CHECK_ARG((((uintptr_t)x | (uintptr_t)residual | (uintptr_t)out | (uintptr_t)weight) & 15) == 0,
                  "allreduce_add_rmsnorm_push: pointers must be 16-byte aligned");
   const int64_t phase_bytes = (box_bytes / 4) & ~(int64_t)255;  // [2 parities][inbox | outbox]
