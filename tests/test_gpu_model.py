@@ -290,3 +290,100 @@ def test_spec_verify_windows_match_expanded_and_oracle():
     for i, (g, w) in enumerate(zip(flat_got, want, strict=True)):
         if g != w:  # documented near-tie rule
             assert float(ologits[i, w] - ologits[i, g]) <= 2e-2 + 1e-2 * abs(float(ologits[i, w]))
+
+
+def test_worker_speculative_steps_emit_the_plain_greedy_stream():
+    """N4 on the device: the worker verifies scheduled drafts in window mode (``runner.verify``) and emits exactly the
+    tokens plain greedy decoding emits -- right drafts are accepted with a bonus token, wrong ones cost nothing but
+    the step (reference SpeculativeDecodeController.verify_greedy, v1/spec_decode.py:243-294)."""
+    pytest.importorskip("vllm")
+    from vllm.v1.core.sched.output import CachedRequestData, NewRequestData, SchedulerOutput
+
+    from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
+    from vllm_metal_b200.lm.decoder import PRESETS, Model
+    from vllm_metal_b200.v1.model_runner import PagedModelRunner
+    from vllm_metal_b200.v1.worker import B200Worker
+
+    args, bs, nb = PRESETS["tiny"], 16, 24
+    model = Model(args, torch.bfloat16, "cuda", seed=4)
+    rng = np.random.default_rng(12)
+    prompts = {"A": rng.integers(0, args.vocab, 37).tolist(), "B": rng.integers(0, args.vocab, 18).tolist()}
+    blocks = {"A": [5, 9, 2, 17, 11], "B": [3, 20, 7, 1]}
+
+    def make_worker():
+        cache = B200PagedKVCache(args.num_layers, args.n_kv_heads, args.head_dim, nb, bs, torch.bfloat16, "cuda")
+        w = object.__new__(B200Worker)
+        w._requests, w._pending, w._drafts, w._drafter = {}, None, {}, None
+        w.model, w.kv_cache = model, cache
+        w.model_runner = PagedModelRunner(model, cache, max_batch=4, max_model_len=8 * bs, use_cuda_graph=False)
+        return w
+
+    def sched(new, num, computed, spec):
+        new_reqs = [NewRequestData(req_id=r, prompt_token_ids=prompts[r], mm_features=[], sampling_params=None,
+                                   pooling_params=None, block_ids=(blocks[r],), num_computed_tokens=0,
+                                   lora_request=None) for r in new]
+        old = [r for r in num if r not in new]
+        cached = CachedRequestData(req_ids=old, resumed_req_ids=set(), new_token_ids=[[] for _ in old], all_token_ids={},
+                                   new_block_ids=[None for _ in old], num_computed_tokens=[computed[r] for r in old],
+                                   num_output_tokens=[1 for _ in old])
+        return SchedulerOutput(scheduled_new_reqs=new_reqs, scheduled_cached_reqs=cached, num_scheduled_tokens=num,
+                               total_num_scheduled_tokens=sum(num.values()), scheduled_spec_decode_tokens=spec,
+                               scheduled_encoder_inputs={}, num_common_prefix_blocks=[0], finished_req_ids=set(),
+                               free_encoder_mm_hashes=[])
+
+    def run(w, num, computed, new=(), spec=None):
+        w.execute_model(sched(list(new), num, computed, spec or {}))
+        out = w.sample_tokens(None)
+        return dict(zip(out.req_ids, out.sampled_token_ids, strict=True))
+
+    # plain greedy: prefill both, then 14 one-token steps
+    w = make_worker()
+    plain = {r: [] for r in prompts}
+    computed = {r: 0 for r in prompts}
+    got = run(w, {r: len(prompts[r]) for r in prompts}, computed, new=prompts)
+    for r in prompts:
+        plain[r] += got[r]
+        computed[r] = len(prompts[r])
+    for _ in range(14):
+        got = run(w, {r: 1 for r in prompts}, computed)
+        for r in prompts:
+            plain[r] += got[r]
+            computed[r] += 1
+
+    # speculative: the same requests; drafts alternate between the true continuation (accepted + bonus), a wrong
+    # first draft (rejected at once) and a right-then-wrong pair
+    w = make_worker()
+    spec_out = {r: [] for r in prompts}
+    computed = {r: 0 for r in prompts}
+    got = run(w, {r: len(prompts[r]) for r in prompts}, computed, new=prompts)
+    for r in prompts:
+        spec_out[r] += got[r]
+        computed[r] = len(prompts[r])
+    step = 0
+    while min(len(v) for v in spec_out.values()) < 12:
+        spec, num = {}, {}
+        for r in prompts:
+            done = len(spec_out[r])
+            truth = plain[r][done:done + 3]
+            if len(truth) < 3:
+                drafts = []
+            elif step % 3 == 0:
+                drafts = truth                                      # all three accepted, bonus token on top
+            elif step % 3 == 1:
+                drafts = [(truth[0] + 1) % args.vocab, truth[1]]    # wrong at once
+            else:
+                drafts = [truth[0], (truth[1] + 1) % args.vocab]    # one accepted, then the correction
+            if drafts:
+                spec[r] = drafts
+            num[r] = 1 + len(drafts)
+        got = run(w, num, computed, spec=spec)
+        for r in prompts:
+            emitted = got[r]
+            want_n = {0: 4, 1: 1, 2: 2}[step % 3] if r in spec else 1
+            assert len(emitted) == want_n, (r, step, emitted, spec.get(r))
+            spec_out[r] += emitted
+            computed[r] += len(emitted)
+        step += 1
+    for r in prompts:
+        n = min(len(spec_out[r]), len(plain[r]))
+        assert spec_out[r][:n] == plain[r][:n], r

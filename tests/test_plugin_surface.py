@@ -226,11 +226,99 @@ def test_worker_rejects_what_it_does_not_implement():
     w._requests, w._pending, w.model_runner = {}, None, _SpyRunner()
     with pytest.raises(NotImplementedError, match="SchedulerOutput"):
         w.execute_model(types.SimpleNamespace(decodes=[], prefills=[]))  # the old private duck type
-    so = _sched()
-    so.scheduled_spec_decode_tokens = {"A": [1]}
-    with pytest.raises(NotImplementedError, match="speculative"):
-        w.execute_model(so)
+    with pytest.raises(NotImplementedError, match="supported: ngram"):
+        B200Worker._build_drafter(types.SimpleNamespace(method="eagle", num_speculative_tokens=3))
     w.execute_model(_sched())
     with pytest.raises(NotImplementedError, match="structured"):
         w.sample_tokens(object())
     assert w.get_supported_tasks() == ("generate",) and w.take_draft_token_ids() is None
+
+
+def test_worker_verifies_scheduled_drafts_and_proposes_ngram_drafts():
+    """N4: vLLM schedules the worker's own drafts back as ``scheduled_spec_decode_tokens``; a pure verification step
+    goes through ``runner.verify`` in the window-mode layout (one (blocks, seq_len, K+1) request per window), greedy
+    acceptance follows the reference (v1/spec_decode.py:272-292), a step with a prefill keeps the expanded layout."""
+    from vllm.v1.core.sched.output import CachedRequestData, NewRequestData
+    from vllm.v1.outputs import DraftTokenIds
+
+    from vllm_metal_b200.v1.spec_decode import NgramDrafter, verify_greedy
+    from vllm_metal_b200.v1.worker import B200Worker
+
+    assert verify_greedy([5, 6, 7], [5, 6]) == [5, 6, 7]       # all drafts hold: + bonus token
+    assert verify_greedy([5, 9, 7], [5, 6]) == [5, 9]          # second draft rejected: target's token instead
+    assert verify_greedy([4, 6, 7], [5, 6]) == [4]
+    d = NgramDrafter(3, min_n=2, max_n=3)
+    assert d.propose([1, 2, 3, 4, 9, 1, 2, 3]) == [4, 9, 1]    # suffix (1,2,3) seen at 0 -> what followed it
+    assert d.propose([1, 2, 3, 4, 9, 1, 2, 3], room=1) == [4]
+    assert d.propose([1, 2, 3, 4]) == [] and d.propose([7, 7]) == []
+
+    class _VerifyRunner(_SpyRunner):
+        def __init__(self, rows):
+            super().__init__()
+            self.rows, self.verified = rows, []
+
+        def verify(self, tokens, reqs):
+            self.verified.append((list(tokens), [(list(b), s, n) for b, s, n in reqs]))
+            return [self.rows.pop(0) for _ in reqs]
+
+    w = object.__new__(B200Worker)
+    w._requests, w._pending, w._drafts = {}, None, {}
+    w._drafter = B200Worker._build_drafter(types.SimpleNamespace(method="ngram", num_speculative_tokens=2,
+                                                                 prompt_lookup_min=2, prompt_lookup_max=3))
+    spy = w.model_runner = _VerifyRunner(rows=[[31, 32, 50], [60, 61, 62]])
+    spy.next_tok = 30
+    prompt = [30, 31, 32, 33, 7, 30, 31]
+    w.execute_model(_sched(new=[NewRequestData(req_id="A", prompt_token_ids=prompt, mm_features=[], sampling_params=None,
+                                               pooling_params=None, block_ids=([3, 4],), num_computed_tokens=0,
+                                               lora_request=None)], num={"A": 7}))
+    assert w.sample_tokens(None).sampled_token_ids == [[30]]
+    drafts = w.take_draft_token_ids()  # history ...30 31 | 30 -> suffix (31, 30)? no; (30, 31, 30) no; n=2: (31, 30) no
+    assert drafts is None or isinstance(drafts, DraftTokenIds)
+    st = w._requests["A"]
+    assert st.tokens == prompt + [30] and st.num_computed == 7
+
+    def cached(n_computed):
+        return CachedRequestData(req_ids=["A"], resumed_req_ids=set(), new_token_ids=[[]], all_token_ids={},
+                                 new_block_ids=[None], num_computed_tokens=[n_computed], num_output_tokens=[1])
+
+    # verification step 1: drafts [31, 32]; target rows say 31, 32, then 50 -> both accepted + bonus
+    so = _sched(cached=cached(7), num={"A": 3})
+    so.scheduled_spec_decode_tokens = {"A": [31, 32]}
+    w.execute_model(so)
+    out = w.sample_tokens(None)
+    assert spy.verified[-1] == ([30, 31, 32], [([3, 4], 7, 3)])
+    assert out.sampled_token_ids == [[31, 32, 50]]
+    assert st.tokens == prompt + [30, 31, 32, 50] and st.num_computed == 10
+    drafts = w.take_draft_token_ids()
+    assert drafts is None or drafts.req_ids == ["A"]
+    assert w.take_draft_token_ids() is None  # handed out once
+
+    # verification step 2: first draft rejected -> only the target's token, KV position count follows
+    so = _sched(cached=cached(10), num={"A": 3})
+    so.scheduled_spec_decode_tokens = {"A": [1, 2]}
+    w.execute_model(so)
+    assert w.sample_tokens(None).sampled_token_ids == [[60]]
+    assert st.tokens[-2:] == [50, 60] and st.num_computed == 11
+
+    # a window scheduled together with a prefill: expanded layout through execute (3-tuple decode request)
+    spy.next_tok = 70
+    so = _sched(new=[NewRequestData(req_id="B", prompt_token_ids=[1, 2], mm_features=[], sampling_params=None,
+                                    pooling_params=None, block_ids=([9],), num_computed_tokens=0, lora_request=None)],
+                cached=cached(11), num={"A": 2, "B": 2})
+    so.scheduled_spec_decode_tokens = {"A": [70]}
+
+    def execute3(tokens, decodes, prefills):
+        spy.calls.append((list(tokens), [tuple(x) for x in decodes], [tuple(x) for x in prefills]))
+        return [70, 71, 99]  # two window rows (expanded), then B's prefill
+
+    spy.execute = execute3
+    w.execute_model(so)
+    out = w.sample_tokens(None)
+    assert spy.calls[-1] == ([60, 70, 1, 2], [([3, 4], 11, 2)], [([9], 2, 0)])
+    assert out.req_ids == ["A", "B"] and out.sampled_token_ids == [[70, 71], [99]]
+
+    # malformed window: the row count must be 1 + drafts
+    so = _sched(cached=cached(13), num={"A": 2})
+    so.scheduled_spec_decode_tokens = {"A": [1, 2]}
+    with pytest.raises(RuntimeError, match="draft tokens scheduled"):
+        w.execute_model(so)

@@ -77,6 +77,22 @@ class B200Worker(WorkerBase):
         self._allreduce = None
         self._pending = None
         self._requests: dict[str, _RequestState] = {}
+        self._drafter = self._build_drafter(getattr(vllm_config, "speculative_config", None))
+        self._drafts: dict[str, list[int]] = {}
+
+    @staticmethod
+    def _build_drafter(spec: Any):
+        """Reference model_runner.py:905-934: Gemma4 MTP / draft_model / ngram.  The n-gram (prompt-lookup) drafter is
+        host-only; model-based drafters are outside the decode hot path and raise."""
+        if spec is None:
+            return None
+        from .spec_decode import NgramDrafter
+
+        if getattr(spec, "method", None) != "ngram":
+            raise NotImplementedError(
+                f"speculative method {getattr(spec, 'method', None)!r} is outside the B200 decode hot path (supported: ngram)")
+        return NgramDrafter(int(spec.num_speculative_tokens), int(getattr(spec, "prompt_lookup_min", None) or 2),
+                            int(getattr(spec, "prompt_lookup_max", None) or 5))
 
     # ---- device / distributed (worker.py:117-193) -----------------------------
     def init_device(self) -> None:
@@ -196,8 +212,7 @@ class B200Worker(WorkerBase):
                 raise NotImplementedError(
                     f"execute_model expects vllm.v1.core.sched.output.SchedulerOutput; {type(so).__name__} has no "
                     f"'{field}'")
-        if so.scheduled_spec_decode_tokens:
-            raise NotImplementedError("speculative decoding is outside the B200 decode hot path")
+        spec_tokens = dict(so.scheduled_spec_decode_tokens or {})  # req_id -> scheduled draft token ids
         for rid in list(so.finished_req_ids) + list(so.preempted_req_ids or ()):
             self._requests.pop(rid, None)
         for nr in so.scheduled_new_reqs:
@@ -223,8 +238,18 @@ class B200Worker(WorkerBase):
             if cached.new_token_ids and cached.new_token_ids[i]:  # pipeline-parallel peers only; we sample here
                 st.tokens = st.tokens[:st.num_computed] + list(cached.new_token_ids[i])
         decodes, prefills = [], []  # (req_id, state, n)
+        windows = False
         for rid, n in so.num_scheduled_tokens.items():
             st = self._requests[rid]
+            drafts = spec_tokens.get(rid) or []
+            if drafts:
+                # a verification window: the last committed token + the scheduled drafts (model_runner.py:1200-1209)
+                if st.num_computed + 1 != len(st.tokens) or n != 1 + len(drafts):
+                    raise RuntimeError(f"request {rid}: {len(drafts)} draft tokens scheduled as {n} rows from "
+                                       f"{st.num_computed} of {len(st.tokens)} known tokens")
+                windows = True
+                decodes.append((rid, st, int(n)))
+                continue
             if st.num_computed + n > len(st.tokens):
                 raise RuntimeError(f"request {rid}: scheduled {n} tokens from {st.num_computed} but only "
                                    f"{len(st.tokens)} are known")
@@ -232,9 +257,11 @@ class B200Worker(WorkerBase):
         tokens: list[int] = []
         dec_rows, pre_rows = [], []
         grouped = getattr(self.model_runner, "group_block_sizes", None) is not None
-        for _, st, _n in decodes:
+        for rid, st, n in decodes:
             tokens.append(st.tokens[st.num_computed])
-            dec_rows.append((st.block_ids if grouped else st.block_ids[0], st.num_computed))
+            tokens.extend(spec_tokens.get(rid) or [])
+            blocks = st.block_ids if grouped else st.block_ids[0]
+            dec_rows.append((blocks, st.num_computed, n) if windows else (blocks, st.num_computed))
         for _, st, n in prefills:
             tokens.extend(st.tokens[st.num_computed:st.num_computed + n])
             pre_rows.append((st.block_ids if grouped else st.block_ids[0], n, st.num_computed))
@@ -242,12 +269,24 @@ class B200Worker(WorkerBase):
         r = self.model_runner
         if not tokens:
             sampled = []
+        elif windows and not pre_rows:
+            # pure verification step: window-mode layout, the rows of a window share every KV read
+            sampled = r.verify(tokens, dec_rows)
+        elif windows:
+            # any prefill segment keeps the batch on the expanded layout (attention/context.py:276-280): one segment,
+            # hence one greedy token, per window row
+            flat = r.execute(tokens, dec_rows, pre_rows)
+            sampled, at = [], 0
+            for _, _, n in decodes:
+                sampled.append(flat[at:at + n])
+                at += n
+            sampled.extend(flat[at:])
         elif not pre_rows and r.use_cuda_graph and len(dec_rows) <= r.max_batch:
             # pure decode: the CUDA-graph path (pinned staging -> one H2D -> graph replay -> D2H token ids)
             sampled = r.decode_step(tokens, [b for b, _ in dec_rows], [n for _, n in dec_rows])
         else:
             sampled = r.execute(tokens, dec_rows, pre_rows)
-        self._pending = (order, sampled)
+        self._pending = (order, sampled, spec_tokens)
 
     def sample_tokens(self, grammar_output: Any = None):
         """Greedy tokens of the step as a ``ModelRunnerOutput`` (reference ``_build_output``,
@@ -259,21 +298,45 @@ class B200Worker(WorkerBase):
             raise NotImplementedError("structured output (grammar bitmask) is outside the B200 decode hot path")
         if self._pending is None:
             return None
-        (order, sampled), self._pending = self._pending, None
+        (order, sampled, spec_tokens), self._pending = self._pending, None
+        from .spec_decode import verify_greedy
+
         req_ids, out = [], []
+        self._drafts = {}
         for (rid, st, n), tok in zip(order, sampled, strict=True):
             req_ids.append(rid)
-            if st.num_computed + n >= len(st.tokens):  # reached the last known token: this step samples
-                st.tokens.append(int(tok))
-                out.append([int(tok)])
+            drafts = spec_tokens.get(rid) or []
+            if drafts:
+                # accepted drafts + the target's own token at the first mismatch (or the bonus token); the KV rows of
+                # rejected drafts are overwritten when real tokens reach those positions
+                emitted = verify_greedy(tok, drafts)
+                st.tokens.extend(emitted)
+                st.num_computed += len(emitted)
+                out.append(emitted)
+            elif st.num_computed + n >= len(st.tokens):  # reached the last known token: this step samples
+                t = int(tok[-1]) if isinstance(tok, (list, tuple)) else int(tok)
+                st.tokens.append(t)
+                out.append([t])
+                st.num_computed += n
             else:
                 out.append([])
-            st.num_computed += n
+                st.num_computed += n
+            drafter = getattr(self, "_drafter", None)
+            if drafter is not None and out[-1]:
+                max_len = int(getattr(getattr(self, "model_config", None), "max_model_len", 1 << 30))
+                self._drafts[rid] = drafter.propose(st.tokens, max_len - len(st.tokens) - 1)
         return ModelRunnerOutput(req_ids=req_ids, req_id_to_index={r: i for i, r in enumerate(req_ids)},
                                  sampled_token_ids=out, logprobs=None, prompt_logprobs_dict={}, pooler_output=[])
 
     def take_draft_token_ids(self):
-        return None  # no speculative drafts on this path (reference worker.py:287-289 forwards the runner's)
+        """Drafts for the requests that sampled last step (reference worker.py:286-288 -> model_runner.py:730); ``None``
+        without a drafter.  vLLM schedules them as ``scheduled_spec_decode_tokens`` of the next step."""
+        if getattr(self, "_drafter", None) is None or not getattr(self, "_drafts", None):
+            return None
+        from vllm.v1.outputs import DraftTokenIds
+
+        drafts, self._drafts = self._drafts, {}
+        return DraftTokenIds(req_ids=list(drafts), draft_token_ids=[drafts[r] for r in drafts])
 
     def get_supported_tasks(self) -> tuple[str, ...]:
         return ("generate",)
