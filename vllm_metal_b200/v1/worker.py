@@ -4,9 +4,10 @@ Mirrors the method set of ``MetalWorker(WorkerBase)`` (vllm_metal/v1/worker.py:6
 init, model load, KV-cache sizing/spec/initialisation, ``execute_model`` -> ``sample_tokens``.
 The engine-side scheduler drives it; everything on the device goes through
 ``v1/model_runner.py::PagedModelRunner`` -> ``sdpa_forward`` -> the C-ABI kernels.  Only the
-greedy decode + chunked-prefill contract of the hot path is implemented: LoRA, multimodal,
-speculative drafts, sleep mode and pipeline parallelism raise or no-op exactly where the
-reference's worker has its own gates (DESIGN.md "out of scope").
+greedy decode + chunked-prefill contract of the hot path is implemented, plus greedy verification of
+scheduled draft tokens in the decode kernel's window mode with a prompt-lookup drafter
+(``v1/spec_decode.py``): LoRA, multimodal, model-based drafters, sleep mode and pipeline parallelism
+raise or no-op exactly where the reference's worker has its own gates (DESIGN.md "out of scope").
 """
 
 from __future__ import annotations
