@@ -205,3 +205,25 @@ def test_oracle_not_imported_by_product():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+
+
+def test_oracle_moe_routing_and_activation_semantics():
+    """oracle/moe.py: gpt-oss routing = softmax over the k selected logits; Qwen3-MoE routing = softmax over all, top-k,
+    renormalised; ties go to the lowest expert id; the clipped SwiGLU saturates at the limit."""
+    from oracle import moe
+
+    logits = np.array([[1.0, 3.0, 3.0, -2.0], [0.0, 0.0, 0.0, 0.0]], np.float32)
+    idx, sc = moe.route(logits, 2, "topk_softmax")
+    assert idx.tolist() == [[1, 2], [0, 1]]
+    np.testing.assert_allclose(sc, [[0.5, 0.5], [0.5, 0.5]], atol=1e-6)
+    idx2, sc2 = moe.route(logits, 2, "softmax_topk", norm_topk_prob=False)
+    assert idx2.tolist() == [[1, 2], [0, 1]]
+    p = np.exp(logits[0] - 3.0) / np.exp(logits[0] - 3.0).sum()
+    np.testing.assert_allclose(sc2[0], p[[1, 2]], rtol=1e-6)
+    np.testing.assert_allclose(moe.route(logits, 2, "softmax_topk")[1].sum(-1), 1.0, atol=1e-6)
+    g, u = np.array([100.0, -100.0, 1.0], np.float32), np.array([100.0, -100.0, 0.5], np.float32)
+    a = moe.activation(g, u, "gpt_oss")
+    np.testing.assert_allclose(a[0], 7.0 / (1.0 + np.exp(-1.702 * 7.0)) * 8.0, rtol=1e-6)  # both clipped at the limit
+    assert abs(a[1]) < 1e-30                                                            # sigmoid(-170) kills it
+    np.testing.assert_allclose(a[2], 1.0 / (1.0 + np.exp(-1.702)) * 1.5, rtol=1e-6)
+    np.testing.assert_allclose(moe.activation(g[2:], u[2:], "silu"), 1.0 / (1.0 + np.exp(-1.0)) * 0.5, rtol=1e-6)

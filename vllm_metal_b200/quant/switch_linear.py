@@ -1,0 +1,178 @@
+"""Quantized mixture-of-experts MLP: ``QuantizedSwitchLinear`` / ``SwitchGLU`` / ``MoEBlock``.
+
+The reference reaches MoE models (gpt-oss: 32 experts, top-4) through mlx-lm's ``SwitchGLU`` whose expert
+projections are ``QuantizedSwitchLinear`` modules -- named in vllm_metal/quant/awq_loader.py:171-173 -- i.e.
+``mx.gather_qmm(x, weight, scales, biases, rhs_indices=indices, transpose=True, group_size, bits)`` over stacked
+expert weights ``[E, N, K*bits/32]`` (third-party arithmetic: mlx 0.32.0 / mlx-lm 254d153, not under
+/root/reference -> parity unpinned, semantics restated in oracle/moe.py).  Same attribute names and shapes here.
+
+B200 form: the (token, expert) pairs are sorted by expert and every expert that received rows runs ONE affine
+quantized GEMM over its gathered rows through the same C-ABI kernels as the dense linears (`b200_qlinear`): each
+expert's weights are streamed once per step however many tokens picked it.  The per-expert row counts are read back
+to the host once per block (one small D2H copy): this is the functional path of row N2 -- launch-bound at decode
+batch sizes (3 x experts-hit launches per layer); a grouped persistent kernel is the next step and is not built.
+"""
+
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from ..metal import get_ops
+from .affine import quantize
+
+
+class QuantizedSwitchLinear(nn.Module):
+    """Stacked expert linears: ``weight`` uint32 ``[E, N, K*bits/32]``, ``scales`` / ``biases`` ``[E, N, K/g]``,
+    optional dense ``bias`` ``[E, N]`` (mlx-lm ``QuantizedSwitchLinear``)."""
+
+    def __init__(self, in_features: int, out_features: int, num_experts: int, bias: bool = False,
+                 group_size: int = 64, bits: int = 4, dtype: torch.dtype = torch.bfloat16, device=None) -> None:
+        super().__init__()
+        if in_features % group_size:
+            raise ValueError(f"in_features {in_features} not divisible by group_size {group_size}")
+        self.group_size, self.bits = group_size, bits
+        e, n, k = num_experts, out_features, in_features
+        self.register_buffer("weight", torch.zeros((e, n, k * bits // 32), dtype=torch.int32, device=device))
+        self.register_buffer("scales", torch.zeros((e, n, k // group_size), dtype=dtype, device=device))
+        self.register_buffer("biases", torch.zeros((e, n, k // group_size), dtype=dtype, device=device))
+        if bias:
+            self.register_buffer("bias", torch.zeros((e, n), dtype=dtype, device=device))
+        else:
+            self.bias = None
+
+    @property
+    def num_experts(self) -> int:
+        return self.scales.shape[0]
+
+    @property
+    def out_features(self) -> int:
+        return self.scales.shape[1]
+
+    @property
+    def in_features(self) -> int:
+        return self.scales.shape[2] * self.group_size
+
+    @classmethod
+    def from_dense(cls, weight: torch.Tensor, bias: torch.Tensor | None = None, group_size: int = 64, bits: int = 4,
+                   dtype: torch.dtype = torch.bfloat16) -> QuantizedSwitchLinear:
+        """``weight`` ``[E, N, K]`` dense; every expert is quantized like a ``QuantizedLinear``."""
+        e, n, k = weight.shape
+        m = cls(k, n, e, bias is not None, group_size, bits, dtype, weight.device)
+        for i in range(e):
+            w, s, b = quantize(weight[i], group_size, bits, dtype)
+            m.weight[i].copy_(w)
+            m.scales[i].copy_(s)
+            m.biases[i].copy_(b)
+        if bias is not None:
+            m.bias.copy_(bias.to(dtype))
+        return m
+
+    def forward_sorted(self, x_sorted: torch.Tensor, counts: list[int]) -> torch.Tensor:
+        """``x_sorted`` ``[P, K]``: rows grouped by expert (``counts[e]`` consecutive rows for expert e).  One quantized
+        GEMM per expert that has rows; returns ``[P, N]``."""
+        ops = get_ops()
+        out = torch.empty((x_sorted.shape[0], self.out_features), dtype=self.scales.dtype, device=x_sorted.device)
+        at = 0
+        for e, c in enumerate(counts):
+            if c == 0:
+                continue
+            ops.quantized_matmul(x_sorted[at:at + c], self.weight[e], self.scales[e], self.biases[e], transpose=True,
+                                 group_size=self.group_size, bits=self.bits,
+                                 bias=None if self.bias is None else self.bias[e], out=out[at:at + c])
+            at += c
+        return out
+
+    def forward(self, x: torch.Tensor, indices: torch.Tensor) -> torch.Tensor:
+        """``mx.gather_qmm`` form: ``x`` ``[T, K]`` (shared by a token's experts) or ``[T, k, K]``; ``indices``
+        ``[T, k]`` -> ``[T, k, N]``."""
+        t, k = indices.shape
+        order, counts = _sort_pairs(indices, self.num_experts)
+        rows = x if x.dim() == 3 else x[:, None, :].expand(t, k, x.shape[-1])
+        xs = rows.reshape(t * k, -1).index_select(0, order)
+        ys = self.forward_sorted(xs.contiguous(), counts)
+        out = torch.empty_like(ys)
+        out.index_copy_(0, order, ys)
+        return out.reshape(t, k, -1)
+
+
+def _sort_pairs(indices: torch.Tensor, num_experts: int) -> tuple[torch.Tensor, list[int]]:
+    flat = indices.reshape(-1).to(torch.int64)
+    order = torch.argsort(flat, stable=True)
+    counts = torch.bincount(flat, minlength=num_experts).tolist()  # the one host read-back of the block
+    return order, counts
+
+
+def _act_silu(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
+    return torch.nn.functional.silu(gate) * up
+
+
+def _act_gpt_oss(gate: torch.Tensor, up: torch.Tensor, alpha: float = 1.702, limit: float = 7.0) -> torch.Tensor:
+    """gpt-oss's clipped SwiGLU (mlx-lm gpt_oss.py ``swiglu``): ``g = min(gate, limit)``, ``u = clip(up, +-limit)``,
+    ``g * sigmoid(alpha * g) * (u + 1)``."""
+    g = gate.clamp(max=limit)
+    u = up.clamp(min=-limit, max=limit)
+    return g * torch.sigmoid(alpha * g) * (u + 1.0)
+
+
+ACTIVATIONS = {"silu": _act_silu, "gpt_oss": _act_gpt_oss}
+
+
+class SwitchGLU(nn.Module):
+    """``down(act(gate(x), up(x)))`` per selected expert (mlx-lm ``SwitchGLU``).  The activation runs in fp32 on the
+    dtype-rounded projections and is rounded once."""
+
+    def __init__(self, hidden: int, inter: int, num_experts: int, bias: bool = False, group_size: int = 64,
+                 bits: int = 4, dtype: torch.dtype = torch.bfloat16, device=None, activation: str = "silu") -> None:
+        super().__init__()
+        mk = lambda i, o: QuantizedSwitchLinear(i, o, num_experts, bias, group_size, bits, dtype, device)  # noqa: E731
+        self.gate_proj, self.up_proj, self.down_proj = mk(hidden, inter), mk(hidden, inter), mk(inter, hidden)
+        self.activation = activation
+
+    def forward(self, x: torch.Tensor, indices: torch.Tensor) -> torch.Tensor:
+        t, k = indices.shape
+        order, counts = _sort_pairs(indices, self.gate_proj.num_experts)
+        token_of_pair = torch.div(order, k, rounding_mode="floor")
+        xs = x.index_select(0, token_of_pair).contiguous()  # rows grouped by expert: gathered once for gate and up
+        g = self.gate_proj.forward_sorted(xs, counts)
+        u = self.up_proj.forward_sorted(xs, counts)
+        h = ACTIVATIONS[self.activation](g.float(), u.float()).to(g.dtype)
+        ys = self.down_proj.forward_sorted(h, counts)
+        out = torch.empty_like(ys)
+        out.index_copy_(0, order, ys)
+        return out.reshape(t, k, -1)
+
+
+class MoEBlock(nn.Module):
+    """Router + top-k experts + weighted sum.
+
+    ``routing="topk_softmax"`` (gpt-oss): top-k of the router logits, softmax over the k selected logits.
+    ``routing="softmax_topk"`` (Qwen3-MoE style): softmax over all experts, top-k, optionally renormalised.
+    Router and softmax in fp32; ``y = sum_j score_j * expert_j(x)`` accumulated in fp32, rounded once."""
+
+    def __init__(self, router: nn.Module, experts: SwitchGLU, top_k: int, routing: str = "topk_softmax",
+                 norm_topk_prob: bool = True) -> None:
+        super().__init__()
+        if routing not in ("topk_softmax", "softmax_topk"):
+            raise ValueError(f"unknown routing {routing!r}")
+        self.router, self.experts, self.top_k = router, experts, int(top_k)
+        self.routing, self.norm_topk_prob = routing, norm_topk_prob
+
+    def route(self, x: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+        logits = self.router(x).float()
+        if self.routing == "topk_softmax":
+            vals, idx = torch.topk(logits, self.top_k, dim=-1)
+            return idx, torch.softmax(vals, dim=-1)
+        probs = torch.softmax(logits, dim=-1)
+        vals, idx = torch.topk(probs, self.top_k, dim=-1)
+        if self.norm_topk_prob:
+            vals = vals / vals.sum(dim=-1, keepdim=True)
+        return idx, vals
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, x.shape[-1])
+        idx, scores = self.route(x2)
+        y = self.experts(x2, idx)  # [T, k, hidden]
+        out = (y.float() * scores[..., None]).sum(dim=1).to(x.dtype)
+        return out.reshape(*lead, -1)
