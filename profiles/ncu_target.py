@@ -3,6 +3,7 @@
 
     python profiles/ncu_target.py qgemm [gate_up|qkv|o_proj|down] [ksplit] [dequant_warps]
     python profiles/ncu_target.py attn
+    WINDOW=4 python profiles/ncu_target.py window     # decode attention in spec-verify window mode
 
 Weights / KV rotate over buffers larger than L2 so the profiled launch streams from HBM.
 """
@@ -55,11 +56,16 @@ def main():
         bt = (torch.randperm(nb - 1, device="cuda", generator=gen) + 1).int().reshape(batch, blocks)
         seq = torch.full((batch,), ctx + 1, dtype=torch.int32, device="cuda")
         cu = torch.arange(batch + 1, dtype=torch.int32, device="cuda")
-        q = torch.randn((batch, hq, d), device="cuda", generator=gen).bfloat16()
+        win = int(os.environ.get("WINDOW", "4")) if what == "window" else 1  # spec-verify window mode: K+1 rows per sequence
+        if win > 1:
+            seq = torch.full((batch,), ctx + 1, dtype=torch.int32, device="cuda")  # the window's rows end at ctx + 1
+            cu = torch.arange(0, batch * win + 1, win, dtype=torch.int32, device="cuda")
+        q = torch.randn((batch * win, hq, d), device="cuda", generator=gen).bfloat16()
         out = torch.empty_like(q)
         for _ in range(2):
             for kc, vc in caches:
-                ops.paged_attention_primitive(q, kc, vc, hkv, d ** -0.5, 0.0, bt, seq, cu, bs, ctx + 1, -1, out)
+                ops.paged_attention_primitive(q, kc, vc, hkv, d ** -0.5, 0.0, bt, seq, cu, bs, ctx + 1, -1, out,
+                                              window_seqlen_q=win)
         torch.cuda.synchronize()
         print("attn ok", float(out.float().abs().mean()))
 
