@@ -387,3 +387,84 @@ def test_worker_speculative_steps_emit_the_plain_greedy_stream():
     for r in prompts:
         n = min(len(spec_out[r]), len(plain[r]))
         assert spec_out[r][:n] == plain[r][:n], r
+
+
+def test_worker_deferred_sampling_emits_the_synchronous_stream():
+    """N4 deferred sampling on the device: with the one-step-ahead pipeline every decode step is submitted before the
+    previous step's tokens are read (inputs gathered from the previous argmax on the GPU); the emitted tokens are the
+    synchronous worker's, token for token, across a block boundary and a request joining / leaving mid-way."""
+    pytest.importorskip("vllm")
+    from vllm.v1.core.sched.output import CachedRequestData, NewRequestData, SchedulerOutput
+    from vllm.v1.outputs import AsyncModelRunnerOutput
+
+    from vllm_metal_b200.attention.caches.kv_cache import B200PagedKVCache
+    from vllm_metal_b200.lm.decoder import PRESETS, Model
+    from vllm_metal_b200.v1.decode_pipeline import DecodePipeline
+    from vllm_metal_b200.v1.model_runner import PagedModelRunner
+    from vllm_metal_b200.v1.worker import B200Worker
+
+    args, bs, nb = PRESETS["tiny"], 16, 24
+    model = Model(args, torch.bfloat16, "cuda", seed=6)
+    rng = np.random.default_rng(13)
+    prompts = {"A": rng.integers(0, args.vocab, 29).tolist(), "B": rng.integers(0, args.vocab, 14).tolist(),
+               "C": rng.integers(0, args.vocab, 9).tolist()}
+    blocks = {"A": [5, 9, 2, 17], "B": [3, 20, 7], "C": [1, 12, 4]}
+
+    def run(pipelined: bool) -> dict[str, list[int]]:
+        cache = B200PagedKVCache(args.num_layers, args.n_kv_heads, args.head_dim, nb, bs, torch.bfloat16, "cuda")
+        w = object.__new__(B200Worker)
+        w._requests, w._pending, w._drafts, w._drafter = {}, None, {}, None
+        w._pipeline = DecodePipeline() if pipelined else None
+        w.model, w.kv_cache = model, cache
+        w.model_runner = PagedModelRunner(model, cache, max_batch=4, max_model_len=4 * bs, use_cuda_graph=True)
+        emitted = {r: [] for r in prompts}
+        computed = {r: 0 for r in prompts}
+        outstanding = []  # async outputs the "engine" has not taken yet
+
+        def take(out):
+            got = out.get_output() if isinstance(out, AsyncModelRunnerOutput) else out
+            for rid, toks in zip(got.req_ids, got.sampled_token_ids, strict=True):
+                emitted[rid] += toks
+
+        def step(new, num, finished=()):
+            new_reqs = [NewRequestData(req_id=r, prompt_token_ids=prompts[r], mm_features=[], sampling_params=None,
+                                       pooling_params=None, block_ids=(blocks[r],), num_computed_tokens=0,
+                                       lora_request=None) for r in new]
+            old = [r for r in num if r not in new]
+            cached = CachedRequestData(req_ids=old, resumed_req_ids=set(), new_token_ids=[[] for _ in old],
+                                       all_token_ids={}, new_block_ids=[None for _ in old],
+                                       num_computed_tokens=[computed[r] for r in old], num_output_tokens=[1 for _ in old])
+            so = SchedulerOutput(scheduled_new_reqs=new_reqs, scheduled_cached_reqs=cached, num_scheduled_tokens=num,
+                                 total_num_scheduled_tokens=sum(num.values()), scheduled_spec_decode_tokens={},
+                                 scheduled_encoder_inputs={}, num_common_prefix_blocks=[0],
+                                 finished_req_ids=set(finished), free_encoder_mm_hashes=[])
+            w.execute_model(so)
+            out = w.sample_tokens(None)
+            for r, n in num.items():
+                computed[r] += n
+            # the engine takes output k only after step k+1 was submitted (async scheduling)
+            outstanding.append(out)
+            while len(outstanding) > 1:
+                take(outstanding.pop(0))
+
+        step(["A", "B"], {"A": 29, "B": 14})
+        for i in range(22):
+            if i == 6:
+                step(["C"], {"A": 1, "B": 1, "C": 9})       # C joins: a synchronous step in the middle
+            elif i == 15:
+                step([], {"A": 1, "C": 1}, finished=["B"])   # B leaves: the batch shrinks, rows move
+            elif i > 15:
+                step([], {"A": 1, "C": 1})
+            elif i > 6:
+                step([], {"A": 1, "B": 1, "C": 1})
+            else:
+                step([], {"A": 1, "B": 1})
+        while outstanding:
+            take(outstanding.pop(0))
+        if pipelined:
+            assert w._pipeline.submitted >= 18, w._pipeline.blocked
+        return emitted
+
+    sync, piped = run(False), run(True)
+    assert {r: len(v) for r, v in piped.items()} == {r: len(v) for r, v in sync.items()}
+    assert piped == sync

@@ -322,3 +322,92 @@ def test_worker_verifies_scheduled_drafts_and_proposes_ngram_drafts():
     so.scheduled_spec_decode_tokens = {"A": [1, 2]}
     with pytest.raises(RuntimeError, match="draft tokens scheduled"):
         w.execute_model(so)
+
+
+def test_worker_defers_sampling_one_step_ahead():
+    """N4 deferred sampling (reference v1/decode_pipeline.py invariants): eligible pure-decode steps return an
+    ``AsyncModelRunnerOutput``; the next step is submitted with placeholder inputs that name the pending step's rows;
+    bookkeeping happens before submit, values are backfilled on resolve; an ineligible step resolves first."""
+    from vllm.v1.core.sched.output import CachedRequestData, NewRequestData
+    from vllm.v1.outputs import AsyncModelRunnerOutput, ModelRunnerOutput
+
+    from vllm_metal_b200.v1.decode_pipeline import PENDING_TOKEN_PLACEHOLDER, DecodePipeline
+    from vllm_metal_b200.v1.worker import B200Worker
+
+    class _Handle:
+        def __init__(self, toks):
+            self.toks, self.reads = toks, 0
+
+        def tokens(self):
+            self.reads += 1
+            return self.toks
+
+    class _PipeRunner(_SpyRunner):
+        use_cuda_graph, max_batch = True, 4
+
+        def __init__(self):
+            super().__init__()
+            self.submits, self.handles = [], []
+
+        def submit_decode(self, tokens, blocks, seq_lens, pending_rows):
+            self.submits.append((list(tokens), [list(b) for b in blocks], list(seq_lens), list(pending_rows)))
+            h = _Handle(list(range(self.next_tok, self.next_tok + len(tokens))))
+            self.next_tok += len(tokens)
+            self.handles.append(h)
+            return h
+
+        def decode_step(self, tokens, blocks, seq_lens):
+            raise AssertionError("the synchronous graph path must not run on an eligible step")
+
+    w = object.__new__(B200Worker)
+    w._requests, w._pending, w._drafts, w._drafter = {}, None, {}, None
+    w._pipeline = DecodePipeline()
+    spy = w.model_runner = _PipeRunner()
+
+    def new_req(rid, prompt, blocks):
+        return NewRequestData(req_id=rid, prompt_token_ids=prompt, mm_features=[], sampling_params=None,
+                              pooling_params=None, block_ids=(blocks,), num_computed_tokens=0, lora_request=None)
+
+    def cached(ids, computed):
+        return CachedRequestData(req_ids=ids, resumed_req_ids=set(), new_token_ids=[[] for _ in ids], all_token_ids={},
+                                 new_block_ids=[None for _ in ids], num_computed_tokens=computed,
+                                 num_output_tokens=[1 for _ in ids])
+
+    # prefill: new requests -> synchronous path (gate: "new requests scheduled")
+    w.execute_model(_sched(new=[new_req("A", [1, 2, 3], [7]), new_req("B", [4, 5], [9])], num={"A": 3, "B": 2}))
+    out = w.sample_tokens(None)
+    assert isinstance(out, ModelRunnerOutput) and out.sampled_token_ids == [[1000], [1001]]
+    assert w._pipeline.blocked == {"new requests scheduled": 1}
+
+    # step 1: pure decode -> deferred; real tokens go in, nothing is read back
+    w.execute_model(_sched(cached=cached(["A", "B"], [3, 2]), num={"A": 1, "B": 1}))
+    out1 = w.sample_tokens(None)
+    assert isinstance(out1, AsyncModelRunnerOutput)
+    assert spy.submits[-1] == ([1000, 1001], [[7], [9]], [3, 2], [-1, -1])
+    a, b = w._requests["A"], w._requests["B"]
+    assert a.tokens[-1] == PENDING_TOKEN_PLACEHOLDER and a.num_computed == 4 and b.num_computed == 3
+    assert spy.handles[0].reads == 0
+
+    # step 2 is submitted BEFORE step 1's output is taken: placeholders name step 1's rows; B comes first this time
+    w.execute_model(_sched(cached=cached(["B", "A"], [3, 4]), num={"B": 1, "A": 1}))
+    assert spy.submits[-1][2:] == ([3, 4], [1, 0]) and spy.handles[0].reads == 0
+    out2 = w.sample_tokens(None)          # submitting step 2 resolves step 1 on the host
+    assert spy.handles[0].reads == 1
+    assert a.tokens[-2:] == [1002, PENDING_TOKEN_PLACEHOLDER] and b.tokens[-2:] == [1003, PENDING_TOKEN_PLACEHOLDER]
+    r1 = out1.get_output()                # the engine takes step 1 late: cached, no second read
+    assert r1.req_ids == ["A", "B"] and r1.sampled_token_ids == [[1002], [1003]] and spy.handles[0].reads == 1
+
+    # step 3: A finishes, a new request arrives -> ineligible: the pending step 2 is resolved first, then the
+    # synchronous path runs with real tokens only
+    w.execute_model(_sched(new=[new_req("C", [8, 9], [11])], cached=cached(["B"], [4]), num={"B": 1, "C": 2},
+                           finished=["A"]))
+    assert spy.handles[1].reads == 1 and b.tokens[-1] == 1004 and PENDING_TOKEN_PLACEHOLDER not in b.tokens
+    assert a.tokens[-1] == 1005           # backfilled through the direct reference although A was dropped
+    assert "A" not in w._requests
+    assert spy.calls[-1] == ([1004, 8, 9], [([9], 4)], [([11], 2, 0)])
+    out3 = w.sample_tokens(None)
+    assert isinstance(out3, ModelRunnerOutput) and out3.req_ids == ["B", "C"]
+    r2 = out2.get_output()
+    assert r2.req_ids == ["B", "A"] and r2.sampled_token_ids == [[1004], [1005]]
+    assert out1.get_output() is r1        # the last two resolved steps are kept for a late reader
+    assert w._pipeline.submitted == 2

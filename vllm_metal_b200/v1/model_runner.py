@@ -44,6 +44,12 @@ class StepBuffers:
         self.host_np = self.host.numpy()
         self.out_tokens = torch.zeros(b, dtype=torch.int32, device=device)
         self.out_host = torch.zeros(b, dtype=torch.int32).pin_memory()
+        # one-step-ahead pipeline (submit_decode): the previous step's sampled tokens stay on the device as the next
+        # step's inputs; two pinned read-back buffers alternate so a step's tokens can be read after the next submit
+        self.prev_tokens = torch.zeros(b, dtype=torch.int32, device=device)
+        self.out_host2 = [torch.zeros(b, dtype=torch.int32).pin_memory() for _ in range(2)]
+        self.gather_host = torch.zeros(2 * b, dtype=torch.int64).pin_memory()
+        self.gather_dev = torch.zeros(2 * b, dtype=torch.int64, device=device)
 
     def view(self, name: str, on_host: bool = False):
         off, n = self.offsets[name]
@@ -71,6 +77,20 @@ class StepBuffers:
     def upload(self) -> int:
         self.dev.copy_(self.host, non_blocking=True)
         return self.words * 4
+
+
+class _PendingTokens:
+    """Tokens of a submitted decode step; ``tokens()`` waits for the read-back."""
+
+    def __init__(self, event, host: torch.Tensor, n: int) -> None:
+        self._event, self._host, self._n = event, host, n
+        self._tokens: list[int] | None = None
+
+    def tokens(self) -> list[int]:
+        if self._tokens is None:
+            self._event.synchronize()
+            self._tokens = self._host[: self._n].tolist()
+        return self._tokens
 
 
 class PagedModelRunner:
@@ -218,6 +238,43 @@ class PagedModelRunner:
             torch.cuda.current_stream().synchronize()
             return self.buf.out_host[:n].tolist()
         return None
+
+    def submit_decode(self, token_ids, block_ids, seq_lens, pending_rows: Sequence[int] | None = None):
+        """One pure-decode step WITHOUT waiting for its tokens (one-step-ahead pipelining, reference
+        v1/decode_pipeline.py:1-26): host metadata -> pinned -> H2D -> graph -> async D2H, returns a handle whose
+        ``tokens()`` blocks on the read-back event.  ``pending_rows[i] >= 0`` says request i's input token is row
+        ``pending_rows[i]`` of the PREVIOUS submitted step, whose value the host has not seen: it is gathered on the
+        device (``token_ids[i]`` is ignored); -1 = ``token_ids[i]`` is the real token."""
+        n = len(token_ids)
+        b = self.buf
+        gather = [(i, r) for i, r in enumerate(pending_rows or ()) if r >= 0]
+        ids = [0 if (pending_rows and pending_rows[i] >= 0) else int(t) for i, t in enumerate(token_ids)]
+        # the pinned mirrors are reused every step: the previous step's H2D copies (queued behind the step before it)
+        # must have left them before the host writes this step's metadata
+        prev_upload = getattr(self, "_upload_event", None)
+        if prev_upload is not None:
+            prev_upload.synchronize()
+        max_len = self.fill_decode(ids, block_ids, seq_lens)
+        self.h2d_bytes += b.upload()
+        if gather:
+            # prev_tokens holds the previous step's argmax (copied before this step's argmax overwrites out_tokens)
+            g = len(gather)
+            b.gather_host[:g] = torch.tensor([i for i, _ in gather], dtype=torch.int64)
+            b.gather_host[g:2 * g] = torch.tensor([r for _, r in gather], dtype=torch.int64)
+            b.gather_dev[:2 * g].copy_(b.gather_host[:2 * g], non_blocking=True)
+            self.h2d_bytes += 16 * g
+            b.view("input_ids").index_copy_(0, b.gather_dev[:g], b.prev_tokens.index_select(0, b.gather_dev[g:2 * g]))
+        self._upload_event = torch.cuda.Event()
+        self._upload_event.record()
+        self.run_decode(n, max_len)
+        b.prev_tokens[:n].copy_(b.out_tokens[:n])
+        self._submit_serial = getattr(self, "_submit_serial", 0) + 1
+        host = b.out_host2[self._submit_serial & 1]
+        host[:n].copy_(b.out_tokens[:n], non_blocking=True)
+        self.d2h_bytes += n * 4
+        ev = torch.cuda.Event()
+        ev.record()
+        return _PendingTokens(ev, host, n)
 
     def run_decode(self, batch: int, max_seq_len: int, *, advance: bool = False) -> None:
         """Forward + argmax over the persistent buffers (graph replay when enabled).

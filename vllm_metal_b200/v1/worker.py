@@ -80,6 +80,15 @@ class B200Worker(WorkerBase):
         self._requests: dict[str, _RequestState] = {}
         self._drafter = self._build_drafter(getattr(vllm_config, "speculative_config", None))
         self._drafts: dict[str, list[int]] = {}
+        # one-step-ahead decode pipelining (reference v1/decode_pipeline.py): on with vLLM's async scheduling, or forced
+        # by B200_DECODE_PIPELINE=1
+        import os
+
+        from .decode_pipeline import DecodePipeline
+
+        want = os.environ.get("B200_DECODE_PIPELINE")
+        enabled = (want == "1") if want is not None else bool(getattr(self.scheduler_config, "async_scheduling", False))
+        self._pipeline = DecodePipeline() if enabled else None
 
     @staticmethod
     def _build_drafter(spec: Any):
@@ -268,6 +277,22 @@ class B200Worker(WorkerBase):
             pre_rows.append((st.block_ids if grouped else st.block_ids[0], n, st.num_computed))
         order = decodes + prefills
         r = self.model_runner
+        pipe = getattr(self, "_pipeline", None)
+        if pipe is not None:
+            reason = None if not tokens else pipe.block_reason(
+                so, has_prefill_rows=bool(pre_rows), has_spec_tokens=windows, runner=r, batch=len(dec_rows),
+                drafter=getattr(self, "_drafter", None))
+            if tokens and reason is None:
+                # deferred step: input tokens the host has not seen yet are gathered from the pending step's argmax on
+                # the device; nothing here waits for the GPU
+                rows = [pipe.pending_row(rid) if st.tokens[st.num_computed] < 0 else -1 for rid, st, _ in decodes]
+                if any(row < 0 and st.tokens[st.num_computed] < 0 for row, (_, st, _) in zip(rows, decodes, strict=True)):
+                    raise RuntimeError("decode pipeline: a placeholder token has no pending row")
+                handle = r.submit_decode(tokens, [b for b, _ in dec_rows], [n for _, n in dec_rows], rows)
+                self._pending = (order, handle, "deferred")
+                return
+            pipe.begin_step()  # synchronous step: the pending tokens land before any state is read
+            tokens = self._retokenize(decodes, prefills, spec_tokens)
         if not tokens:
             sampled = []
         elif windows and not pre_rows:
@@ -300,6 +325,17 @@ class B200Worker(WorkerBase):
         if self._pending is None:
             return None
         (order, sampled, spec_tokens), self._pending = self._pending, None
+        if spec_tokens == "deferred":
+            # value-independent bookkeeping now, token values when the engine asks (decode_pipeline.py invariants)
+            from .decode_pipeline import PENDING_TOKEN_PLACEHOLDER
+
+            entries = []
+            for row, (rid, st, n) in enumerate(order):
+                st.tokens.append(PENDING_TOKEN_PLACEHOLDER)
+                st.num_computed += n
+                entries.append((rid, st, len(st.tokens) - 1, row))
+            self._drafts = {}
+            return self._pipeline.submit(sampled, entries)
         from .spec_decode import verify_greedy
 
         req_ids, out = [], []
@@ -328,6 +364,16 @@ class B200Worker(WorkerBase):
                 self._drafts[rid] = drafter.propose(st.tokens, max_len - len(st.tokens) - 1)
         return ModelRunnerOutput(req_ids=req_ids, req_id_to_index={r: i for i, r in enumerate(req_ids)},
                                  sampled_token_ids=out, logprobs=None, prompt_logprobs_dict={}, pooler_output=[])
+
+    def _retokenize(self, decodes, prefills, spec_tokens) -> list[int]:
+        """The packed input ids of a step, rebuilt after ``begin_step`` replaced placeholders by real tokens."""
+        tokens: list[int] = []
+        for rid, st, _n in decodes:
+            tokens.append(st.tokens[st.num_computed])
+            tokens.extend(spec_tokens.get(rid) or [])
+        for _, st, n in prefills:
+            tokens.extend(st.tokens[st.num_computed:st.num_computed + n])
+        return tokens
 
     def take_draft_token_ids(self):
         """Drafts for the requests that sampled last step (reference worker.py:286-288 -> model_runner.py:730); ``None``
