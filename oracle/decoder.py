@@ -151,11 +151,21 @@ class OracleDecoder:
                     q, self.kc[li], self.vc[li], bt, seq_lens, cu, self.d ** -0.5, L.get("window", -1), 0.0,
                     L.get("sinks"), dtype=dt)
             a = L["o"].matmul(a.reshape(t, nq), dt)
-            if L.get("gate_up") is None:
+            if L.get("gate_up") is None and L.get("moe") is None:
                 delta = a
                 continue
             h = round_to(h + a, dt)
             x = rms_norm(h, L["post_norm"], self.eps, dt)
+            if L.get("moe") is not None:
+                from . import moe as omoe
+
+                m = L["moe"]
+                forced = m.get("forced")  # tests: the product's (indices, scores) of this forward, see gpu_helpers
+                ind, sc = forced.pop(0) if forced else (None, None)
+                delta, _, _ = omoe.moe_block(x, m["router_w"], m["router_b"], m["gate"], m["up"], m["down"], m["top_k"],
+                                             m["group_size"], m["bits"], dt, m["routing"], m["act"], m["norm_topk_prob"],
+                                             indices=ind, scores=sc)
+                continue
             delta = L["down"].matmul(silu_mul(L["gate_up"].matmul(x, dt), dt), dt)
         if delta is not None:
             h = round_to(h + delta, dt)

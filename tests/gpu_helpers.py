@@ -85,6 +85,23 @@ def assert_close(got: torch.Tensor | np.ndarray, want: np.ndarray, dtype: str, w
 
 # ---------------------------------------------------------------- model level ---
 
+def moe_weights(block):
+    """Host copies of a product ``MoEBlock`` for ``oracle.moe.moe_block``.  The product's routing of every forward is
+    handed to the oracle (``forced``): expert choice is discrete, so a 1-ulp difference in the hidden state that
+    reaches the router can flip an expert and change the output far beyond any tolerance; routing parity itself is
+    tested on identical inputs in tests/test_gpu_moe.py and tests/test_host_logic.py."""
+    block.trace = []
+    def stack(m):
+        return (m.weight.cpu().numpy().view(np.uint32), to_np(m.scales), to_np(m.biases),
+                None if m.bias is None else to_np(m.bias))
+
+    g = block.experts
+    return dict(router_w=to_np(block.router.weight), router_b=None if block.router.bias is None else to_np(block.router.bias),
+                gate=stack(g.gate_proj), up=stack(g.up_proj), down=stack(g.down_proj), top_k=block.top_k,
+                group_size=g.gate_proj.group_size, bits=g.gate_proj.bits, routing=block.routing, act=g.activation,
+                norm_topk_prob=block.norm_topk_prob, forced=block.trace)
+
+
 def oracle_from_model(model, num_blocks, block_size, c_attention=False):
     """Build an ``oracle.decoder.OracleDecoder`` holding the SAME quantised weights
     as a product ``lm.decoder.Model`` (copied to host; nothing is recomputed)."""
@@ -106,8 +123,9 @@ def oracle_from_model(model, num_blocks, block_size, c_attention=False):
             qkv=qw(at.qkv_proj), o=qw(at.o_proj),
             q_norm=None if at.q_norm is None else to_np(at.q_norm.weight),
             k_norm=None if at.k_norm is None else to_np(at.k_norm.weight),
-            gate_up=None if layer.mlp is None else qw(layer.mlp.gate_up_proj),
-            down=None if layer.mlp is None else qw(layer.mlp.down_proj),
+            gate_up=None if layer.mlp is None or hasattr(layer.mlp, "block") else qw(layer.mlp.gate_up_proj),
+            down=None if layer.mlp is None or hasattr(layer.mlp, "block") else qw(layer.mlp.down_proj),
+            moe=None if not hasattr(layer.mlp, "block") else moe_weights(layer.mlp.block),
             sinks=None if at.sinks is None else to_np(at.sinks), window=windows[i]))
     weights = dict(embed=qw(model.embed_tokens), lm_head=None if model.lm_head is None else qw(model.lm_head),
                    norm=to_np(model.norm.weight), layers=layers)

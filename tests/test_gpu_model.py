@@ -93,6 +93,19 @@ def test_tiny_gpt_oss_style_sinks_and_window():
     assert near <= 0.05 * (exact + near)
 
 
+def test_tiny_gpt_oss_style_moe_model():
+    """N2 at the model level: sinks + alternating sliding window + a 4-expert top-2 MoE MLP with gpt-oss's clipped
+    SwiGLU, router / expert biases -- packed prefill + greedy decode vs the oracle decoder (oracle/moe.py)."""
+    ov = dict(qk_norm=False, sinks=True, sliding_window=16, layer_types=["sliding_attention", "full_attention"],
+              tie_embeddings=False, num_experts=4, experts_per_tok=2, moe_activation="gpt_oss", moe_bias=True,
+              intermediate=256)
+    exact, near = _run(ov, steps=16, prompt_lens=[33, 9])
+    assert near <= 0.05 * (exact + near)
+    exact, near = _run(dict(num_experts=8, experts_per_tok=2, moe_routing="softmax_topk", intermediate=128), steps=8,
+                       prompt_lens=[12, 20, 5])
+    assert near <= 0.05 * (exact + near)
+
+
 def test_tiny_cuda_graph_decode_matches_oracle():
     exact, near = _run({}, steps=40, prompt_lens=[30, 31, 500], cuda_graph=True)
     assert near <= 0.05 * (exact + near)

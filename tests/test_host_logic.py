@@ -227,3 +227,34 @@ def test_oracle_moe_routing_and_activation_semantics():
     assert abs(a[1]) < 1e-30                                                            # sigmoid(-170) kills it
     np.testing.assert_allclose(a[2], 1.0 / (1.0 + np.exp(-1.702)) * 1.5, rtol=1e-6)
     np.testing.assert_allclose(moe.activation(g[2:], u[2:], "silu"), 1.0 / (1.0 + np.exp(-1.0)) * 0.5, rtol=1e-6)
+
+
+def test_switch_linear_shards_are_slices_of_the_stacked_experts():
+    """Tensor-parallel MoE: gate / up shard every expert's output rows, down shards K on group boundaries with the
+    dense bias on rank 0 only -- literal slices of the packed tensors, and the rank partials add up to the whole."""
+    import torch
+
+    from oracle import affine_quant as oq
+    from vllm_metal_b200.quant.switch_linear import QuantizedSwitchLinear
+
+    g = torch.Generator().manual_seed(3)
+    sw = QuantizedSwitchLinear.from_dense(torch.randn((3, 64, 256), generator=g) * 0.1, torch.randn((3, 64), generator=g),
+                                          64, 4, torch.bfloat16)
+    up = [sw.shard_rows(r, 2) for r in range(2)]
+    assert torch.equal(torch.cat([u.weight for u in up], 1), sw.weight)
+    assert torch.equal(torch.cat([u.bias for u in up], 1), sw.bias)
+    down = [sw.shard_cols(r, 2) for r in range(2)]
+    assert down[0].bias is not None and down[1].bias is None and down[0].in_features == 128
+    assert torch.equal(torch.cat([d.scales for d in down], 2), sw.scales)
+
+    def dense(m, e):
+        return oq.dequantize(m.weight[e].numpy().view(np.uint32), m.scales[e].float().numpy(), m.biases[e].float().numpy(),
+                             m.group_size, m.bits).astype(np.float64)
+
+    x = torch.randn((5, 256), generator=g).double().numpy()
+    for e in range(3):
+        full = x @ dense(sw, e).T
+        part = sum(x[:, r * 128:(r + 1) * 128] @ dense(down[r], e).T for r in range(2))
+        np.testing.assert_allclose(part, full, rtol=1e-10, atol=1e-10)
+    with pytest.raises(ValueError):
+        sw.shard_cols(0, 8)  # 256 / 8 = 32 is not a multiple of the group size

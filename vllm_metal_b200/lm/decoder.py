@@ -45,6 +45,12 @@ class ModelArgs:
     bits: int = 4
     group_size: int = 64
     mlp: bool = True  # False: attention block only (gpt-oss config: MoE MLP out of scope)
+    # mixture-of-experts MLP (quant/switch_linear.py): > 0 experts replaces the dense MLP of every layer
+    num_experts: int = 0
+    experts_per_tok: int = 0
+    moe_activation: str = "silu"        # "silu" | "gpt_oss" (clipped SwiGLU)
+    moe_routing: str = "topk_softmax"   # gpt-oss; "softmax_topk" = Qwen3-MoE
+    moe_bias: bool = False
 
     def sliding_window_per_layer(self) -> list[int]:
         if not self.layer_types:
@@ -147,12 +153,50 @@ class MLP(nn.Module):
         return self.down_proj(get_ops().silu_mul(self.gate_up_proj(x)))
 
 
+class MoEMLP(nn.Module):
+    """Router + top-k quantized experts (gpt-oss / Qwen3-MoE wiring of mlx-lm); tensor parallel over the experts'
+    intermediate dimension, so the output is this rank's partial sum like the dense MLP's."""
+
+    def __init__(self, args: ModelArgs, gen, dtype, device, rank: int, world: int) -> None:
+        super().__init__()
+        from ..quant.switch_linear import MoEBlock, QuantizedSwitchLinear, Router, SwitchGLU
+
+        e, h, i = args.num_experts, args.hidden, args.intermediate
+
+        def rand(n, k, std):
+            w = torch.empty((e, n, k), dtype=torch.float32, device=device).normal_(0.0, std, generator=gen).to(dtype)
+            b = None
+            if args.moe_bias:
+                b = torch.empty((e, n), dtype=torch.float32, device=device).normal_(0.0, 0.02, generator=gen).to(dtype)
+            return QuantizedSwitchLinear.from_dense(w, b, args.group_size, args.bits, dtype)
+
+        glu = SwitchGLU(h, i // world, e, args.moe_bias, args.group_size, args.bits, dtype, device,
+                        activation=args.moe_activation)
+        glu.gate_proj = rand(i, h, 0.05).shard_rows(rank, world)
+        glu.up_proj = rand(i, h, 0.05).shard_rows(rank, world)
+        glu.down_proj = rand(h, i, 0.05).shard_cols(rank, world)
+        router = Router(h, e, args.moe_bias, dtype, device)
+        router.weight.copy_(torch.empty((e, h), dtype=torch.float32, device=device).normal_(0.0, 0.5, generator=gen))
+        if router.bias is not None:
+            router.bias.copy_(torch.empty((e,), dtype=torch.float32, device=device).normal_(0.0, 0.1, generator=gen))
+        self.block = MoEBlock(router, glu, args.experts_per_tok, args.moe_routing)
+        self.dtype = dtype
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.dtype != self.dtype:  # fp16 hand-over from the norm: the values are bf16-representable, the cast is exact
+            x = x.to(self.dtype)
+        return self.block(x)
+
+
 class DecoderLayer(nn.Module):
     def __init__(self, args: ModelArgs, gen, dtype, device, rank: int, world: int) -> None:
         super().__init__()
         self.self_attn = Attention(args, gen, dtype, device, rank, world)
         self.input_layernorm = RMSNorm(args.hidden, args.rms_eps, dtype, device)
-        self.mlp = MLP(args, gen, dtype, device, rank, world) if args.mlp else None
+        if args.mlp and args.num_experts > 0:
+            self.mlp = MoEMLP(args, gen, dtype, device, rank, world)
+        else:
+            self.mlp = MLP(args, gen, dtype, device, rank, world) if args.mlp else None
         self.post_attention_layernorm = RMSNorm(args.hidden, args.rms_eps, dtype, device) if args.mlp else None
 
 

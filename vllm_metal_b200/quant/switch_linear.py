@@ -68,6 +68,34 @@ class QuantizedSwitchLinear(nn.Module):
             m.bias.copy_(bias.to(dtype))
         return m
 
+    def _slice(self, rows: slice, groups: slice, words: slice, keep_bias: bool) -> QuantizedSwitchLinear:
+        w, sc, bi = self.weight[:, rows, words], self.scales[:, rows, groups], self.biases[:, rows, groups]
+        m = QuantizedSwitchLinear(sc.shape[2] * self.group_size, sc.shape[1], self.num_experts,
+                                  self.bias is not None and keep_bias, self.group_size, self.bits, self.scales.dtype,
+                                  self.weight.device)
+        m.weight.copy_(w)
+        m.scales.copy_(sc)
+        m.biases.copy_(bi)
+        if m.bias is not None:
+            m.bias.copy_(self.bias[:, rows])
+        return m
+
+    def shard_rows(self, rank: int, world: int) -> QuantizedSwitchLinear:
+        """Column-parallel: every expert's output rows [rank*N/world, ...) (gate / up of a tensor-parallel MoE)."""
+        n = self.out_features
+        if n % world:
+            raise ValueError(f"out_features {n} not divisible by world size {world}")
+        return self._slice(slice(rank * n // world, (rank + 1) * n // world), slice(None), slice(None), True)
+
+    def shard_cols(self, rank: int, world: int) -> QuantizedSwitchLinear:
+        """Row-parallel along K on group boundaries (down); the dense bias stays on rank 0."""
+        k = self.in_features
+        if k % world or (k // world) % self.group_size:
+            raise ValueError(f"in_features {k} / {world} must be a multiple of group_size {self.group_size}")
+        kw = k // world
+        return self._slice(slice(None), slice(rank * kw // self.group_size, (rank + 1) * kw // self.group_size),
+                           slice(rank * kw * self.bits // 32, (rank + 1) * kw * self.bits // 32), rank == 0)
+
     def forward_sorted(self, x_sorted: torch.Tensor, counts: list[int]) -> torch.Tensor:
         """``x_sorted`` ``[P, K]``: rows grouped by expert (``counts[e]`` consecutive rows for expert e).  One quantized
         GEMM per expert that has rows; returns ``[P, N]``."""
@@ -143,6 +171,25 @@ class SwitchGLU(nn.Module):
         return out.reshape(t, k, -1)
 
 
+class Router(nn.Module):
+    """Dense router ``x @ W^T (+ b)`` (mlx-lm: ``nn.Linear(hidden, num_experts)``): fp32 accumulate, logits rounded to
+    the activation dtype."""
+
+    def __init__(self, hidden: int, num_experts: int, bias: bool, dtype: torch.dtype = torch.bfloat16, device=None) -> None:
+        super().__init__()
+        self.register_buffer("weight", torch.zeros((num_experts, hidden), dtype=dtype, device=device))
+        if bias:
+            self.register_buffer("bias", torch.zeros((num_experts,), dtype=dtype, device=device))
+        else:
+            self.bias = None
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        y = x.float() @ self.weight.float().t()
+        if self.bias is not None:
+            y = y + self.bias.float()
+        return y.to(x.dtype)
+
+
 class MoEBlock(nn.Module):
     """Router + top-k experts + weighted sum.
 
@@ -157,14 +204,18 @@ class MoEBlock(nn.Module):
             raise ValueError(f"unknown routing {routing!r}")
         self.router, self.experts, self.top_k = router, experts, int(top_k)
         self.routing, self.norm_topk_prob = routing, norm_topk_prob
+        self.trace: list | None = None  # tests: a list collects (indices, scores) of every forward
 
     def route(self, x: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
         logits = self.router(x).float()
+        # stable descending sort: equal scores (bf16-rounded logits do tie) go to the lowest expert id, on every rank
+        # and in the oracle alike -- torch.topk leaves the order of ties unspecified
         if self.routing == "topk_softmax":
-            vals, idx = torch.topk(logits, self.top_k, dim=-1)
-            return idx, torch.softmax(vals, dim=-1)
+            vals, idx = torch.sort(logits, dim=-1, descending=True, stable=True)
+            return idx[:, :self.top_k], torch.softmax(vals[:, :self.top_k], dim=-1)
         probs = torch.softmax(logits, dim=-1)
-        vals, idx = torch.topk(probs, self.top_k, dim=-1)
+        vals, idx = torch.sort(probs, dim=-1, descending=True, stable=True)
+        vals, idx = vals[:, :self.top_k], idx[:, :self.top_k]
         if self.norm_topk_prob:
             vals = vals / vals.sum(dim=-1, keepdim=True)
         return idx, vals
@@ -173,6 +224,8 @@ class MoEBlock(nn.Module):
         lead = x.shape[:-1]
         x2 = x.reshape(-1, x.shape[-1])
         idx, scores = self.route(x2)
+        if self.trace is not None:
+            self.trace.append((idx.cpu().numpy(), scores.cpu().numpy()))
         y = self.experts(x2, idx)  # [T, k, hidden]
         out = (y.float() * scores[..., None]).sum(dim=1).to(x.dtype)
         return out.reshape(*lead, -1)

@@ -103,7 +103,9 @@ class PagedModelRunner:
         self.block_size = kv_cache.block_size
         self.max_batch = max_batch
         self.max_blocks = (max_model_len + self.block_size - 1) // self.block_size
-        self.use_cuda_graph = use_cuda_graph
+        # the MoE expert path reads its per-expert row counts back to the host every block: not capturable
+        has_moe = any(hasattr(getattr(layer, "mlp", None), "block") for layer in getattr(model, "layers", []))
+        self.use_cuda_graph = use_cuda_graph and not has_moe
         self.group_block_sizes: tuple[int, ...] | None = None  # set by the worker for multi-group KV layouts
         self.buf = StepBuffers(max_batch, self.max_blocks, self.device)
         self._graphs: dict[tuple[int, int, bool], torch.cuda.CUDAGraph] = {}
