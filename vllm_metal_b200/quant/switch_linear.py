@@ -131,6 +131,16 @@ def _sort_pairs(indices: torch.Tensor, num_experts: int) -> tuple[torch.Tensor, 
     return order, counts
 
 
+def _f16_operand(x: torch.Tensor, lin: QuantizedSwitchLinear) -> torch.Tensor:
+    """The tensor-core linears multiply fp16 operands and would cast every expert's slice of a bf16 ``x`` on their own
+    (one more launch per expert): cast the gathered rows once for all experts.  Exact: the values are bf16."""
+    ops = get_ops()
+    if (x.dtype == torch.bfloat16 and lin.scales.dtype == torch.bfloat16 and lin.in_features % 64 == 0
+            and x.data_ptr() % 16 == 0 and x.stride(0) % 8 == 0 and getattr(ops, "_qlinear_kernel", 0) != 1):
+        return ops.cast_f16(x)
+    return x
+
+
 def _act_silu(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
     return torch.nn.functional.silu(gate) * up
 
@@ -162,10 +172,11 @@ class SwitchGLU(nn.Module):
         order, counts = _sort_pairs(indices, self.gate_proj.num_experts)
         token_of_pair = torch.div(order, k, rounding_mode="floor")
         xs = x.index_select(0, token_of_pair).contiguous()  # rows grouped by expert: gathered once for gate and up
+        xs = _f16_operand(xs, self.gate_proj)
         g = self.gate_proj.forward_sorted(xs, counts)
         u = self.up_proj.forward_sorted(xs, counts)
         h = ACTIVATIONS[self.activation](g.float(), u.float()).to(g.dtype)
-        ys = self.down_proj.forward_sorted(h, counts)
+        ys = self.down_proj.forward_sorted(_f16_operand(h, self.down_proj), counts)
         out = torch.empty_like(ys)
         out.index_copy_(0, order, ys)
         return out.reshape(t, k, -1)
