@@ -214,6 +214,16 @@ int b200_qlinear(const void* x, const uint32_t* w, const void* scales,
                  int K, int group_size, int bits, int x_dtype, int dtype, int sb_dtype,
                  int64_t x_stride, int64_t y_stride, void* stream);
 
+/* Stacked experts (mixture-of-experts MLP): `mx.gather_qmm(x, w, scales, biases, rhs_indices, transpose=True, ...)` of
+ * mlx-lm's QuantizedSwitchLinear (named in vllm_metal/quant/awq_loader.py:171-173) over rows ALREADY GROUPED by
+ * expert.  w [E, N, K*bits/32], scales / biases [E, N, K/group_size], bias [E, N] or NULL, all contiguous;
+ * counts: HOST int32 [E]; expert e multiplies the counts[e] rows of x that follow the rows of experts 0..e-1, results
+ * in the same rows of y.  One b200_qlinear launch per expert with rows, same kernels and bits as b200_qlinear. */
+int b200_qlinear_experts(const void* x, const uint32_t* w, const void* scales, const void* biases,
+                         const void* bias, void* y, const int32_t* counts, int num_experts, int N, int K,
+                         int group_size, int bits, int x_dtype, int dtype, int sb_dtype, int64_t x_stride,
+                         int64_t y_stride, void* stream);
+
 /* Test / tuning knob: which kernel b200_qlinear runs.  0 = auto (tcgen05 + TMEM + TMA kernel
  * whenever the shape qualifies, else the mma.sync kernel), 1 = always the mma.sync kernel,
  * 2 = tcgen05 kernel or B200_ERR_UNSUPPORTED.  Process-wide; returns 0 on success. */

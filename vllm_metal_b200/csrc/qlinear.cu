@@ -562,3 +562,36 @@ extern "C" int b200_dequantize_rows(const uint32_t* w, const void* scales, const
     return check_launch("dequantize_rows_kernel");
   });
 }
+
+
+// Stacked-expert form (mx.gather_qmm over rows already grouped by expert; mlx-lm QuantizedSwitchLinear, named in
+// vllm_metal/quant/awq_loader.py:171-173): expert e multiplies the `counts[e]` consecutive rows of x that follow the
+// rows of experts 0..e-1.  One b200_qlinear launch per expert that has rows, issued from this one call -- the host
+// cost per expert is a C loop iteration, not a trip through the Python shim.
+extern "C" int b200_qlinear_experts(const void* x, const uint32_t* w, const void* scales, const void* biases,
+                                    const void* bias, void* y, const int32_t* counts, int num_experts, int N, int K,
+                                    int group_size, int bits, int x_dtype, int dtype, int sb_dtype, int64_t x_stride,
+                                    int64_t y_stride, void* stream) {
+  using namespace b200;
+  B200_CHECK_ARG(counts && num_experts > 0, "qlinear_experts: bad arguments");
+  int rc = check_quant_args("qlinear_experts", N, K, group_size, bits, sb_dtype);
+  if (rc != B200_OK) return rc;
+  const size_t w_words = (size_t)N * ((size_t)K * bits / 32);
+  const size_t sb_bytes = (size_t)N * (K / group_size) * dtype_size(sb_dtype);
+  const size_t xe = dtype_size(x_dtype), ye = dtype_size(dtype);
+  int64_t at = 0;
+  for (int e = 0; e < num_experts; ++e) {
+    const int c = counts[e];
+    B200_CHECK_ARG(c >= 0, "qlinear_experts: negative row count for expert %d", e);
+    if (c == 0) continue;
+    rc = b200_qlinear(reinterpret_cast<const char*>(x) + (size_t)at * x_stride * xe, w + e * w_words,
+                      reinterpret_cast<const char*>(scales) + e * sb_bytes,
+                      reinterpret_cast<const char*>(biases) + e * sb_bytes,
+                      bias ? reinterpret_cast<const char*>(bias) + (size_t)e * N * ye : nullptr,
+                      reinterpret_cast<char*>(y) + (size_t)at * y_stride * ye, c, N, K, group_size, bits, x_dtype, dtype,
+                      sb_dtype, x_stride, y_stride, stream);
+    if (rc != B200_OK) return rc;
+    at += c;
+  }
+  return B200_OK;
+}

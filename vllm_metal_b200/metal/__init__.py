@@ -96,6 +96,7 @@ EXPORTED_SYMBOLS = (
     "b200_paged_attention",
     "b200_paged_attention_static_scratch",
     "b200_qlinear",
+    "b200_qlinear_experts",
     "b200_qlinear_prepack",
     "b200_qlinear_prepacked",
     "b200_set_qlinear_variant",
@@ -173,6 +174,8 @@ def load_library() -> ctypes.CDLL:
     lib.b200_copy_blocks.argtypes = [vp, vp, vp, vp, i32, i64, i64, vp]
     lib.b200_qlinear.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, vp]
     lib.b200_qlinear_prepacked.argtypes = lib.b200_qlinear.argtypes
+    lib.b200_qlinear_experts.argtypes = [vp, vp, vp, vp, vp, vp, ctypes.POINTER(ctypes.c_int32), i32, i32, i32, i32, i32,
+                                         i32, i32, i32, i64, i64, vp]
     lib.b200_qlinear_prepack.argtypes = [vp, vp, i32, i32, i32, i32, vp]
     lib.b200_dequantize_rows.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
     lib.b200_qstream_blob_bytes.restype = ctypes.c_int64
@@ -512,6 +515,33 @@ class _Ops:
         self._check(rc)
         self.launches += n_launch
         return out.reshape(*lead, n_out)
+
+    def quantized_matmul_experts(self, x, w, scales, biases, counts, group_size: int = 64, bits: int = 4, bias=None):
+        """``mx.gather_qmm`` over rows grouped by expert: ``x`` ``[P, K]`` (bf16 / fp16), stacked ``w`` ``[E, N,
+        K*bits/32]``, ``scales`` / ``biases`` ``[E, N, K/g]``, ``bias`` ``[E, N]`` or None, ``counts`` host ints [E]
+        (rows per expert, in order).  One C call; one kernel launch per expert that has rows."""
+        for n, t in (("x", x), ("w", w), ("scales", scales), ("biases", biases)):
+            _require_cuda(n, t)
+        e, n_out, words = w.shape
+        k = words * 32 // bits
+        if x.dim() != 2 or x.shape[1] != k or x.stride(1) != 1:
+            raise ValueError(f"x must be [P, {k}] with unit inner stride, got {tuple(x.shape)}")
+        if len(counts) != e or sum(counts) != x.shape[0]:
+            raise ValueError(f"counts must hold {e} row counts adding up to {x.shape[0]}")
+        if scales.shape != (e, n_out, k // group_size) or biases.shape != scales.shape or scales.dtype != biases.dtype:
+            raise ValueError(f"scales/biases must be [{e}, {n_out}, {k // group_size}] of one dtype")
+        odt = torch.bfloat16 if (x.dtype == torch.float16 and scales.dtype == torch.bfloat16) else x.dtype
+        out = torch.empty((x.shape[0], n_out), dtype=odt, device=x.device)
+        if bias is not None:
+            bias = bias.to(dtype=odt).contiguous()
+        c_arr = (ctypes.c_int32 * e)(*[int(c) for c in counts])
+        rc = self._lib.b200_qlinear_experts(
+            x.data_ptr(), w.contiguous().data_ptr(), scales.contiguous().data_ptr(), biases.contiguous().data_ptr(),
+            _ptr(bias), out.data_ptr(), c_arr, e, n_out, k, group_size, bits, _dtype_code("x", x), _dtype_code("out", out),
+            _dtype_code("scales", scales), x.stride(0), out.stride(0), _stream())
+        self._check(rc)
+        self.launches += sum(1 for c in counts if c)
+        return out
 
     def qlinear_prepack(self, w, bits: int = 4, inverse: bool = False, out=None):
         """Load-time repack of an MLX-layout packed weight into the streaming layout (same shape)."""

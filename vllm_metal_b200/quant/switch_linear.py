@@ -7,7 +7,8 @@ expert weights ``[E, N, K*bits/32]`` (third-party arithmetic: mlx 0.32.0 / mlx-l
 /root/reference -> parity unpinned, semantics restated in oracle/moe.py).  Same attribute names and shapes here.
 
 B200 form: the (token, expert) pairs are sorted by expert and every expert that received rows runs ONE affine
-quantized GEMM over its gathered rows through the same C-ABI kernels as the dense linears (`b200_qlinear`): each
+quantized GEMM over its gathered rows through the same kernels as the dense linears (`b200_qlinear_experts`: one
+C-ABI call per projection that loops over the experts): each
 expert's weights are streamed once per step however many tokens picked it.  The per-expert row counts are read back
 to the host once per block (one small D2H copy): this is the functional path of row N2 -- launch-bound at decode
 batch sizes (3 x experts-hit launches per layer); a grouped persistent kernel is the next step and is not built.
@@ -97,19 +98,10 @@ class QuantizedSwitchLinear(nn.Module):
                            slice(rank * kw * self.bits // 32, (rank + 1) * kw * self.bits // 32), rank == 0)
 
     def forward_sorted(self, x_sorted: torch.Tensor, counts: list[int]) -> torch.Tensor:
-        """``x_sorted`` ``[P, K]``: rows grouped by expert (``counts[e]`` consecutive rows for expert e).  One quantized
-        GEMM per expert that has rows; returns ``[P, N]``."""
-        ops = get_ops()
-        out = torch.empty((x_sorted.shape[0], self.out_features), dtype=self.scales.dtype, device=x_sorted.device)
-        at = 0
-        for e, c in enumerate(counts):
-            if c == 0:
-                continue
-            ops.quantized_matmul(x_sorted[at:at + c], self.weight[e], self.scales[e], self.biases[e], transpose=True,
-                                 group_size=self.group_size, bits=self.bits,
-                                 bias=None if self.bias is None else self.bias[e], out=out[at:at + c])
-            at += c
-        return out
+        """``x_sorted`` ``[P, K]``: rows grouped by expert (``counts[e]`` consecutive rows for expert e).  One C-ABI call
+        (``b200_qlinear_experts``) that launches one quantized GEMM per expert with rows; returns ``[P, N]``."""
+        return get_ops().quantized_matmul_experts(x_sorted, self.weight, self.scales, self.biases, counts,
+                                                  self.group_size, self.bits, bias=self.bias)
 
     def forward(self, x: torch.Tensor, indices: torch.Tensor) -> torch.Tensor:
         """``mx.gather_qmm`` form: ``x`` ``[T, K]`` (shared by a token's experts) or ``[T, k, K]``; ``indices``
@@ -118,7 +110,7 @@ class QuantizedSwitchLinear(nn.Module):
         order, counts = _sort_pairs(indices, self.num_experts)
         rows = x if x.dim() == 3 else x[:, None, :].expand(t, k, x.shape[-1])
         xs = rows.reshape(t * k, -1).index_select(0, order)
-        ys = self.forward_sorted(xs.contiguous(), counts)
+        ys = self.forward_sorted(_f16_operand(xs.contiguous(), self), counts)
         out = torch.empty_like(ys)
         out.index_copy_(0, order, ys)
         return out.reshape(t, k, -1)
